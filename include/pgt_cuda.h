@@ -1,0 +1,149 @@
+/* pgt_cuda.h -- C-ABI of libpgt_cuda.so: the B200 (sm_100a) implementation of PyGlassTools'
+ * Irving-Kirkwood / thermo pair-sum hot path.
+ *
+ * Plain C, opaque handle, plain pointers and sizes; no C++/torch types cross this boundary.
+ * Every entry point returns 0 on success or a negative pgt_status; pgt_last_error(ctx) gives
+ * the message.  The caller owns every host buffer, the library owns every device buffer.
+ * One pgt_ctx drives ONE device on ONE stream; multi-GPU = one ctx (and normally one process)
+ * per device, each given a shard [g0,g1) of the grid points (pgt_grid_set_shard).
+ *
+ * Each entry point names the reference interface (file:line under /root/reference/pyglasstools/)
+ * whose role it takes over.  There is no CPU fallback behind this header: without a CUDA device
+ * pgt_ctx_create fails.
+ */
+#ifndef PGT_CUDA_H
+#define PGT_CUDA_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct pgt_ctx pgt_ctx;
+
+typedef enum {
+    PGT_OK = 0,
+    PGT_ERR_CUDA = -1,        /* a CUDA runtime call or kernel failed */
+    PGT_ERR_ARG = -2,         /* invalid argument / call order */
+    PGT_ERR_UNSUPPORTED = -3, /* valid in the reference, not implemented on device (3-D, adaptive quadrature, ...) */
+    PGT_ERR_STATE = -4,       /* a required earlier stage has not run */
+    PGT_ERR_DATA = -5,        /* the frame violates a documented precondition (box too small, z != 0 in 2-D, ...) */
+    PGT_ERR_NCCL = -6
+} pgt_status;
+
+/* pair-model ids: the eight classes exported by potential/module-potential.cpp:13-34 */
+enum { PGT_POT_LJ = 0, PGT_POT_FORCESHIFTED_LJ = 1, PGT_POT_POLY12 = 2, PGT_POT_POLY18 = 3, PGT_POT_POLY10 = 4,
+       PGT_POT_POLY106 = 5, PGT_POT_POLYYUKAWA = 6, PGT_POT_POLYLJ = 7 };
+/* coarse-graining kernels: irvingkirkwood/cgfunc/module-cgfunc.cpp:12-19 */
+enum { PGT_CG_OCTIC = 0, PGT_CG_RECT = 1, PGT_CG_MOLLIFIER = 2 };
+/* quadrature modes: FixedPointCGFunc (CoarseGrainFunction.h:56-92); adaptive (:94-134) is PGT_ERR_UNSUPPORTED */
+enum { PGT_QUAD_FIXEDPOINT = 0, PGT_QUAD_ADAPTIVE = 1 };
+/* observable masks */
+enum { PGT_OBS_VIRIAL = 1u, PGT_OBS_KINETIC = 2u, PGT_OBS_DENSITY = 4u,      /* IK fields */
+       PGT_OBS_ENERGY = 8u, PGT_OBS_BORN = 16u };                           /* thermo only */
+/* observable ids for downloads */
+enum { PGT_FIELD_VIRIAL = 0, PGT_FIELD_KINETIC = 1, PGT_FIELD_DENSITY = 2 };
+/* stage ids for pgt_stage_time_ms */
+enum { PGT_STAGE_UPLOAD = 0, PGT_STAGE_CELLS = 1, PGT_STAGE_BONDS = 2, PGT_STAGE_IK = 3, PGT_STAGE_THERMO = 4,
+       PGT_STAGE_DOWNLOAD = 5, PGT_STAGE_COUNT = 6 };
+
+/* ---- context ------------------------------------------------------------------------------- */
+/* Replaces: MPI::Communicator construction at import (module-pyglasstools.cpp:50-58).          */
+int pgt_ctx_create(int device, pgt_ctx** out);
+int pgt_ctx_destroy(pgt_ctx* ctx);
+const char* pgt_last_error(const pgt_ctx* ctx);      /* ctx may be NULL: last create error */
+int pgt_device_count(int* n);
+int pgt_synchronize(pgt_ctx* ctx);
+/* The CUDA stream (cudaStream_t) every kernel of this ctx is launched on, for event timing. */
+void* pgt_stream(pgt_ctx* ctx);
+
+/* ---- models -------------------------------------------------------------------------------- */
+/* Replaces: ShortRangePairPotential<M>(scaled_rcut, params) (potential/PairPotential.h:69-123).
+ * params: the vector the Python factories build (potential/__init__.py:78-143).               */
+int pgt_potential_set(pgt_ctx* ctx, int model_id, double scaled_rcut, const double* params, int nparams);
+/* Replaces: FixedPointCGFunc<D>(order, rcut) (cgfunc/CoarseGrainFunction.h:56-92) and the GSL
+ * glfixed table (cgfunc/FixedPointQuadrature.h:35).                                            */
+int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int order);
+/* Replaces: Calculator::max_rcut, frozen at construction (Calculator.h:37-46).                 */
+int pgt_set_max_rcut(pgt_ctx* ctx, double max_rcut);
+/* Optional tuning: target cell side of the device cell list (default max_rcut/2).              */
+int pgt_set_cell_size(pgt_ctx* ctx, double cell_side);
+
+/* ---- frame --------------------------------------------------------------------------------- */
+/* Replaces: ParticleSystem ctor + setParticleSystemData + init_neighbour_search
+ * (ParticleSystem.cc:3-30; Aboria NeighbourSearchBase.h:208-237) and SimBox (SimBox.cc:25-52).
+ * pos: N x 3 (float or double), diam: N, mass: N or NULL (=1), vel: N x 3 or NULL (=0).
+ * box: Lx,Ly,Lz (Lz forced to 1 when dim==2 as utils.py:15-16 does).  Host pointers; the copy
+ * is asynchronous on the ctx stream from the caller's (ideally pinned) memory.               */
+int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel,
+                     int is_f32, int64_t N, const double box[3], int dim);
+/* Same, from DEVICE pointers already resident in HBM on ctx's device (no host copy).           */
+int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, const void* d_mass, const void* d_vel,
+                         int is_f32, int64_t N, const double box[3], int dim);
+/* Stage 1: wrap/kill + counting-sort cell list.  Replaces Aboria CellList build (CellList.h:143-194). */
+int pgt_build_cells(pgt_ctx* ctx);
+/* Stages 2-3: pair forces + per-particle compacted half-bond list.  Replaces the inner
+ * euclidean_search + getPairForceDivR of IrvingKirkwood.h:93-105.                              */
+int pgt_build_bonds(pgt_ctx* ctx);
+int pgt_frame_counts(pgt_ctx* ctx, int64_t* n_live, int64_t* n_halfbonds, int64_t* n_cells);
+
+/* ---- grid ---------------------------------------------------------------------------------- */
+/* Replaces: ikcalculator grid construction + scatter_v (irvingkirkwood/__init__.py:45-63).
+ * Cartesian: point g = i*ny + j at (xs[i], ys[j], 0), i-major.                                 */
+int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double* ys, int ny);
+/* Arbitrary points (radialcalculator, irvingkirkwood/__init__.py:80-166): xyz is G x 3.        */
+int pgt_grid_set_points(pgt_ctx* ctx, const double* xyz, int64_t G);
+/* This ctx computes global points [g0,g1) (np.array_split boundaries are the caller's job).    */
+int pgt_grid_set_shard(pgt_ctx* ctx, int64_t g0, int64_t g1);
+
+/* ---- compute ------------------------------------------------------------------------------- */
+/* Stages 4-5.  Replaces IrvingKirkwood::compute (irvingkirkwood/IrvingKirkwood.h:74-110).      */
+int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask);
+/* Copies a field of the local shard to host: (g1-g0) x Dim*Dim doubles, col-major per point
+ * (index a + Dim*b, CoarseGrainedField.h:160-183), or (g1-g0) doubles for the density.         */
+int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out);
+/* Device pointer of a field of the local shard (for NCCL / zero-copy consumers).               */
+int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubles);
+/* Stage 6.  Replaces ThermoCalculator::compute + divideByVolume (thermo/ThermoCalculator.h:58-90).
+ * out layout (doubles): [0..Dim^2) virial, [Dim^2..2Dim^2) kinetic, [2Dim^2] potential energy,
+ * then Dim^4 Born tensor (col-major flat); all already multiplied by 1/vol.  Entries whose
+ * observable is not in obs_mask are 0.  out must hold 2*Dim^2 + 1 + Dim^4 doubles.              */
+int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out);
+
+/* ---- parity exports / instrumentation ------------------------------------------------------ */
+/* Ordered force-carrying pairs (orig_i, orig_j) and r_ij = r_i - r_j(image) as the reference's
+ * inner loop sees them; call with cap=0 to get the count.                                      */
+int pgt_export_bonds(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j, double* rij_xy, double* fdivr);
+/* Ordered neighbour pairs within max_rcut (inclusive), force-carrying or not.                  */
+int pgt_export_neighbors(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j);
+/* Wrapped positions in original order (x,y per particle) and alive flags.                      */
+int pgt_export_wrapped(pgt_ctx* ctx, double* xy, uint8_t* alive);
+/* Device time of the last execution of a stage (CUDA events on the ctx stream).                */
+int pgt_stage_time_ms(pgt_ctx* ctx, int stage, float* ms);
+/* Number of kernels launched by this ctx since creation.                                       */
+int64_t pgt_kernel_launches(const pgt_ctx* ctx);
+/* Scalar host-side evaluation of the pair model (getPairEnergy/ForceDivR/BondStiffness/getRcut;
+ * PairPotential.h:92-122) and CG kernel; what: 0 energy, 1 force/r, 2 stiffness, 3 rcut^2.     */
+double pgt_pair_eval(int model_id, double scaled_rcut, const double* params, int nparams,
+                     const double rij[3], double di, double dj, int what);
+double pgt_cg_delta(int kernel_id, double cg_rcut, double dr_sq);
+double pgt_cg_bond(int kernel_id, double cg_rcut, int order, const double x[3], const double ri[3], const double rij[3]);
+/* FP64 FMA peak probe: runs a dependent-chain DFMA kernel, returns achieved TFLOP/s.            */
+int pgt_fp64_peak_probe(pgt_ctx* ctx, double* tflops);
+
+/* ---- multi-GPU (NCCL over NVLink) ---------------------------------------------------------- */
+/* 128-byte NCCL unique id, to be broadcast by the caller's own plumbing.                       */
+int pgt_comm_unique_id(void* id128);
+int pgt_comm_init(pgt_ctx* ctx, int nranks, int rank, const void* id128);
+/* Final field gather: every rank contributes its shard, out_dev (device, G_total*ncomp doubles
+ * on every rank) receives all shards in rank order.  counts[r] = doubles contributed by rank r. */
+int pgt_comm_allgather_field(pgt_ctx* ctx, int field_id, const int64_t* counts, void* out_dev);
+/* Sum-reduce n doubles in place on the host buffer via the device (thermo partial sums).       */
+int pgt_comm_allreduce_sum(pgt_ctx* ctx, double* inout_host, int n);
+int pgt_comm_destroy(pgt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PGT_CUDA_H */

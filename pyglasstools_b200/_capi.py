@@ -1,0 +1,297 @@
+"""ctypes binding of libpgt_cuda.so (include/pgt_cuda.h).
+
+This is the only door from Python into the CUDA library.  There is no fallback: if the shared
+library is missing or no CUDA device is present, importing / creating a context raises.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libpgt_cuda.so")
+
+POT_IDS = {"lj": 0, "forceshifted-lj": 1, "poly12": 2, "poly18": 3, "poly10": 4, "poly106": 5, "polyyukawa": 6,
+           "polylj": 7}
+CG_IDS = {"octic": 0, "rect": 1, "mollifier": 2}
+OBS_VIRIAL, OBS_KINETIC, OBS_DENSITY, OBS_ENERGY, OBS_BORN = 1, 2, 4, 8, 16
+FIELD_VIRIAL, FIELD_KINETIC, FIELD_DENSITY = 0, 1, 2
+STAGES = {"upload": 0, "cells": 1, "bonds": 2, "ik": 3, "thermo": 4, "download": 5}
+
+EXPORTED = [
+    "pgt_ctx_create", "pgt_ctx_destroy", "pgt_last_error", "pgt_device_count", "pgt_synchronize", "pgt_stream",
+    "pgt_potential_set", "pgt_cg_set", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
+    "pgt_frame_set_device", "pgt_build_cells", "pgt_build_bonds", "pgt_frame_counts", "pgt_grid_set_cartesian",
+    "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_device_ptr",
+    "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
+    "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
+    "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
+]
+
+_lib = None
+
+
+class PgtError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("libpgt_cuda error %d: %s" % (code, msg))
+        self.code = code
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError("%s not found: build it with `make -C pyglasstools_b200/csrc` "
+                              "(there is no CPU fallback)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        L.pgt_last_error.restype = C.c_char_p
+        L.pgt_last_error.argtypes = [C.c_void_p]
+        L.pgt_stream.restype = C.c_void_p
+        L.pgt_stream.argtypes = [C.c_void_p]
+        L.pgt_kernel_launches.restype = C.c_int64
+        L.pgt_kernel_launches.argtypes = [C.c_void_p]
+        L.pgt_pair_eval.restype = C.c_double
+        L.pgt_pair_eval.argtypes = [C.c_int, C.c_double, C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double),
+                                    C.c_double, C.c_double, C.c_int]
+        L.pgt_cg_delta.restype = C.c_double
+        L.pgt_cg_delta.argtypes = [C.c_int, C.c_double, C.c_double]
+        L.pgt_cg_bond.restype = C.c_double
+        L.pgt_cg_bond.argtypes = [C.c_int, C.c_double, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double),
+                                  C.POINTER(C.c_double)]
+        L.pgt_ctx_create.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+        L.pgt_ctx_destroy.argtypes = [C.c_void_p]
+        L.pgt_synchronize.argtypes = [C.c_void_p]
+        L.pgt_potential_set.argtypes = [C.c_void_p, C.c_int, C.c_double, C.POINTER(C.c_double), C.c_int]
+        L.pgt_cg_set.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int]
+        L.pgt_set_max_rcut.argtypes = [C.c_void_p, C.c_double]
+        L.pgt_set_cell_size.argtypes = [C.c_void_p, C.c_double]
+        L.pgt_frame_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64,
+                                       C.POINTER(C.c_double), C.c_int]
+        L.pgt_frame_set_device.argtypes = L.pgt_frame_upload.argtypes
+        L.pgt_build_cells.argtypes = [C.c_void_p]
+        L.pgt_build_bonds.argtypes = [C.c_void_p]
+        L.pgt_frame_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.pgt_grid_set_cartesian.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int, C.POINTER(C.c_double), C.c_int]
+        L.pgt_grid_set_points.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int64]
+        L.pgt_grid_set_shard.argtypes = [C.c_void_p, C.c_int64, C.c_int64]
+        L.pgt_ik_compute.argtypes = [C.c_void_p, C.c_uint]
+        L.pgt_ik_download.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.pgt_ik_device_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
+        L.pgt_thermo_compute.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
+        L.pgt_export_bonds.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p,
+                                       C.c_void_p]
+        L.pgt_export_neighbors.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
+        L.pgt_export_wrapped.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        L.pgt_stage_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
+        L.pgt_fp64_peak_probe.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.pgt_comm_unique_id.argtypes = [C.c_void_p]
+        L.pgt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+        L.pgt_comm_allgather_field.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p]
+        L.pgt_comm_allreduce_sum.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int]
+        L.pgt_comm_destroy.argtypes = [C.c_void_p]
+        _lib = L
+    return _lib
+
+
+def _dp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class Context:
+    """One device, one stream (pgt_ctx)."""
+
+    def __init__(self, device=0):
+        self._h = C.c_void_p()
+        rc = lib().pgt_ctx_create(int(device), C.byref(self._h))
+        if rc != 0:
+            raise PgtError(rc, lib().pgt_last_error(None).decode())
+        self.device = device
+        self._keep = {}
+
+    def close(self):
+        if getattr(self, "_h", None) and self._h:
+            lib().pgt_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        if rc != 0:
+            raise PgtError(rc, lib().pgt_last_error(self._h).decode())
+
+    # models -----------------------------------------------------------------
+    def set_potential(self, model, scaled_rcut, params):
+        mid = POT_IDS[model] if isinstance(model, str) else int(model)
+        p = np.ascontiguousarray(params, np.float64)
+        self._ck(lib().pgt_potential_set(self._h, mid, float(scaled_rcut), _dp(p), len(p)))
+
+    def set_cg(self, kernel, rcut, order, mode=0):
+        kid = CG_IDS[kernel] if isinstance(kernel, str) else int(kernel)
+        self._ck(lib().pgt_cg_set(self._h, kid, float(rcut), int(mode), int(order)))
+
+    def set_max_rcut(self, v):
+        self._ck(lib().pgt_set_max_rcut(self._h, float(v)))
+
+    def set_cell_size(self, v):
+        self._ck(lib().pgt_set_cell_size(self._h, float(v)))
+
+    # frame ------------------------------------------------------------------
+    def upload(self, pos, diam, box, mass=None, vel=None, dim=2):
+        f32 = pos.dtype == np.float32
+        dt = np.float32 if f32 else np.float64
+        pos = np.ascontiguousarray(pos, dt)
+        diam = np.ascontiguousarray(diam, dt)
+        mass = None if mass is None else np.ascontiguousarray(mass, dt)
+        vel = None if vel is None else np.ascontiguousarray(vel, dt)
+        self._keep["frame"] = (pos, diam, mass, vel)      # the copy is asynchronous
+        b = (C.c_double * 3)(*[float(x) for x in box[:3]])
+        vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        self._ck(lib().pgt_frame_upload(self._h, vp(pos), vp(diam), vp(mass), vp(vel), int(f32), len(diam), b, dim))
+
+    def set_device_frame(self, d_pos, d_diam, n, box, is_f32=True, d_mass=None, d_vel=None, dim=2):
+        b = (C.c_double * 3)(*[float(x) for x in box[:3]])
+        self._ck(lib().pgt_frame_set_device(self._h, C.c_void_p(d_pos), C.c_void_p(d_diam),
+                                            C.c_void_p(d_mass) if d_mass else None,
+                                            C.c_void_p(d_vel) if d_vel else None, int(is_f32), int(n), b, dim))
+
+    def build_cells(self):
+        self._ck(lib().pgt_build_cells(self._h))
+
+    def build_bonds(self):
+        self._ck(lib().pgt_build_bonds(self._h))
+
+    def counts(self):
+        a, b, c = C.c_int64(), C.c_int64(), C.c_int64()
+        self._ck(lib().pgt_frame_counts(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return dict(n_live=a.value, n_halfbonds=b.value, n_cells=c.value)
+
+    # grid -------------------------------------------------------------------
+    def set_grid_cartesian(self, xs, ys):
+        xs = np.ascontiguousarray(xs, np.float64)
+        ys = np.ascontiguousarray(ys, np.float64)
+        self._ck(lib().pgt_grid_set_cartesian(self._h, _dp(xs), len(xs), _dp(ys), len(ys)))
+        self.G = len(xs) * len(ys)
+        self.g0, self.g1 = 0, self.G
+
+    def set_grid_points(self, xyz):
+        xyz = np.ascontiguousarray(xyz, np.float64).reshape(-1, 3)
+        self._ck(lib().pgt_grid_set_points(self._h, _dp(xyz), len(xyz)))
+        self.G = len(xyz)
+        self.g0, self.g1 = 0, self.G
+
+    def set_shard(self, g0, g1):
+        self._ck(lib().pgt_grid_set_shard(self._h, int(g0), int(g1)))
+        self.g0, self.g1 = int(g0), int(g1)
+
+    # compute ----------------------------------------------------------------
+    def ik_compute(self, obs_mask=OBS_VIRIAL):
+        self._ck(lib().pgt_ik_compute(self._h, int(obs_mask)))
+
+    def ik_download(self, field=FIELD_VIRIAL, out=None):
+        n = self.g1 - self.g0
+        shape = (n,) if field == FIELD_DENSITY else (n, 4)
+        if out is None:
+            out = np.empty(shape, np.float64)
+        self._ck(lib().pgt_ik_download(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def ik_device_ptr(self, field=FIELD_VIRIAL):
+        p, n = C.c_void_p(), C.c_int64()
+        self._ck(lib().pgt_ik_device_ptr(self._h, int(field), C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def thermo(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
+        out = np.zeros(25, np.float64)
+        self._ck(lib().pgt_thermo_compute(self._h, int(obs_mask), _dp(out)))
+        return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy())
+
+    # exports ----------------------------------------------------------------
+    def export_bonds(self):
+        n = C.c_int64()
+        self._ck(lib().pgt_export_bonds(self._h, 0, C.byref(n), None, None, None, None))
+        m = n.value
+        i, j = np.empty(m, np.int32), np.empty(m, np.int32)
+        rij, f = np.empty((m, 2)), np.empty(m)
+        if m:
+            vp = lambda a: a.ctypes.data_as(C.c_void_p)
+            self._ck(lib().pgt_export_bonds(self._h, m, C.byref(n), vp(i), vp(j), vp(rij), vp(f)))
+        return i, j, rij, f
+
+    def export_neighbors(self):
+        n = C.c_int64()
+        self._ck(lib().pgt_export_neighbors(self._h, 0, C.byref(n), None, None))
+        m = n.value
+        i, j = np.empty(m, np.int32), np.empty(m, np.int32)
+        if m:
+            vp = lambda a: a.ctypes.data_as(C.c_void_p)
+            self._ck(lib().pgt_export_neighbors(self._h, m, C.byref(n), vp(i), vp(j)))
+        return i, j
+
+    def export_wrapped(self, n):
+        xy = np.empty((n, 2))
+        alive = np.empty(n, np.uint8)
+        self._ck(lib().pgt_export_wrapped(self._h, xy.ctypes.data_as(C.c_void_p), alive.ctypes.data_as(C.c_void_p)))
+        return xy, alive.astype(bool)
+
+    # instrumentation ----------------------------------------------------------
+    def stage_ms(self, stage):
+        ms = C.c_float()
+        self._ck(lib().pgt_stage_time_ms(self._h, STAGES[stage] if isinstance(stage, str) else stage, C.byref(ms)))
+        return ms.value
+
+    def sync(self):
+        self._ck(lib().pgt_synchronize(self._h))
+
+    def stream(self):
+        return lib().pgt_stream(self._h)
+
+    def launches(self):
+        return lib().pgt_kernel_launches(self._h)
+
+    def fp64_peak(self):
+        t = C.c_double()
+        self._ck(lib().pgt_fp64_peak_probe(self._h, C.byref(t)))
+        return t.value
+
+    # nccl -------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        buf = (C.c_char * 128)()
+        rc = lib().pgt_comm_unique_id(buf)
+        if rc != 0:
+            raise PgtError(rc, lib().pgt_last_error(None).decode())
+        return bytes(buf)
+
+    def comm_init(self, nranks, rank, uid):
+        buf = (C.c_char * 128).from_buffer_copy(uid)
+        self._ck(lib().pgt_comm_init(self._h, nranks, rank, buf))
+
+    def comm_allgather_field(self, field, counts, out_dev_ptr):
+        c = (C.c_int64 * len(counts))(*[int(x) for x in counts])
+        self._ck(lib().pgt_comm_allgather_field(self._h, int(field), c, C.c_void_p(out_dev_ptr)))
+
+    def comm_allreduce_sum(self, arr):
+        a = np.ascontiguousarray(arr, np.float64)
+        self._ck(lib().pgt_comm_allreduce_sum(self._h, _dp(a), a.size))
+        return a
+
+
+def pair_eval(model, scaled_rcut, params, rij, di, dj, what):
+    p = np.ascontiguousarray(params, np.float64)
+    r = np.ascontiguousarray(rij, np.float64)
+    mid = POT_IDS[model] if isinstance(model, str) else int(model)
+    return lib().pgt_pair_eval(mid, float(scaled_rcut), _dp(p), len(p), _dp(r), float(di), float(dj), int(what))
+
+
+def cg_delta(kernel, rcut, dr_sq):
+    return lib().pgt_cg_delta(CG_IDS[kernel] if isinstance(kernel, str) else int(kernel), float(rcut), float(dr_sq))
+
+
+def cg_bond(kernel, rcut, order, x, ri, rij):
+    x, ri, rij = (np.ascontiguousarray(a, np.float64) for a in (x, ri, rij))
+    return lib().pgt_cg_bond(CG_IDS[kernel] if isinstance(kernel, str) else int(kernel), float(rcut), int(order),
+                             _dp(x), _dp(ri), _dp(rij))

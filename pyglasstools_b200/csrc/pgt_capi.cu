@@ -1,0 +1,994 @@
+// pgt_capi.cu -- context management and the C-ABI of libpgt_cuda.so (include/pgt_cuda.h).
+#include "pgt_cuda.h"
+#include "pgt_kernels.cuh"
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+namespace {
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+thread_local std::string g_create_error;
+
+// --- NCCL, resolved lazily with dlopen so the library loads (and single-GPU runs work) without it
+typedef struct { char internal[128]; } pgtNcclUniqueId;
+typedef void* pgtNcclComm;
+struct NcclApi {
+    void* handle = nullptr;
+    int (*GetUniqueId)(pgtNcclUniqueId*) = nullptr;
+    int (*CommInitRank)(pgtNcclComm*, int, pgtNcclUniqueId, int) = nullptr;
+    int (*CommDestroy)(pgtNcclComm) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, pgtNcclComm, cudaStream_t) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, pgtNcclComm, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+};
+NcclApi g_nccl;
+
+bool load_nccl(std::string& err)
+{
+    if (g_nccl.ok) return true;
+    const char* names[] = { "libnccl.so.2", "libnccl.so" };
+    for (const char* n : names) {
+        g_nccl.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (g_nccl.handle) break;
+    }
+    if (!g_nccl.handle) { err = std::string("cannot dlopen libnccl: ") + dlerror(); return false; }
+#define PGT_SYM(field, name)                                                      \
+    *(void**)(&g_nccl.field) = dlsym(g_nccl.handle, name);                        \
+    if (!g_nccl.field) { err = std::string("libnccl lacks ") + name; return false; }
+    PGT_SYM(GetUniqueId, "ncclGetUniqueId")
+    PGT_SYM(CommInitRank, "ncclCommInitRank")
+    PGT_SYM(CommDestroy, "ncclCommDestroy")
+    PGT_SYM(AllReduce, "ncclAllReduce")
+    PGT_SYM(Broadcast, "ncclBroadcast")
+    PGT_SYM(GroupStart, "ncclGroupStart")
+    PGT_SYM(GroupEnd, "ncclGroupEnd")
+    PGT_SYM(GetErrorString, "ncclGetErrorString")
+#undef PGT_SYM
+    g_nccl.ok = true;
+    return true;
+}
+
+// Gauss-Legendre nodes on [-1,1] by Newton iteration in long double (independent of the oracle's tables).
+void gauss_legendre_half(int n, std::vector<double>& x, std::vector<double>& w)
+{
+    const int m = (n + 1) / 2;
+    x.assign(m, 0.0);
+    w.assign(m, 0.0);
+    const long double pi = 3.14159265358979323846264338327950288L;
+    for (int i = 1; i <= m; ++i) {
+        long double z = cosl(pi * (i - 0.25L) / (n + 0.5L));
+        long double pp = 1;
+        for (int it = 0; it < 100; ++it) {
+            long double p1 = 1, p2 = 0;
+            for (int j = 1; j <= n; ++j) {
+                long double p3 = p2;
+                p2 = p1;
+                p1 = ((2 * j - 1) * z * p2 - (j - 1) * p3) / j;
+            }
+            pp = n * (z * p1 - p2) / (z * z - 1);
+            long double z1 = z;
+            z = z1 - p1 / pp;
+            if (fabsl(z - z1) < 1e-19L) break;
+        }
+        if ((n & 1) && i == m) z = 0;
+        {   // derivative at the converged root
+            long double p1 = 1, p2 = 0;
+            for (int j = 1; j <= n; ++j) {
+                long double p3 = p2;
+                p2 = p1;
+                p1 = ((2 * j - 1) * z * p2 - (j - 1) * p3) / j;
+            }
+            pp = (z == 0) ? (long double)n * (-p2) / (-1) : n * (z * p1 - p2) / (z * z - 1);
+        }
+        // ascending non-negative abscissae, like the GSL table the reference integrates with
+        x[m - i] = (double)z;
+        w[m - i] = (double)(2 / ((1 - z * z) * pp * pp));
+    }
+}
+
+}  // namespace
+
+struct pgt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    PgtLaunchCounter launches{ 0 };
+
+    // models
+    bool have_pot = false, have_cg = false;
+    PgtPot pot{};
+    PgtCG cg{};
+    int nq = 0;
+    double max_rcut = 0.0;
+    double cell_side_user = 0.0;
+
+    // frame
+    bool have_frame = false, cells_built = false, bonds_built = false;
+    long long N = 0;
+    int is_f32 = 0;
+    int dim = 2;
+    PgtBox box{};
+    double vol = 0.0;
+    const void *src_pos = nullptr, *src_diam = nullptr, *src_mass = nullptr, *src_vel = nullptr;
+    DevBuf raw_pos, raw_diam, raw_mass, raw_vel;
+    PgtCells cells{};
+    int n_live = 0;
+    long long n_hb = 0;
+    DevBuf cell_of, cell_count, cell_fill, sorted_orig, scan_scratch, eflags;
+    DevBuf sx, sy, sd, skxx, skxy, skyy;
+    DevBuf hb_cnt, hb_b, hb_f, hb_j;
+
+    // grid
+    int grid_mode = -1;
+    int nx = 0, ny = 0;
+    long long G = 0, g0 = 0, g1 = 0;
+    DevBuf gxs, gys, gpts;
+
+    // outputs
+    DevBuf out_virial, out_kinetic, out_density;
+    unsigned last_ik_mask = 0;
+    DevBuf thermo_partials, thermo_out;
+    double* h_small = nullptr;   // pinned scratch for small read-backs
+
+    // timing
+    cudaEvent_t ev0[PGT_STAGE_COUNT]{}, ev1[PGT_STAGE_COUNT]{};
+    bool ev_valid[PGT_STAGE_COUNT]{};
+
+    // tuning
+    int ik_lanes = 32;
+
+    // nccl
+    pgtNcclComm comm = nullptr;
+    int nranks = 1, rank = 0;
+    DevBuf comm_scratch;
+};
+
+namespace {
+
+int fail(pgt_ctx* c, int code, const char* fmt, ...)
+{
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    else g_create_error = buf;
+    return code;
+}
+
+#define CK(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) return fail(ctx, PGT_ERR_CUDA, "%s failed: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
+
+int ensure(pgt_ctx* ctx, DevBuf& b, size_t bytes)
+{
+    if (bytes <= b.cap) return PGT_OK;
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = bytes + bytes / 8 + 256;
+    CK(cudaMalloc(&b.p, want));
+    b.cap = want;
+    return PGT_OK;
+}
+#define ENSURE(buf, bytes)                          \
+    do {                                            \
+        int rc_ = ensure(ctx, buf, (bytes));        \
+        if (rc_ != PGT_OK) return rc_;              \
+    } while (0)
+
+void stage_begin(pgt_ctx* ctx, int s) { cudaEventRecord(ctx->ev0[s], ctx->stream); }
+void stage_end(pgt_ctx* ctx, int s)
+{
+    cudaEventRecord(ctx->ev1[s], ctx->stream);
+    ctx->ev_valid[s] = true;
+}
+
+int check_eflags(pgt_ctx* ctx, int flags)
+{
+    if (flags & PGT_EFLAG_WRAP_RUNAWAY)
+        return fail(ctx, PGT_ERR_DATA, "a particle lies more than %d box lengths outside the box", PGT_WRAP_MAX_ITERS);
+    if (flags & PGT_EFLAG_Z_NONZERO)
+        return fail(ctx, PGT_ERR_UNSUPPORTED, "2-D frame with non-zero z coordinates is not supported on device");
+    return PGT_OK;
+}
+
+PgtFrameView frame_view(const pgt_ctx* c)
+{
+    PgtFrameView v{};
+    v.n = c->n_live;
+    v.sx = c->sx.as<double>();
+    v.sy = c->sy.as<double>();
+    v.sd = c->sd.as<double>();
+    const bool kin = c->src_vel != nullptr;
+    v.skxx = kin ? c->skxx.as<double>() : nullptr;
+    v.skxy = kin ? c->skxy.as<double>() : nullptr;
+    v.skyy = kin ? c->skyy.as<double>() : nullptr;
+    v.sorig = c->sorted_orig.as<int>();
+    v.cell_start = c->cell_count.as<int>();
+    v.hb_off = c->hb_cnt.as<int>();
+    v.hb_b = c->hb_b.as<double2>();
+    v.hb_f = c->hb_f.as<double>();
+    v.hb_j = c->hb_j.as<int>();
+    return v;
+}
+
+int set_box(pgt_ctx* ctx, const double box[3], int dim)
+{
+    if (dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "only dim == 2 is implemented on device (got %d)", dim);
+    ctx->dim = dim;
+    double L[3] = { box[0], box[1], 1.0 };   // utils.py:15-16 forces Lz = 1 in 2-D
+    for (int d = 0; d < 3; ++d) {
+        if (!(L[d] > 0) || !std::isfinite(L[d])) return fail(ctx, PGT_ERR_ARG, "box length %d is not positive", d);
+        // SimBox::setBounds with origin 0 (SimBox.cc:48-52)
+        ctx->box.hi[d] = 0.5 * L[d] - 0.0;
+        ctx->box.lo[d] = (-1.0) * ctx->box.hi[d] - 2.0 * 0.0;
+        ctx->box.L[d] = ctx->box.hi[d] - ctx->box.lo[d];   // Aboria: bmax - bmin
+    }
+    ctx->box.dim = dim;
+    ctx->vol = L[0] * L[1];
+    return PGT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pgt_device_count(int* n)
+{
+    cudaError_t e = cudaGetDeviceCount(n);
+    if (e != cudaSuccess) { *n = 0; g_create_error = cudaGetErrorString(e); return PGT_ERR_CUDA; }
+    return PGT_OK;
+}
+
+int pgt_ctx_create(int device, pgt_ctx** out)
+{
+    if (!out) return PGT_ERR_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    cudaError_t e = cudaGetDeviceCount(&ndev);
+    if (e != cudaSuccess || ndev == 0)
+        return fail(nullptr, PGT_ERR_CUDA, "no CUDA device available (%s); libpgt_cuda has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    if (device < 0 || device >= ndev) return fail(nullptr, PGT_ERR_ARG, "device %d out of range [0,%d)", device, ndev);
+    pgt_ctx* ctx = new pgt_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+        fail(nullptr, PGT_ERR_CUDA, "cannot initialise device %d: %s", device, cudaGetErrorString(e));
+        delete ctx;
+        return PGT_ERR_CUDA;
+    }
+    for (int s = 0; s < PGT_STAGE_COUNT; ++s) {
+        cudaEventCreate(&ctx->ev0[s]);
+        cudaEventCreate(&ctx->ev1[s]);
+    }
+    cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocDefault);
+    if (const char* env = getenv("PGT_IK_LANES")) {
+        int l = atoi(env);
+        if (l == 8 || l == 16 || l == 32) ctx->ik_lanes = l;
+    }
+    *out = ctx;
+    return PGT_OK;
+}
+
+int pgt_ctx_destroy(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_OK;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
+    DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
+                       &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
+                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_f, &ctx->hb_j, &ctx->gxs, &ctx->gys, &ctx->gpts,
+                       &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->thermo_partials, &ctx->thermo_out,
+                       &ctx->comm_scratch };
+    for (DevBuf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    for (int s = 0; s < PGT_STAGE_COUNT; ++s) {
+        cudaEventDestroy(ctx->ev0[s]);
+        cudaEventDestroy(ctx->ev1[s]);
+    }
+    if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    cudaStreamDestroy(ctx->stream);
+    delete ctx;
+    return PGT_OK;
+}
+
+const char* pgt_last_error(const pgt_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_error.c_str(); }
+
+int pgt_synchronize(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PGT_OK;
+}
+
+void* pgt_stream(pgt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int64_t pgt_kernel_launches(const pgt_ctx* ctx) { return ctx ? ctx->launches.n : 0; }
+
+// ---------------------------------------------------------------------------------- models
+static int expected_nparams(int model)
+{
+    switch (model) {
+    case PGT_POT_LJ: case PGT_POT_FORCESHIFTED_LJ: return 2;
+    case PGT_POT_POLY10: case PGT_POT_POLYYUKAWA: return 6;
+    case PGT_POT_POLY12: case PGT_POT_POLY18: case PGT_POT_POLY106: case PGT_POT_POLYLJ: return 5;
+    }
+    return -1;
+}
+
+static int fill_pot(PgtPot& P, int model_id, double scaled_rcut, const double* params, int nparams)
+{
+    const int want = expected_nparams(model_id);
+    if (want < 0 || nparams < want || nparams > 8 || !params) return -1;
+    P.model = model_id;
+    P.nparams = nparams;
+    P.scaled_rcut = scaled_rcut;
+    P.rcutsq = scaled_rcut * scaled_rcut;
+    for (int k = 0; k < 8; ++k) P.p[k] = k < nparams ? params[k] : 0.0;
+    return 0;
+}
+
+int pgt_potential_set(pgt_ctx* ctx, int model_id, double scaled_rcut, const double* params, int nparams)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (fill_pot(ctx->pot, model_id, scaled_rcut, params, nparams) != 0)
+        return fail(ctx, PGT_ERR_ARG, "bad pair model %d / parameter count %d", model_id, nparams);
+    ctx->have_pot = true;
+    ctx->bonds_built = false;
+    return PGT_OK;
+}
+
+int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int order)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (kernel_id < PGT_CG_OCTIC || kernel_id > PGT_CG_MOLLIFIER) return fail(ctx, PGT_ERR_ARG, "unknown CG kernel %d", kernel_id);
+    if (quad_mode != PGT_QUAD_FIXEDPOINT)
+        return fail(ctx, PGT_ERR_UNSUPPORTED, "adaptive (GSL QAG) bond quadrature is not implemented on device");
+    if (order < 1 || order > PGT_MAX_GL) return fail(ctx, PGT_ERR_UNSUPPORTED, "quadrature order %d outside [1,%d]", order, PGT_MAX_GL);
+    if (!(cg_rcut > 0)) return fail(ctx, PGT_ERR_ARG, "cg_rcut must be positive");
+    CK(cudaSetDevice(ctx->device));
+    ctx->cg.kernel = kernel_id;
+    ctx->cg.order = order;
+    ctx->cg.rcut = cg_rcut;
+    ctx->cg.rcutsq = cg_rcut * cg_rcut;
+    ctx->cg.norm = pgt_cg_norm(kernel_id, cg_rcut);
+    // nodes in GSL's visiting order: centre (odd n), then +-pairs; weights carry (b-a)/2 = 0.5
+    std::vector<double> x, w, s, ww;
+    gauss_legendre_half(order, x, w);
+    const int m = (order + 1) / 2;
+    int i0 = 0;
+    if (order & 1) { s.push_back(0.5); ww.push_back(0.5 * w[0]); i0 = 1; }
+    for (int i = i0; i < m; ++i) {
+        const double Ax = 0.5 * x[i];
+        s.push_back(0.5 + Ax); ww.push_back(0.5 * w[i]);
+        s.push_back(0.5 - Ax); ww.push_back(0.5 * w[i]);
+    }
+    ctx->nq = (int)s.size();
+    CK(pgt_upload_gl_tables(s.data(), ww.data(), ctx->nq, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));   // s/ww are stack-owned
+    ctx->have_cg = true;
+    return PGT_OK;
+}
+
+int pgt_set_max_rcut(pgt_ctx* ctx, double max_rcut)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!(max_rcut > 0) || !std::isfinite(max_rcut)) return fail(ctx, PGT_ERR_ARG, "max_rcut must be positive");
+    if (max_rcut != ctx->max_rcut) { ctx->cells_built = false; ctx->bonds_built = false; }
+    ctx->max_rcut = max_rcut;
+    return PGT_OK;
+}
+
+int pgt_set_cell_size(pgt_ctx* ctx, double cell_side)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    ctx->cell_side_user = cell_side > 0 ? cell_side : 0.0;
+    ctx->cells_built = false;
+    ctx->bonds_built = false;
+    return PGT_OK;
+}
+
+// ---------------------------------------------------------------------------------- frame
+static int set_frame_common(pgt_ctx* ctx, int is_f32, int64_t N, const double box[3], int dim)
+{
+    if (N < 0 || N > 2000000000LL) return fail(ctx, PGT_ERR_ARG, "particle count %lld out of range", (long long)N);
+    int rc = set_box(ctx, box, dim);
+    if (rc != PGT_OK) return rc;
+    ctx->N = N;
+    ctx->is_f32 = is_f32 ? 1 : 0;
+    ctx->have_frame = true;
+    ctx->cells_built = false;
+    ctx->bonds_built = false;
+    return PGT_OK;
+}
+
+int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel, int is_f32,
+                     int64_t N, const double box[3], int dim)
+{
+    if (!ctx || !pos || !diam || !box) return fail(ctx, PGT_ERR_ARG, "pgt_frame_upload: null argument");
+    CK(cudaSetDevice(ctx->device));
+    int rc = set_frame_common(ctx, is_f32, N, box, dim);
+    if (rc != PGT_OK) return rc;
+    const size_t es = is_f32 ? 4 : 8;
+    stage_begin(ctx, PGT_STAGE_UPLOAD);
+    ENSURE(ctx->raw_pos, (size_t)N * 3 * es);
+    ENSURE(ctx->raw_diam, (size_t)N * es);
+    CK(cudaMemcpyAsync(ctx->raw_pos.p, pos, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->raw_diam.p, diam, (size_t)N * es, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->src_pos = ctx->raw_pos.p;
+    ctx->src_diam = ctx->raw_diam.p;
+    ctx->src_mass = nullptr;
+    ctx->src_vel = nullptr;
+    if (mass) {
+        ENSURE(ctx->raw_mass, (size_t)N * es);
+        CK(cudaMemcpyAsync(ctx->raw_mass.p, mass, (size_t)N * es, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->src_mass = ctx->raw_mass.p;
+    }
+    if (vel) {
+        ENSURE(ctx->raw_vel, (size_t)N * 3 * es);
+        CK(cudaMemcpyAsync(ctx->raw_vel.p, vel, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
+        ctx->src_vel = ctx->raw_vel.p;
+    }
+    stage_end(ctx, PGT_STAGE_UPLOAD);
+    return PGT_OK;
+}
+
+int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, const void* d_mass, const void* d_vel, int is_f32,
+                         int64_t N, const double box[3], int dim)
+{
+    if (!ctx || !d_pos || !d_diam || !box) return fail(ctx, PGT_ERR_ARG, "pgt_frame_set_device: null argument");
+    int rc = set_frame_common(ctx, is_f32, N, box, dim);
+    if (rc != PGT_OK) return rc;
+    ctx->src_pos = d_pos;
+    ctx->src_diam = d_diam;
+    ctx->src_mass = d_mass;
+    ctx->src_vel = d_vel;
+    return PGT_OK;
+}
+
+int pgt_build_cells(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!ctx->have_frame) return fail(ctx, PGT_ERR_STATE, "pgt_build_cells: no frame");
+    if (!(ctx->max_rcut > 0)) return fail(ctx, PGT_ERR_STATE, "pgt_build_cells: max_rcut not set");
+    CK(cudaSetDevice(ctx->device));
+    const long long N = ctx->N;
+
+    // cell geometry: side ~ max_rcut/2, never more than ~8 cells per particle
+    double side = ctx->cell_side_user > 0 ? ctx->cell_side_user : 0.5 * ctx->max_rcut;
+    const double Lx = ctx->box.L[0], Ly = ctx->box.L[1];
+    const double min_side = std::sqrt(Lx * Ly / (8.0 * (double)std::max<long long>(N, 1) + 64.0));
+    side = std::max(side, min_side);
+    PgtCells& c = ctx->cells;
+    c.ncx = std::max(1, (int)std::floor(Lx / side));
+    c.ncy = std::max(1, (int)std::floor(Ly / side));
+    if ((long long)c.ncx * c.ncy > 1500000000LL) return fail(ctx, PGT_ERR_DATA, "cell grid %d x %d too large", c.ncx, c.ncy);
+    const double cwx = Lx / c.ncx, cwy = Ly / c.ncy;
+    c.inv_cwx = 1.0 / cwx;
+    c.inv_cwy = 1.0 / cwy;
+    c.reach = (int)std::ceil(ctx->max_rcut / std::min(cwx, cwy) + 1e-9);
+    if (c.ncx < 2 * c.reach + 1 || c.ncy < 2 * c.reach + 1)
+        return fail(ctx, PGT_ERR_DATA, "box %g x %g too small for max_rcut %g (needs at least %d cells per axis)", Lx, Ly,
+                    ctx->max_rcut, 2 * c.reach + 1);
+    const int ncells = c.ncx * c.ncy;
+
+    stage_begin(ctx, PGT_STAGE_CELLS);
+    ENSURE(ctx->cell_of, sizeof(int) * (size_t)std::max<long long>(N, 1));
+    ENSURE(ctx->cell_count, sizeof(int) * ((size_t)ncells + 1));
+    ENSURE(ctx->cell_fill, sizeof(int) * (size_t)ncells);
+    ENSURE(ctx->sorted_orig, sizeof(int) * (size_t)std::max<long long>(N, 1));
+    ENSURE(ctx->scan_scratch, sizeof(int) * (size_t)pgt_scan_scratch_ints(std::max<long long>(ncells, N) + 1));
+    ENSURE(ctx->eflags, sizeof(int) * 4);
+    CK(cudaMemsetAsync(ctx->cell_count.p, 0, sizeof(int) * ((size_t)ncells + 1), ctx->stream));
+    CK(cudaMemsetAsync(ctx->cell_fill.p, 0, sizeof(int) * (size_t)ncells, ctx->stream));
+    CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream));
+
+    pgt_launch_wrap_count(ctx->src_pos, ctx->is_f32, N, ctx->box, c, ctx->cell_of.as<int>(), ctx->cell_count.as<int>(),
+                          ctx->eflags.as<int>(), ctx->stream, &ctx->launches);
+    pgt_launch_scan_exclusive(ctx->cell_count.as<int>(), ctx->cell_count.as<int>(), (long long)ncells + 1,
+                              ctx->scan_scratch.as<int>(), ctx->stream, &ctx->launches);
+    pgt_launch_scatter_ids(ctx->cell_of.as<int>(), N, ctx->cell_count.as<int>(), ctx->cell_fill.as<int>(),
+                           ctx->sorted_orig.as<int>(), ctx->stream, &ctx->launches);
+    pgt_launch_cell_sort(ctx->sorted_orig.as<int>(), ctx->cell_count.as<int>(), ncells, ctx->stream, &ctx->launches);
+
+    // live count and error flags (two ints) back to the host
+    int* h = reinterpret_cast<int*>(ctx->h_small);
+    CK(cudaMemcpyAsync(h, ctx->cell_count.as<int>() + ncells, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(h + 1, ctx->eflags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->n_live = h[0];
+    int rc = check_eflags(ctx, h[1]);
+    if (rc != PGT_OK) return rc;
+
+    const size_t nl = (size_t)std::max(ctx->n_live, 1);
+    ENSURE(ctx->sx, sizeof(double) * nl);
+    ENSURE(ctx->sy, sizeof(double) * nl);
+    ENSURE(ctx->sd, sizeof(double) * nl);
+    const bool kin = ctx->src_vel != nullptr;
+    if (kin) {
+        ENSURE(ctx->skxx, sizeof(double) * nl);
+        ENSURE(ctx->skxy, sizeof(double) * nl);
+        ENSURE(ctx->skyy, sizeof(double) * nl);
+    }
+    pgt_launch_gather_sorted(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box,
+                             ctx->sorted_orig.as<int>(), ctx->n_live, ctx->sx.as<double>(), ctx->sy.as<double>(),
+                             ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr, kin ? ctx->skxy.as<double>() : nullptr,
+                             kin ? ctx->skyy.as<double>() : nullptr, ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    stage_end(ctx, PGT_STAGE_CELLS);
+    ctx->cells_built = true;
+    ctx->bonds_built = false;
+    return PGT_OK;
+}
+
+int pgt_build_bonds(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: cells not built");
+    if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: no pair potential");
+    CK(cudaSetDevice(ctx->device));
+    const int n = ctx->n_live;
+    stage_begin(ctx, PGT_STAGE_BONDS);
+    ENSURE(ctx->hb_cnt, sizeof(int) * ((size_t)n + 1));
+    CK(cudaMemsetAsync(ctx->hb_cnt.as<int>() + n, 0, sizeof(int), ctx->stream));
+    PgtFrameView fr = frame_view(ctx);
+    pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), nullptr, nullptr, nullptr,
+                     ctx->stream, &ctx->launches);
+    pgt_launch_scan_exclusive(ctx->hb_cnt.as<int>(), ctx->hb_cnt.as<int>(), (long long)n + 1, ctx->scan_scratch.as<int>(),
+                              ctx->stream, &ctx->launches);
+    int* h = reinterpret_cast<int*>(ctx->h_small);
+    CK(cudaMemcpyAsync(h, ctx->hb_cnt.as<int>() + n, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (h[0] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
+    ctx->n_hb = h[0];
+    const size_t nb = (size_t)std::max<long long>(ctx->n_hb, 1);
+    ENSURE(ctx->hb_b, sizeof(double2) * nb);
+    ENSURE(ctx->hb_f, sizeof(double) * nb);
+    ENSURE(ctx->hb_j, sizeof(int) * nb);
+    fr = frame_view(ctx);
+    pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), ctx->hb_b.as<double2>(),
+                     ctx->hb_f.as<double>(), ctx->hb_j.as<int>(), ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    stage_end(ctx, PGT_STAGE_BONDS);
+    ctx->bonds_built = true;
+    return PGT_OK;
+}
+
+int pgt_frame_counts(pgt_ctx* ctx, int64_t* n_live, int64_t* n_halfbonds, int64_t* n_cells)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (n_live) *n_live = ctx->cells_built ? ctx->n_live : -1;
+    if (n_halfbonds) *n_halfbonds = ctx->bonds_built ? ctx->n_hb : -1;
+    if (n_cells) *n_cells = ctx->cells_built ? (int64_t)ctx->cells.ncx * ctx->cells.ncy : -1;
+    return PGT_OK;
+}
+
+// ---------------------------------------------------------------------------------- grid
+int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double* ys, int ny)
+{
+    if (!ctx || !xs || !ys || nx < 0 || ny < 0) return fail(ctx, PGT_ERR_ARG, "pgt_grid_set_cartesian: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    ENSURE(ctx->gxs, sizeof(double) * (size_t)std::max(nx, 1));
+    ENSURE(ctx->gys, sizeof(double) * (size_t)std::max(ny, 1));
+    CK(cudaMemcpyAsync(ctx->gxs.p, xs, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->gys.p, ys, sizeof(double) * ny, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->grid_mode = 0;
+    ctx->nx = nx;
+    ctx->ny = ny;
+    ctx->G = (long long)nx * ny;
+    ctx->g0 = 0;
+    ctx->g1 = ctx->G;
+    return PGT_OK;
+}
+
+int pgt_grid_set_points(pgt_ctx* ctx, const double* xyz, int64_t G)
+{
+    if (!ctx || (!xyz && G > 0) || G < 0) return fail(ctx, PGT_ERR_ARG, "pgt_grid_set_points: bad argument");
+    CK(cudaSetDevice(ctx->device));
+    ENSURE(ctx->gpts, sizeof(double) * 3 * (size_t)std::max<long long>(G, 1));
+    if (G > 0) CK(cudaMemcpyAsync(ctx->gpts.p, xyz, sizeof(double) * 3 * (size_t)G, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->grid_mode = 1;
+    ctx->G = G;
+    ctx->g0 = 0;
+    ctx->g1 = G;
+    return PGT_OK;
+}
+
+int pgt_grid_set_shard(pgt_ctx* ctx, int64_t g0, int64_t g1)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_grid_set_shard: no grid");
+    if (g0 < 0 || g1 < g0 || g1 > ctx->G) return fail(ctx, PGT_ERR_ARG, "shard [%lld,%lld) outside [0,%lld)", (long long)g0, (long long)g1, ctx->G);
+    ctx->g0 = g0;
+    ctx->g1 = g1;
+    return PGT_OK;
+}
+
+// ---------------------------------------------------------------------------------- compute
+int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: cells not built");
+    if ((obs_mask & PGT_OBS_VIRIAL) && !ctx->bonds_built) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: bonds not built");
+    if (!ctx->have_cg) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no coarse-graining function");
+    if (ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no grid");
+    if (!(obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_KINETIC | PGT_OBS_DENSITY))) return fail(ctx, PGT_ERR_ARG, "pgt_ik_compute: empty observable mask");
+    if (ctx->cg.rcut >= ctx->box.L[0] || ctx->cg.rcut >= ctx->box.L[1])
+        return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
+    CK(cudaSetDevice(ctx->device));
+    const long long gl = ctx->g1 - ctx->g0;
+    const size_t n = (size_t)std::max<long long>(gl, 1);
+    if (obs_mask & PGT_OBS_VIRIAL) ENSURE(ctx->out_virial, sizeof(double) * 4 * n);
+    if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 4 * n);
+    if (obs_mask & PGT_OBS_DENSITY) ENSURE(ctx->out_density, sizeof(double) * n);
+
+    PgtIKArgs a{};
+    a.fr = frame_view(ctx);
+    a.grid.mode = ctx->grid_mode;
+    a.grid.nx = ctx->nx;
+    a.grid.ny = ctx->ny;
+    a.grid.xs = ctx->gxs.as<double>();
+    a.grid.ys = ctx->gys.as<double>();
+    a.grid.pts = ctx->gpts.as<double>();
+    a.grid.g0 = ctx->g0;
+    a.grid.g1 = ctx->g1;
+    a.box = ctx->box;
+    a.cells = ctx->cells;
+    a.cg = ctx->cg;
+    a.inv_rcutsq = 1.0 / ctx->cg.rcutsq;
+    a.nq = ctx->nq;
+    a.out_virial = ctx->out_virial.as<double>();
+    a.out_kinetic = ctx->out_kinetic.as<double>();
+    a.out_density = ctx->out_density.as<double>();
+    a.obs_mask = obs_mask;
+    stage_begin(ctx, PGT_STAGE_IK);
+    if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_lanes, ctx->stream, &ctx->launches));
+    stage_end(ctx, PGT_STAGE_IK);
+    ctx->last_ik_mask = obs_mask;
+    return PGT_OK;
+}
+
+static int field_info(pgt_ctx* ctx, int field_id, DevBuf** buf, int* ncomp)
+{
+    switch (field_id) {
+    case PGT_FIELD_VIRIAL: *buf = &ctx->out_virial; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_VIRIAL) ? 0 : -1;
+    case PGT_FIELD_KINETIC: *buf = &ctx->out_kinetic; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_KINETIC) ? 0 : -1;
+    case PGT_FIELD_DENSITY: *buf = &ctx->out_density; *ncomp = 1; return (ctx->last_ik_mask & PGT_OBS_DENSITY) ? 0 : -1;
+    }
+    return -2;
+}
+
+int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out)
+{
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_ik_download: null argument");
+    DevBuf* b;
+    int nc;
+    int rc = field_info(ctx, field_id, &b, &nc);
+    if (rc == -2) return fail(ctx, PGT_ERR_ARG, "unknown field %d", field_id);
+    if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
+    CK(cudaSetDevice(ctx->device));
+    const long long gl = ctx->g1 - ctx->g0;
+    stage_begin(ctx, PGT_STAGE_DOWNLOAD);
+    if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->stream));
+    stage_end(ctx, PGT_STAGE_DOWNLOAD);
+    CK(cudaStreamSynchronize(ctx->stream));
+    return PGT_OK;
+}
+
+int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubles)
+{
+    if (!ctx || !d_ptr) return fail(ctx, PGT_ERR_ARG, "pgt_ik_device_ptr: null argument");
+    DevBuf* b;
+    int nc;
+    int rc = field_info(ctx, field_id, &b, &nc);
+    if (rc == -2) return fail(ctx, PGT_ERR_ARG, "unknown field %d", field_id);
+    if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
+    *d_ptr = b->p;
+    if (n_doubles) *n_doubles = (int64_t)nc * (ctx->g1 - ctx->g0);
+    return PGT_OK;
+}
+
+int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
+{
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: cells not built");
+    if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: no pair potential");
+    CK(cudaSetDevice(ctx->device));
+    const int blocks = pgt_thermo_blocks(ctx->n_live);
+    ENSURE(ctx->thermo_partials, sizeof(double) * 25 * (size_t)blocks);
+    ENSURE(ctx->thermo_out, sizeof(double) * 32);
+    stage_begin(ctx, PGT_STAGE_THERMO);
+    pgt_launch_thermo(ctx->pot, frame_view(ctx), ctx->box, ctx->cells, ctx->max_rcut, obs_mask, 1 / ctx->vol,
+                      ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    stage_end(ctx, PGT_STAGE_THERMO);
+    CK(cudaMemcpyAsync(ctx->h_small, ctx->thermo_out.p, sizeof(double) * 25, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const double* h = ctx->h_small;
+    // device order: virial 4 | kinetic 4 | energy | born 16  ->  API order (same, documented in the header)
+    for (int k = 0; k < 25; ++k) out[k] = h[k];
+    return PGT_OK;
+}
+
+// ---------------------------------------------------------------------------------- exports
+static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32_t* oi, int32_t* oj, double* rij_xy, double* fdivr)
+{
+    if (!ctx || !n) return fail(ctx, PGT_ERR_ARG, "export: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "export: cells not built");
+    CK(cudaSetDevice(ctx->device));
+    const int np = ctx->n_live;
+    std::vector<int> off((size_t)np + 1), js, orig((size_t)std::max(np, 1));
+    std::vector<double2> b;
+    std::vector<double> f;
+    long long total = 0;
+    if (bonds) {
+        if (!ctx->bonds_built) return fail(ctx, PGT_ERR_STATE, "export: bonds not built");
+        total = ctx->n_hb;
+        CK(cudaMemcpy(off.data(), ctx->hb_cnt.p, sizeof(int) * ((size_t)np + 1), cudaMemcpyDeviceToHost));
+        js.resize((size_t)total);
+        b.resize((size_t)total);
+        f.resize((size_t)total);
+        if (total > 0 && cap >= total) {
+            CK(cudaMemcpy(js.data(), ctx->hb_j.p, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(b.data(), ctx->hb_b.p, sizeof(double2) * (size_t)total, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(f.data(), ctx->hb_f.p, sizeof(double) * (size_t)total, cudaMemcpyDeviceToHost));
+        }
+    } else {
+        // neighbours within max_rcut: a private count/scan/fill pass (export only)
+        DevBuf cnt, jbuf;
+        ENSURE(cnt, sizeof(int) * ((size_t)np + 1));
+        CK(cudaMemsetAsync(cnt.as<int>() + np, 0, sizeof(int), ctx->stream));
+        PgtFrameView fr = frame_view(ctx);
+        pgt_launch_bonds(2, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), nullptr, nullptr, nullptr, ctx->stream,
+                         &ctx->launches);
+        pgt_launch_scan_exclusive(cnt.as<int>(), cnt.as<int>(), (long long)np + 1, ctx->scan_scratch.as<int>(), ctx->stream, &ctx->launches);
+        CK(cudaStreamSynchronize(ctx->stream));
+        CK(cudaMemcpy(off.data(), cnt.p, sizeof(int) * ((size_t)np + 1), cudaMemcpyDeviceToHost));
+        total = off[np];
+        if (total > 0 && cap >= total) {
+            ENSURE(jbuf, sizeof(int) * (size_t)total);
+            pgt_launch_bonds(3, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), nullptr, nullptr, jbuf.as<int>(),
+                             ctx->stream, &ctx->launches);
+            CK(cudaStreamSynchronize(ctx->stream));
+            js.resize((size_t)total);
+            CK(cudaMemcpy(js.data(), jbuf.p, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost));
+        }
+        if (cnt.p) cudaFree(cnt.p);
+        if (jbuf.p) cudaFree(jbuf.p);
+    }
+    *n = total;
+    if (cap < total || total == 0) return PGT_OK;
+    if (!oi || !oj) return fail(ctx, PGT_ERR_ARG, "export: null output");
+    CK(cudaMemcpy(orig.data(), ctx->sorted_orig.p, sizeof(int) * (size_t)np, cudaMemcpyDeviceToHost));
+    for (int p = 0; p < np; ++p)
+        for (int e = off[p]; e < off[p + 1]; ++e) {
+            oi[e] = orig[p];
+            oj[e] = orig[js[e]];
+            if (bonds && rij_xy) { rij_xy[2 * e] = -b[e].x; rij_xy[2 * e + 1] = -b[e].y; }   // rij = -dx (IrvingKirkwood.h:101)
+            if (bonds && fdivr) fdivr[e] = f[e];
+        }
+    return PGT_OK;
+}
+
+int pgt_export_bonds(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j, double* rij_xy, double* fdivr)
+{
+    return export_pairs(ctx, true, cap, n, i, j, rij_xy, fdivr);
+}
+
+int pgt_export_neighbors(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j)
+{
+    if (ctx && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "export: no pair potential");
+    return export_pairs(ctx, false, cap, n, i, j, nullptr, nullptr);
+}
+
+int pgt_export_wrapped(pgt_ctx* ctx, double* xy, uint8_t* alive)
+{
+    if (!ctx || !xy) return fail(ctx, PGT_ERR_ARG, "pgt_export_wrapped: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_export_wrapped: cells not built");
+    CK(cudaSetDevice(ctx->device));
+    const int np = ctx->n_live;
+    std::vector<int> orig((size_t)std::max(np, 1));
+    std::vector<double> x((size_t)std::max(np, 1)), y((size_t)std::max(np, 1));
+    CK(cudaStreamSynchronize(ctx->stream));
+    CK(cudaMemcpy(orig.data(), ctx->sorted_orig.p, sizeof(int) * (size_t)np, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(x.data(), ctx->sx.p, sizeof(double) * (size_t)np, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(y.data(), ctx->sy.p, sizeof(double) * (size_t)np, cudaMemcpyDeviceToHost));
+    for (long long i = 0; i < ctx->N; ++i) {
+        xy[2 * i] = xy[2 * i + 1] = NAN;
+        if (alive) alive[i] = 0;
+    }
+    for (int p = 0; p < np; ++p) {
+        xy[2 * (size_t)orig[p]] = x[p];
+        xy[2 * (size_t)orig[p] + 1] = y[p];
+        if (alive) alive[orig[p]] = 1;
+    }
+    return PGT_OK;
+}
+
+int pgt_stage_time_ms(pgt_ctx* ctx, int stage, float* ms)
+{
+    if (!ctx || !ms || stage < 0 || stage >= PGT_STAGE_COUNT) return fail(ctx, PGT_ERR_ARG, "pgt_stage_time_ms: bad argument");
+    if (!ctx->ev_valid[stage]) return fail(ctx, PGT_ERR_STATE, "stage %d has not run", stage);
+    CK(cudaEventSynchronize(ctx->ev1[stage]));
+    CK(cudaEventElapsedTime(ms, ctx->ev0[stage], ctx->ev1[stage]));
+    return PGT_OK;
+}
+
+// scalar host getters ---------------------------------------------------------------------
+double pgt_pair_eval(int model_id, double scaled_rcut, const double* params, int nparams, const double rij[3], double di,
+                     double dj, int what)
+{
+    PgtPot P{};
+    if (fill_pot(P, model_id, scaled_rcut, params, nparams) != 0) return NAN;
+    const double rsq = rij[0] * rij[0] + rij[1] * rij[1] + rij[2] * rij[2];
+    double r = NAN;
+    PGT_DISPATCH_MODEL(model_id, (r = pgt_pair_eval_t<M>(P, rsq, di, dj, what)));
+    return r;
+}
+
+double pgt_cg_delta(int kernel_id, double cg_rcut, double dr_sq)
+{
+    PgtCG cg{};
+    cg.kernel = kernel_id;
+    cg.rcut = cg_rcut;
+    cg.rcutsq = cg_rcut * cg_rcut;
+    cg.norm = pgt_cg_norm(kernel_id, cg_rcut);
+    return pgt_cg_delta_exact(cg, dr_sq);
+}
+
+double pgt_cg_bond(int kernel_id, double cg_rcut, int order, const double x[3], const double ri[3], const double rij[3])
+{
+    if (order < 1 || order > PGT_MAX_GL) return NAN;
+    std::vector<double> gx, gw;
+    gauss_legendre_half(order, gx, gw);
+    const int m = (order + 1) / 2;
+    auto f = [&](double s) {
+        double d2 = 0;
+        for (int k = 0; k < 3; ++k) {
+            const double d = x[k] - (ri[k] + s * rij[k]);
+            d2 += d * d;
+        }
+        return pgt_cg_delta(kernel_id, cg_rcut, d2);
+    };
+    double sum = 0.0;
+    int i0 = 0;
+    if (order & 1) { sum = gw[0] * f(0.5); i0 = 1; }
+    for (int i = i0; i < m; ++i) {
+        const double Ax = 0.5 * gx[i];
+        sum += gw[i] * (f(0.5 + Ax) + f(0.5 - Ax));
+    }
+    return 0.5 * sum;
+}
+
+int pgt_fp64_peak_probe(pgt_ctx* ctx, double* tflops)
+{
+    if (!ctx || !tflops) return PGT_ERR_ARG;
+    CK(cudaSetDevice(ctx->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, ctx->device));
+    const int blocks = prop.multiProcessorCount * 8, threads = 256, iters = 20000;
+    DevBuf out;
+    ENSURE(out, sizeof(double) * (size_t)blocks * threads);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    pgt_launch_fp64_probe(out.as<double>(), 1000, blocks, threads, ctx->stream, &ctx->launches);   // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 3; ++rep) {
+        cudaEventRecord(a, ctx->stream);
+        pgt_launch_fp64_probe(out.as<double>(), iters, blocks, threads, ctx->stream, &ctx->launches);
+        cudaEventRecord(b, ctx->stream);
+        CK(cudaEventSynchronize(b));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        best = std::min(best, ms);
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    cudaFree(out.p);
+    *tflops = 2.0 * 8.0 * (double)iters * blocks * threads / (best * 1e-3) / 1e12;
+    return PGT_OK;
+}
+
+// ---------------------------------------------------------------------------------- NCCL
+int pgt_comm_unique_id(void* id128)
+{
+    std::string err;
+    if (!id128) return PGT_ERR_ARG;
+    if (!load_nccl(err)) { g_create_error = err; return PGT_ERR_NCCL; }
+    pgtNcclUniqueId id;
+    int rc = g_nccl.GetUniqueId(&id);
+    if (rc != 0) { g_create_error = g_nccl.GetErrorString(rc); return PGT_ERR_NCCL; }
+    memcpy(id128, &id, 128);
+    return PGT_OK;
+}
+
+int pgt_comm_init(pgt_ctx* ctx, int nranks, int rank, const void* id128)
+{
+    if (!ctx || !id128 || nranks < 1 || rank < 0 || rank >= nranks) return fail(ctx, PGT_ERR_ARG, "pgt_comm_init: bad argument");
+    std::string err;
+    if (!load_nccl(err)) return fail(ctx, PGT_ERR_NCCL, "%s", err.c_str());
+    CK(cudaSetDevice(ctx->device));
+    pgtNcclUniqueId id;
+    memcpy(&id, id128, 128);
+    int rc = g_nccl.CommInitRank(&ctx->comm, nranks, id, rank);
+    if (rc != 0) return fail(ctx, PGT_ERR_NCCL, "ncclCommInitRank: %s", g_nccl.GetErrorString(rc));
+    ctx->nranks = nranks;
+    ctx->rank = rank;
+    return PGT_OK;
+}
+
+int pgt_comm_allgather_field(pgt_ctx* ctx, int field_id, const int64_t* counts, void* out_dev)
+{
+    if (!ctx || !counts || !out_dev) return fail(ctx, PGT_ERR_ARG, "pgt_comm_allgather_field: null argument");
+    if (!ctx->comm) return fail(ctx, PGT_ERR_STATE, "pgt_comm_allgather_field: communicator not initialised");
+    DevBuf* b;
+    int nc;
+    int rc = field_info(ctx, field_id, &b, &nc);
+    if (rc != 0) return fail(ctx, PGT_ERR_STATE, "field %d not available", field_id);
+    CK(cudaSetDevice(ctx->device));
+    // variable-size all-gather = one broadcast per rank inside a group (NVLink / NVSwitch transport)
+    const int ncclDouble = 8;
+    int nrc = g_nccl.GroupStart();
+    size_t off = 0;
+    for (int r = 0; r < ctx->nranks && nrc == 0; ++r) {
+        double* dst = reinterpret_cast<double*>(out_dev) + off;
+        const void* src = (r == ctx->rank) ? b->p : (const void*)dst;
+        if (counts[r] > 0) nrc = g_nccl.Broadcast(src, dst, (size_t)counts[r], ncclDouble, r, ctx->comm, ctx->stream);
+        off += (size_t)counts[r];
+    }
+    int nrc2 = g_nccl.GroupEnd();
+    if (nrc != 0 || nrc2 != 0) return fail(ctx, PGT_ERR_NCCL, "ncclBroadcast group: %s", g_nccl.GetErrorString(nrc ? nrc : nrc2));
+    return PGT_OK;
+}
+
+int pgt_comm_allreduce_sum(pgt_ctx* ctx, double* inout_host, int n)
+{
+    if (!ctx || !inout_host || n < 0 || n > 256) return fail(ctx, PGT_ERR_ARG, "pgt_comm_allreduce_sum: bad argument");
+    if (!ctx->comm) return fail(ctx, PGT_ERR_STATE, "pgt_comm_allreduce_sum: communicator not initialised");
+    CK(cudaSetDevice(ctx->device));
+    ENSURE(ctx->comm_scratch, sizeof(double) * 256);
+    memcpy(ctx->h_small, inout_host, sizeof(double) * n);
+    CK(cudaMemcpyAsync(ctx->comm_scratch.p, ctx->h_small, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+    const int ncclDouble = 8, ncclSum = 0;
+    int rc = g_nccl.AllReduce(ctx->comm_scratch.p, ctx->comm_scratch.p, (size_t)n, ncclDouble, ncclSum, ctx->comm, ctx->stream);
+    if (rc != 0) return fail(ctx, PGT_ERR_NCCL, "ncclAllReduce: %s", g_nccl.GetErrorString(rc));
+    CK(cudaMemcpyAsync(ctx->h_small, ctx->comm_scratch.p, sizeof(double) * n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    memcpy(inout_host, ctx->h_small, sizeof(double) * n);
+    return PGT_OK;
+}
+
+int pgt_comm_destroy(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
+    ctx->comm = nullptr;
+    ctx->nranks = 1;
+    ctx->rank = 0;
+    return PGT_OK;
+}
+
+}  // extern "C"

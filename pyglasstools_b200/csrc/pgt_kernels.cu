@@ -1,0 +1,829 @@
+// pgt_kernels.cu -- sm_100a kernels for the IK / thermo pair-sum path (see pgt_kernels.cuh).
+//
+// Compiled with -fmad=false: products and sums are rounded separately unless fma() is written
+// explicitly, so every discrete test below is the reference's ISO-C arithmetic.
+#include "pgt_kernels.cuh"
+#include <math_constants.h>
+
+#define FULL_MASK 0xffffffffu
+
+__constant__ double c_gl_s[PGT_MAX_GL];   // quadrature nodes on [0,1]:  0.5 +- 0.5 x_i
+__constant__ double c_gl_w[PGT_MAX_GL];   // weights times (b-a)/2 = 0.5
+
+cudaError_t pgt_upload_gl_tables(const double* s, const double* w, int n, cudaStream_t st)
+{
+    cudaError_t e = cudaMemcpyToSymbolAsync(c_gl_s, s, sizeof(double) * n, 0, cudaMemcpyHostToDevice, st);
+    if (e != cudaSuccess) return e;
+    return cudaMemcpyToSymbolAsync(c_gl_w, w, sizeof(double) * n, 0, cudaMemcpyHostToDevice, st);
+}
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+template <bool F32>
+__device__ __forceinline__ double ld_real(const void* p, long long i)
+{
+    if (F32) return (double)__ldg(reinterpret_cast<const float*>(p) + i);
+    return __ldg(reinterpret_cast<const double*>(p) + i);
+}
+
+// Aboria enforce_domain on a periodic axis (NeighbourSearchBase.h:218-224): repeated +-(high-low).
+__device__ __forceinline__ bool wrap_axis(double& r, double low, double high, int* eflags)
+{
+    if (!isfinite(r)) return false;
+    const double span = high - low;
+    int it = 0;
+    while (r < low) {
+        r += span;
+        if (++it > PGT_WRAP_MAX_ITERS) { if (eflags) atomicOr(eflags, PGT_EFLAG_WRAP_RUNAWAY); return false; }
+    }
+    while (r >= high) {
+        r -= span;
+        if (++it > PGT_WRAP_MAX_ITERS) { if (eflags) atomicOr(eflags, PGT_EFLAG_WRAP_RUNAWAY); return false; }
+    }
+    return true;
+}
+
+__device__ __forceinline__ int cell_coord(double v, double lo, double inv_cw, int nc)
+{
+    int c = __double2int_rd((v - lo) * inv_cw);
+    return min(nc - 1, max(0, c));
+}
+
+// Loads, promotes and wraps particle i.  Returns false when the reference would delete it.
+template <bool F32>
+__device__ __forceinline__ bool load_wrapped(const void* pos, long long i, const PgtBox& box, double& x, double& y, int* eflags)
+{
+    x = ld_real<F32>(pos, 3 * i);
+    y = ld_real<F32>(pos, 3 * i + 1);
+    double z = ld_real<F32>(pos, 3 * i + 2);
+    bool alive = wrap_axis(x, box.lo[0], box.hi[0], eflags);
+    alive = wrap_axis(y, box.lo[1], box.hi[1], eflags) && alive;
+    // third axis is non-periodic in 2-D: out of [lo,hi) or non-finite => deleted
+    if (!isfinite(z) || z < box.lo[2] || z >= box.hi[2]) alive = false;
+    else if (z != 0.0 && alive && eflags) atomicOr(eflags, PGT_EFLAG_Z_NONZERO);
+    return alive;
+}
+
+// ------------------------------------------------------------------------------------------
+// Stage 0/1a: promote + wrap + cell key + histogram
+template <bool F32>
+__global__ void __launch_bounds__(256) k_wrap_count(const void* __restrict__ pos, long long N, PgtBox box, PgtCells cells,
+                                                    int* __restrict__ cell_of, int* __restrict__ cell_count, int* eflags)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    double x, y;
+    int c = -1;
+    if (load_wrapped<F32>(pos, i, box, x, y, eflags)) {
+        const int cx = cell_coord(x, box.lo[0], cells.inv_cwx, cells.ncx);
+        const int cy = cell_coord(y, box.lo[1], cells.inv_cwy, cells.ncy);
+        c = cy * cells.ncx + cx;
+        atomicAdd(&cell_count[c], 1);
+    }
+    cell_of[i] = c;
+}
+
+void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
+                           int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (N <= 0) return;
+    const int blocks = (int)((N + 255) / 256);
+    if (is_f32) k_wrap_count<true><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags);
+    else k_wrap_count<false><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags);
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
+// Exclusive scan of int32 (three phases; in may alias out)
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 8
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_tile(const int* in, int* out, long long n, int* tile_sums)
+{
+    __shared__ int warp_sums[SCAN_THREADS / 32];
+    const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS];
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        sum += v[k];
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(FULL_MASK, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) warp_sums[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int ws = (lane < SCAN_THREADS / 32) ? warp_sums[lane] : 0;
+        int wi = ws;
+#pragma unroll
+        for (int d = 1; d < SCAN_THREADS / 32; d <<= 1) {
+            int t = __shfl_up_sync(FULL_MASK, wi, d);
+            if (lane >= d) wi += t;
+        }
+        if (lane < SCAN_THREADS / 32) warp_sums[lane] = wi - ws;
+        if (lane == SCAN_THREADS / 32 - 1) tile_sums[blockIdx.x] = wi;
+    }
+    __syncthreads();
+    int excl = inc - sum + warp_sums[w];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        if (base + k < n) out[base + k] = excl;
+        excl += v[k];
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_scan_sums(int* sums, int n)
+{
+    __shared__ int warp_sums[32];
+    __shared__ int carry_s;
+    if (threadIdx.x == 0) carry_s = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += 1024) {
+        const int idx = base + threadIdx.x;
+        const int v = idx < n ? sums[idx] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int t = __shfl_up_sync(FULL_MASK, inc, d);
+            if (lane >= d) inc += t;
+        }
+        if (lane == 31) warp_sums[w] = inc;
+        __syncthreads();
+        if (w == 0) {
+            int ws = warp_sums[lane], wi = ws;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int t = __shfl_up_sync(FULL_MASK, wi, d);
+                if (lane >= d) wi += t;
+            }
+            warp_sums[lane] = wi - ws;
+        }
+        __syncthreads();
+        const int carry = carry_s;
+        const int excl = inc - v + warp_sums[w] + carry;
+        if (idx < n) sums[idx] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry_s = excl + v;
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(int* out, long long n, const int* tile_sums)
+{
+    const int add = tile_sums[blockIdx.x];
+    const long long base = (long long)blockIdx.x * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k)
+        if (base + k < n) out[base + k] += add;
+}
+
+long long pgt_scan_scratch_ints(long long n) { return (n + SCAN_TILE - 1) / SCAN_TILE + 1; }
+
+void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* tile_sums, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (n <= 0) return;
+    const int tiles = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+    k_scan_tile<<<tiles, SCAN_THREADS, 0, st>>>(in, out, n, tile_sums);
+    lc->n++;
+    if (tiles > 1) {
+        k_scan_sums<<<1, 1024, 0, st>>>(tile_sums, tiles);
+        k_scan_add<<<tiles, SCAN_THREADS, 0, st>>>(out, n, tile_sums);
+        lc->n += 2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Stage 1b: counting-sort scatter of particle ids, per-cell ordering, gather into sorted SoA
+__global__ void __launch_bounds__(256) k_scatter_ids(const int* __restrict__ cell_of, long long N, const int* __restrict__ cell_start,
+                                                     int* __restrict__ cell_fill, int* __restrict__ sorted_orig)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const int c = cell_of[i];
+    if (c < 0) return;
+    const int slot = cell_start[c] + atomicAdd(&cell_fill[c], 1);
+    sorted_orig[slot] = (int)i;
+}
+
+void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_start, int* cell_fill, int* sorted_orig,
+                            cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (N <= 0) return;
+    k_scatter_ids<<<(int)((N + 255) / 256), 256, 0, st>>>(cell_of, N, cell_start, cell_fill, sorted_orig);
+    lc->n++;
+}
+
+// The atomic scatter leaves each cell's members in arrival order; sorting them by original index
+// makes the layout (and therefore every summation order downstream) reproducible run to run.
+__global__ void __launch_bounds__(256) k_cell_sort(int* __restrict__ sorted_orig, const int* __restrict__ cell_start, int ncells)
+{
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    const int b = cell_start[c], e = cell_start[c + 1];
+    for (int i = b + 1; i < e; ++i) {
+        const int key = sorted_orig[i];
+        int j = i - 1;
+        while (j >= b && sorted_orig[j] > key) {
+            sorted_orig[j + 1] = sorted_orig[j];
+            --j;
+        }
+        sorted_orig[j + 1] = key;
+    }
+}
+
+void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    k_cell_sort<<<(ncells + 255) / 256, 256, 0, st>>>(sorted_orig, cell_start, ncells);
+    lc->n++;
+}
+
+template <bool F32>
+__global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ pos, const void* __restrict__ diam,
+                                                       const void* __restrict__ mass, const void* __restrict__ vel, PgtBox box,
+                                                       const int* __restrict__ sorted_orig, int n_live, double* __restrict__ sx,
+                                                       double* __restrict__ sy, double* __restrict__ sd, double* __restrict__ skxx,
+                                                       double* __restrict__ skxy, double* __restrict__ skyy)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n_live) return;
+    const long long i = sorted_orig[p];
+    double x, y;
+    load_wrapped<F32>(pos, i, box, x, y, nullptr);
+    sx[p] = x;
+    sy[p] = y;
+    sd[p] = ld_real<F32>(diam, i);
+    if (skxx) {
+        const double m = mass ? ld_real<F32>(mass, i) : 1.0;
+        double vx = 0.0, vy = 0.0;
+        if (vel) { vx = ld_real<F32>(vel, 3 * i); vy = ld_real<F32>(vel, 3 * i + 1); }
+        // KineticStress::compute (ListofCommonObservables.h:131-142): m * v[a] * v[b]
+        skxx[p] = m * vx * vx;
+        skxy[p] = m * vx * vy;
+        skyy[p] = m * vy * vy;
+    }
+}
+
+void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
+                              const int* sorted_orig, int n_live, double* sx, double* sy, double* sd, double* skxx,
+                              double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (n_live <= 0) return;
+    const int blocks = (n_live + 255) / 256;
+    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sd, skxx, skxy, skyy);
+    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sd, skxx, skxy, skyy);
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
+// Neighbour enumeration shared by the bond and thermo kernels.
+//
+// Visits every sorted particle q != p whose stored position lies within `rc` (inclusive) of
+// an image centre  c = r_p + k L,  k in {-1,0,1} per periodic axis -- Aboria's euclidean_search
+// (Search.h:186-193, 438-447) restricted to the cells that can contain a hit.  dx = r_q - c is
+// formed exactly as Aboria forms it, and accum = dx^2 + dy^2 (each product and the sum rounded
+// separately; the reference's third term is +0 in 2-D).
+struct Seg { int c0, c1, k; };
+
+__device__ __forceinline__ int split_segments(int u0, int u1, int nc, Seg seg[3])
+{
+    int n = 0;
+    for (int u = u0; u <= u1;) {
+        int k, c0, last;
+        if (u < 0) { k = +1; c0 = u + nc; last = -1; }
+        else if (u >= nc) { k = -1; c0 = u - nc; last = 2 * nc - 1; }
+        else { k = 0; c0 = u; last = nc - 1; }
+        const int ue = min(u1, last);
+        seg[n].c0 = c0; seg[n].c1 = c0 + (ue - u); seg[n].k = k;
+        ++n;
+        u = ue + 1;
+    }
+    return n;
+}
+
+template <class F>
+__device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, int p,
+                                                  double xi, double yi, double rc2, F&& visit)
+{
+    const int cx = cell_coord(xi, box.lo[0], cells.inv_cwx, cells.ncx);
+    const int cy = cell_coord(yi, box.lo[1], cells.inv_cwy, cells.ncy);
+    Seg seg[3];
+    const int nseg = split_segments(cx - cells.reach, cx + cells.reach, cells.ncx, seg);
+    for (int uy = cy - cells.reach; uy <= cy + cells.reach; ++uy) {
+        int ky = 0, row = uy;
+        if (uy < 0) { ky = +1; row = uy + cells.ncy; }
+        else if (uy >= cells.ncy) { ky = -1; row = uy - cells.ncy; }
+        const double cpy = yi + ky * box.L[1];
+        const int rbase = row * cells.ncx;
+        for (int s = 0; s < nseg; ++s) {
+            const double cpx = xi + seg[s].k * box.L[0];
+            const int qb = __ldg(fr.cell_start + rbase + seg[s].c0);
+            const int qe = __ldg(fr.cell_start + rbase + seg[s].c1 + 1);
+            for (int q = qb; q < qe; ++q) {
+                if (q == p) continue;
+                const double dx = __ldg(fr.sx + q) - cpx;
+                const double dy = __ldg(fr.sy + q) - cpy;
+                const double accum = dx * dx + dy * dy;
+                if (!(accum > rc2)) visit(q, dx, dy, accum);
+            }
+        }
+    }
+}
+
+// Stage 2/3.  MODE 0: count force-carrying half-bonds; 1: fill CSR (b, f, j);
+//             MODE 2: count neighbours within max_rcut; 3: fill j only.
+template <int MODEL, int MODE>
+__global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
+                                               int* __restrict__ counts, double2* __restrict__ hb_b, double* __restrict__ hb_f,
+                                               int* __restrict__ hb_j)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= fr.n) return;
+    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+    int n = 0;
+    int w = (MODE == 1 || MODE == 3) ? counts[p] : 0;
+    for_each_neighbor(fr, box, cells, p, xi, yi, rc2, [&](int q, double dx, double dy, double rsq) {
+        if (MODE >= 2) {
+            if (MODE == 3) hb_j[w++] = q;
+            ++n;
+            return;
+        }
+        const double dj = __ldg(fr.sd + q);
+        if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
+        if (MODE == 1) {
+            hb_b[w] = make_double2(dx, dy);
+            hb_f[w] = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_FDIVR);
+            hb_j[w] = q;
+            ++w;
+        }
+        ++n;
+    });
+    if (MODE == 0 || MODE == 2) counts[p] = n;
+}
+
+template <int MODEL>
+static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, int* counts,
+                               double2* hb_b, double* hb_f, int* hb_j, cudaStream_t st)
+{
+    const int blocks = (fr.n + 127) / 128;
+    switch (mode) {
+    case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
+    case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
+    case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
+    default: k_bonds<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
+    }
+}
+
+void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
+                      double2* hb_b, double* hb_f, int* hb_j, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (fr.n <= 0) return;
+    const double rc2 = max_rcut * max_rcut;   // std::pow(max_distance, 2)
+    PGT_DISPATCH_MODEL(pot.model, (launch_bonds_model<M>(mode, pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j, st)));
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
+// Stage 6: thermo pair sums.  One thread per particle visits its neighbours with orig_i < orig_j
+// (ThermoCalculator.h:77-86), block-reduces with warp shuffles, and a single-block second pass
+// adds the per-block partials in a fixed order and multiplies by 1/vol.
+#define THERMO_THREADS 128
+#define THERMO_NVAL 25   // virial 4 | kinetic 4 | energy 1 | born 16
+
+__device__ __forceinline__ double warp_sum(double v)
+{
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) v += __shfl_xor_sync(FULL_MASK, v, d);
+    return v;
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(THERMO_THREADS) k_thermo_pairs(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
+                                                                 unsigned obs_mask, double* __restrict__ partials)
+{
+    __shared__ double red[THERMO_THREADS / 32][THERMO_NVAL];
+    double acc[THERMO_NVAL];
+#pragma unroll
+    for (int k = 0; k < THERMO_NVAL; ++k) acc[k] = 0.0;
+
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < fr.n; p += gridDim.x * blockDim.x) {
+        const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+        const int oi = fr.sorig[p];
+        if ((obs_mask & PGT_OBS_KINETIC) && fr.skxx) {
+            acc[4] += fr.skxx[p]; acc[5] += fr.skxy[p]; acc[6] += fr.skxy[p]; acc[7] += fr.skyy[p];
+        }
+        if (!(obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_ENERGY | PGT_OBS_BORN))) continue;
+        for_each_neighbor(fr, box, cells, p, xi, yi, rc2, [&](int q, double dx, double dy, double rsq) {
+            if (!(oi < __ldg(fr.sorig + q))) return;
+            const double dj = __ldg(fr.sd + q);
+            const double f = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_FDIVR);
+            const double Fx = f * dx, Fy = f * dy;         // rij = +dx (ThermoCalculator.h:84)
+            if (obs_mask & PGT_OBS_VIRIAL) {
+                acc[0] += Fx * dx; acc[1] += Fy * dx; acc[2] += Fx * dy; acc[3] += Fy * dy;   // index a + 2 b
+            }
+            if (obs_mask & PGT_OBS_ENERGY) acc[8] += pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_ENERGY);
+            if (obs_mask & PGT_OBS_BORN) {
+                // (stiffness r_i + F_i) r_j n_k n_l  (ListofCommonObservables.h:157-184)
+                const double st = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_STIFF);
+                const double nrm = sqrt(rsq);
+                const double r[2] = { dx, dy }, F[2] = { Fx, Fy }, nv[2] = { dx / nrm, dy / nrm };
+#pragma unroll
+                for (int l = 0; l < 2; ++l)
+#pragma unroll
+                    for (int k = 0; k < 2; ++k)
+#pragma unroll
+                        for (int j = 0; j < 2; ++j)
+#pragma unroll
+                            for (int i = 0; i < 2; ++i)
+                                acc[9 + i + 2 * (j + 2 * (k + 2 * l))] += (st * r[i] + F[i]) * r[j] * nv[k] * nv[l];
+            }
+        });
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < THERMO_NVAL; ++k) {
+        const double s = warp_sum(acc[k]);
+        if (lane == 0) red[w][k] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < THERMO_NVAL) {
+        double s = 0.0;
+        for (int ww = 0; ww < THERMO_THREADS / 32; ++ww) s += red[ww][threadIdx.x];
+        partials[(size_t)blockIdx.x * THERMO_NVAL + threadIdx.x] = s;
+    }
+}
+
+__global__ void __launch_bounds__(32 * THERMO_NVAL) k_thermo_final(const double* __restrict__ partials, int nblocks, double inv_vol,
+                                                                   double* __restrict__ out)
+{
+    // one warp per value; lanes stride over the blocks, then a fixed-order shuffle tree
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double s = 0.0;
+    for (int b = lane; b < nblocks; b += 32) s += partials[(size_t)b * THERMO_NVAL + k];
+    s = warp_sum(s);
+    if (lane == 0) out[k] = s * inv_vol;      // val * (1/vol)  (ThermoProperty.h:84-87)
+}
+
+int pgt_thermo_blocks(int n)
+{
+    int b = (n + THERMO_THREADS - 1) / THERMO_THREADS;
+    return b < 1 ? 1 : (b > 148 * 16 ? 148 * 16 : b);
+}
+
+template <int MODEL>
+static void launch_thermo_model(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, unsigned obs_mask,
+                                double* partials, int blocks, cudaStream_t st)
+{
+    k_thermo_pairs<MODEL><<<blocks, THERMO_THREADS, 0, st>>>(pot, fr, box, cells, rc2, obs_mask, partials);
+}
+
+void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
+                       double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    int blocks = pgt_thermo_blocks(fr.n);
+    if (blocks > max_blocks) blocks = max_blocks;
+    const double rc2 = max_rcut * max_rcut;
+    PGT_DISPATCH_MODEL(pot.model, (launch_thermo_model<M>(pot, fr, box, cells, rc2, obs_mask, partials, blocks, st)));
+    k_thermo_final<<<1, 32 * THERMO_NVAL, 0, st>>>(partials, blocks, inv_vol, out_dev);
+    lc->n += 2;
+}
+
+// ------------------------------------------------------------------------------------------
+// Stage 4/5: the IK gather.
+//
+// A group of LANES threads owns one grid point x.  Per grid point:
+//  (1) candidate particles = the contiguous sorted ranges of the cell rows overlapping the disc's
+//      bounding box, one (row, x-segment) range per lane, flattened by a prefix sum;
+//  (2) each lane tests one candidate exactly as Aboria does for the outer search
+//      (dx = r_p - (x + kL); dx^2+dy^2 <= R^2, IrvingKirkwood.h:80-87), accumulates the local
+//      observables, and the in-disc lanes publish (2a/R^2, |a|^2/R^2, first half-bond) to shared memory;
+//  (3) the half-bonds of all in-disc particles are flattened into a work queue (prefix sum of the
+//      per-particle counts) and the lanes stride over it: per half-bond the squared distance along
+//      the bond is the quadratic  t(s) = c0 + s (c1 + s c2)  in units of R^2, the coarse-graining
+//      shape is summed at the Gauss-Legendre nodes, and  B f b(x)b  goes into three register
+//      accumulators;
+//  (4) a shuffle tree reduces the group, lane 0 stores 0.5 norm sum  (VirialStress::compute_cg).
+// No atomics anywhere; the result for a grid point is independent of how the grid is sharded.
+#define IK_THREADS 256
+#define IK_TILE_I 8
+#define IK_TILE_J 8
+#define IK_TILE (IK_TILE_I * IK_TILE_J)
+#define IK_QCAP_PER_LANE 16   // queue entries per group pass = 16 * LANES
+#define IK_MAX_RANGES 32
+
+template <int LANES>
+struct IKGroupSmem {
+    int rng_start[IK_MAX_RANGES];
+    int rng_cum[IK_MAX_RANGES + 1];
+    int rng_k[IK_MAX_RANGES];
+    double s_ax[LANES];
+    double s_ay[LANES];
+    double s_c0[LANES];
+    int s_hb0[LANES];
+    unsigned short queue[IK_QCAP_PER_LANE * LANES];
+};
+
+template <int LANES>
+__device__ __forceinline__ unsigned group_mask(int lane_in_warp)
+{
+    if constexpr (LANES >= 32) return FULL_MASK;
+    else return ((1u << LANES) - 1u) << ((lane_in_warp / LANES) * LANES);
+}
+
+template <int KERNEL, int Q>
+__device__ __forceinline__ double bond_quadrature(double c0, double c1, double c2, int nq)
+{
+    double B = 0.0;
+    if (Q > 0) {
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+            const double s = c_gl_s[k];
+            const double t = fma(fma(c2, s, c1), s, c0);
+            // t < 1 on the sign/exponent word: also true for the tiny negative t rounding can produce
+            if (__double2hiint(t) < 0x3FF00000) B = fma(c_gl_w[k], pgt_cg_shape<KERNEL>(t), B);
+        }
+    } else {
+        for (int k = 0; k < nq; ++k) {
+            const double s = c_gl_s[k];
+            const double t = fma(fma(c2, s, c1), s, c0);
+            if (__double2hiint(t) < 0x3FF00000) B = fma(c_gl_w[k], pgt_cg_shape<KERNEL>(t), B);
+        }
+    }
+    return B;
+}
+
+template <int KERNEL, int Q, int LANES, bool LOCAL>
+__global__ void __launch_bounds__(IK_THREADS) k_ik_gather(const PgtIKArgs A)
+{
+    constexpr int GROUPS = IK_THREADS / LANES;
+    constexpr int IK_QCAP = IK_QCAP_PER_LANE * LANES;
+    __shared__ IKGroupSmem<LANES> smem_all[GROUPS];
+
+    const int tid = threadIdx.x;
+    const int group = tid / LANES;
+    const int lane = tid % LANES;
+    const unsigned gmask = group_mask<LANES>(tid & 31);
+    IKGroupSmem<LANES>& sm = smem_all[group];
+
+    const PgtFrameView& fr = A.fr;
+    const double R = A.cg.rcut, R2 = A.cg.rcutsq, iR2 = A.inv_rcutsq;
+    const double Lx = A.box.L[0], Ly = A.box.L[1];
+    const int ncx = A.cells.ncx, ncy = A.cells.ncy;
+
+    // tile -> grid points
+    int tile_i0 = 0, tile_j0 = 0;
+    long long tile_base = 0;
+    if (A.grid.mode == 0) {
+        const int tiles_j = (A.grid.ny + IK_TILE_J - 1) / IK_TILE_J;
+        tile_i0 = (blockIdx.x / tiles_j) * IK_TILE_I;
+        tile_j0 = (blockIdx.x % tiles_j) * IK_TILE_J;
+    } else {
+        tile_base = A.grid.g0 + (long long)blockIdx.x * IK_TILE;
+    }
+
+    for (int it = group; it < IK_TILE; it += GROUPS) {
+        long long g;
+        double gx, gy;
+        if (A.grid.mode == 0) {
+            const int i = tile_i0 + it / IK_TILE_J, j = tile_j0 + it % IK_TILE_J;
+            if (i >= A.grid.nx || j >= A.grid.ny) continue;
+            g = (long long)i * A.grid.ny + j;
+            if (g < A.grid.g0 || g >= A.grid.g1) continue;
+            gx = __ldg(A.grid.xs + i);
+            gy = __ldg(A.grid.ys + j);
+        } else {
+            g = tile_base + it;
+            if (g >= A.grid.g1) continue;
+            gx = __ldg(A.grid.pts + 3 * g);
+            gy = __ldg(A.grid.pts + 3 * g + 1);
+        }
+
+        // image centres x + kL, k = -1, 0, +1 (Search.h:186-189)
+        const double cxm = gx + (-1) * Lx, cxp = gx + (+1) * Lx;
+        const double cym = gy + (-1) * Ly, cyp = gy + (+1) * Ly;
+
+        // unwrapped cell window of the disc's bounding box (padded against rounding at cell edges)
+        const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
+        int ux0 = __double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx);
+        int ux1 = __double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx);
+        int uy0 = __double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy);
+        int uy1 = __double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy);
+        ux0 = max(ux0, -ncx); ux1 = min(ux1, 2 * ncx - 1);
+        uy0 = max(uy0, -ncy); uy1 = min(uy1, 2 * ncy - 1);
+        Seg seg[3];
+        const int nseg = split_segments(ux0, ux1, ncx, seg);
+
+        double axx = 0.0, axy = 0.0, ayy = 0.0;          // virial accumulators (un-normalised)
+        double kxx = 0.0, kxy = 0.0, kyy = 0.0, rho = 0.0;
+
+        const int rows_per_batch = (nseg > 0) ? min(IK_MAX_RANGES, LANES) / nseg : 1;
+        for (int row0 = uy0; row0 <= uy1 && nseg > 0; row0 += rows_per_batch) {
+            const int nrows = min(rows_per_batch, uy1 - row0 + 1);
+            const int nrng = nrows * nseg;
+            // (1) one range per lane, prefix-summed
+            int cnt = 0;
+            if (lane < nrng) {
+                const int row = lane / nseg, sg = lane - row * nseg;
+                int uy = row0 + row, ky = 0;
+                if (uy < 0) { ky = +1; uy += ncy; }
+                else if (uy >= ncy) { ky = -1; uy -= ncy; }
+                const int rbase = uy * ncx;
+                const int qb = __ldg(fr.cell_start + rbase + seg[sg].c0);
+                const int qe = __ldg(fr.cell_start + rbase + seg[sg].c1 + 1);
+                cnt = qe - qb;
+                sm.rng_start[lane] = qb;
+                sm.rng_k[lane] = (seg[sg].k + 1) | ((ky + 1) << 2);
+            }
+            int inc = cnt;
+#pragma unroll
+            for (int d = 1; d < LANES; d <<= 1) {
+                const int t = __shfl_up_sync(gmask, inc, d, LANES);
+                if (lane >= d) inc += t;
+            }
+            if (lane < nrng) sm.rng_cum[lane] = inc - cnt;
+            const int C = __shfl_sync(gmask, inc, LANES - 1, LANES);
+            if (lane == 0) sm.rng_cum[nrng] = C;
+            __syncwarp(gmask);
+
+            // (2) candidate rounds
+            for (int ubase = 0; ubase < C; ubase += LANES) {
+                const int u = ubase + lane;
+                bool in = false;
+                int q = 0, nb = 0, hb0 = 0;
+                double ax = 0.0, ay = 0.0, d2 = 0.0;
+                if (u < C) {
+                    int r = 0;
+#pragma unroll
+                    for (int step = IK_MAX_RANGES / 2; step >= 1; step >>= 1) {
+                        const int m = r + step;
+                        if (m < nrng && sm.rng_cum[m] <= u) r = m;
+                    }
+                    q = sm.rng_start[r] + (u - sm.rng_cum[r]);
+                    const int kk = sm.rng_k[r];
+                    const int kx = (kk & 3) - 1, ky = (kk >> 2) - 1;
+                    const double cpx = kx == 0 ? gx : (kx < 0 ? cxm : cxp);
+                    const double cpy = ky == 0 ? gy : (ky < 0 ? cym : cyp);
+                    ax = __ldg(fr.sx + q) - cpx;
+                    ay = __ldg(fr.sy + q) - cpy;
+                    d2 = ax * ax + ay * ay;
+                    in = !(d2 > R2);
+                }
+                if (LOCAL && in) {
+                    const double cgval = pgt_cg_delta_exact(A.cg, d2);
+                    rho += cgval;
+                    if (fr.skxx) {
+                        kxx = fma(__ldg(fr.skxx + q), cgval, kxx);
+                        kxy = fma(__ldg(fr.skxy + q), cgval, kxy);
+                        kyy = fma(__ldg(fr.skyy + q), cgval, kyy);
+                    }
+                }
+                if (!(A.obs_mask & PGT_OBS_VIRIAL)) continue;
+                if (in) {
+                    hb0 = __ldg(fr.hb_off + q);
+                    nb = __ldg(fr.hb_off + q + 1) - hb0;
+                    sm.s_ax[lane] = ax * (2.0 * iR2);
+                    sm.s_ay[lane] = ay * (2.0 * iR2);
+                    sm.s_c0[lane] = d2 * iR2;
+                    sm.s_hb0[lane] = hb0;
+                }
+                // (3) flatten the half-bonds of the in-disc lanes
+                int tin = nb;
+#pragma unroll
+                for (int d = 1; d < LANES; d <<= 1) {
+                    const int t = __shfl_up_sync(gmask, tin, d, LANES);
+                    if (lane >= d) tin += t;
+                }
+                const int T = __shfl_sync(gmask, tin, LANES - 1, LANES);
+                const int off = tin - nb;
+                for (int T0 = 0; T0 < T; T0 += IK_QCAP) {
+                    __syncwarp(gmask);
+                    {   // producer: lane writes (lane, k) for its own half-bonds that fall in this window
+                        const int k_lo = max(0, T0 - off), k_hi = min(nb, T0 + IK_QCAP - off);
+                        for (int k = k_lo; k < k_hi; ++k) sm.queue[off + k - T0] = (unsigned short)((k << 5) | lane);
+                    }
+                    __syncwarp(gmask);
+                    const int Tw = min(IK_QCAP, T - T0);
+                    for (int t = lane; t < Tw; t += LANES) {
+                        const unsigned e = sm.queue[t];
+                        const int o = e & 31, k = e >> 5;
+                        const int rec = sm.s_hb0[o] + k;
+                        const double2 b = __ldg(fr.hb_b + rec);
+                        const double f = __ldg(fr.hb_f + rec);
+                        const double c0 = sm.s_c0[o];
+                        const double c1 = fma(sm.s_ax[o], b.x, sm.s_ay[o] * b.y);
+                        const double c2 = fma(b.x, b.x, b.y * b.y) * iR2;
+                        const double B = bond_quadrature<KERNEL, Q>(c0, c1, c2, A.nq);
+                        const double wf = B * f;
+                        const double tx = wf * b.x, ty = wf * b.y;
+                        axx = fma(tx, b.x, axx);
+                        axy = fma(tx, b.y, axy);
+                        ayy = fma(ty, b.y, ayy);
+                    }
+                }
+                __syncwarp(gmask);
+            }
+            __syncwarp(gmask);
+        }
+
+        // (4) group reduction and store
+#pragma unroll
+        for (int d = LANES / 2; d >= 1; d >>= 1) {
+            axx += __shfl_xor_sync(gmask, axx, d, LANES);
+            axy += __shfl_xor_sync(gmask, axy, d, LANES);
+            ayy += __shfl_xor_sync(gmask, ayy, d, LANES);
+            if (LOCAL) {
+                kxx += __shfl_xor_sync(gmask, kxx, d, LANES);
+                kxy += __shfl_xor_sync(gmask, kxy, d, LANES);
+                kyy += __shfl_xor_sync(gmask, kyy, d, LANES);
+                rho += __shfl_xor_sync(gmask, rho, d, LANES);
+            }
+        }
+        if (lane == 0) {
+            const long long lg = g - A.grid.g0;
+            if (A.out_virial && (A.obs_mask & PGT_OBS_VIRIAL)) {
+                const double scale = 0.5 * A.cg.norm;       // val += 0.5 * bondval * (f rij (x) rij)
+                double4 v = make_double4(scale * axx, scale * axy, scale * axy, scale * ayy);
+                *reinterpret_cast<double4*>(A.out_virial + 4 * lg) = v;
+            }
+            if (LOCAL && A.out_kinetic && (A.obs_mask & PGT_OBS_KINETIC)) {
+                double4 v = make_double4(kxx, kxy, kxy, kyy);
+                *reinterpret_cast<double4*>(A.out_kinetic + 4 * lg) = v;
+            }
+            if (LOCAL && A.out_density && (A.obs_mask & PGT_OBS_DENSITY)) A.out_density[lg] = rho;
+        }
+    }
+}
+
+template <int KERNEL, int Q, int LANES>
+static cudaError_t launch_ik_t(const PgtIKArgs& a, cudaStream_t st)
+{
+    long long blocks;
+    if (a.grid.mode == 0) {
+        // only the tile rows that intersect the shard
+        const int tiles_j = (a.grid.ny + IK_TILE_J - 1) / IK_TILE_J;
+        const int tiles_i = (a.grid.nx + IK_TILE_I - 1) / IK_TILE_I;
+        blocks = (long long)tiles_i * tiles_j;
+    } else {
+        blocks = (a.grid.g1 - a.grid.g0 + IK_TILE - 1) / IK_TILE;
+    }
+    if (blocks <= 0) return cudaSuccess;
+    const bool local = (a.obs_mask & (PGT_OBS_KINETIC | PGT_OBS_DENSITY)) != 0;
+    if (local) k_ik_gather<KERNEL, Q, LANES, true><<<(unsigned)blocks, IK_THREADS, 0, st>>>(a);
+    else k_ik_gather<KERNEL, Q, LANES, false><<<(unsigned)blocks, IK_THREADS, 0, st>>>(a);
+    return cudaGetLastError();
+}
+
+template <int KERNEL, int LANES>
+static cudaError_t launch_ik_q(const PgtIKArgs& a, cudaStream_t st)
+{
+    switch (a.nq) {
+    case 5: return launch_ik_t<KERNEL, 5, LANES>(a, st);
+    default: return launch_ik_t<KERNEL, 0, LANES>(a, st);
+    }
+}
+
+template <int LANES>
+static cudaError_t launch_ik_k(const PgtIKArgs& a, cudaStream_t st)
+{
+    switch (a.cg.kernel) {
+    case PGT_CG_OCTIC: return launch_ik_q<PGT_CG_OCTIC, LANES>(a, st);
+    case PGT_CG_RECT: return launch_ik_q<PGT_CG_RECT, LANES>(a, st);
+    default: return launch_ik_q<PGT_CG_MOLLIFIER, LANES>(a, st);
+    }
+}
+
+cudaError_t pgt_launch_ik(const PgtIKArgs& a, int lanes, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    lc->n++;
+    switch (lanes) {
+    case 8: return launch_ik_k<8>(a, st);
+    case 16: return launch_ik_k<16>(a, st);
+    default: return launch_ik_k<32>(a, st);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// FP64 FMA peak probe: 8 independent dependent-chains per thread.
+__global__ void __launch_bounds__(256) k_fp64_probe(double* out, int iters)
+{
+    double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+    const double m = 0.999999, c = 1e-7;
+    for (int i = 0; i < iters; ++i) {
+        a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+        a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+    }
+    out[(size_t)blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+void pgt_launch_fp64_probe(double* out, int iters, int blocks, int threads, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    k_fp64_probe<<<blocks, threads, 0, st>>>(out, iters);
+    lc->n++;
+}

@@ -1,0 +1,96 @@
+// pgt_kernels.cuh -- hand-written sm_100a kernels for the IK / thermo pair-sum path.
+//
+// Stage map (BASELINE.json north_star):
+//   0/1  k_wrap_count, scan, k_scatter_ids, k_cell_sort, k_gather_sorted   (cell list, counting sort)
+//   2/3  k_bonds<MODEL, COUNT|FILL>                                        (pair force + compacted half-bonds)
+//   4/5  k_ik_gather<KERNEL, Q, LANES, LOCAL>                              (IK field gather + local observables)
+//   6    k_thermo_pairs<MODEL>, k_thermo_final                             (global virial / energy / Born / kinetic)
+// All arithmetic is FP64; no tensor cores (there is no dense contraction on this path).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "pgt_math.cuh"
+
+#define PGT_MAX_GL 1024          // quadrature nodes kept in constant memory
+#define PGT_WRAP_MAX_ITERS 4096  // a position further than this many box lengths outside is a data error
+
+// error bits raised by kernels (checked by the host after each stage)
+enum { PGT_EFLAG_Z_NONZERO = 1, PGT_EFLAG_WRAP_RUNAWAY = 2, PGT_EFLAG_BOND_OVERFLOW = 4 };
+
+struct PgtBox {
+    double lo[3], hi[3], L[3];
+    int dim;
+};
+
+struct PgtCells {
+    int ncx, ncy;
+    double inv_cwx, inv_cwy;     // 1 / cell width
+    int reach;                   // cells to visit on each side for the max_rcut search
+};
+
+// Sorted (by cell, row-major) structure-of-arrays view of the live particles + half-bond CSR.
+struct PgtFrameView {
+    int n;                       // live particles
+    const double* sx;            // wrapped x
+    const double* sy;            // wrapped y
+    const double* sd;            // diameter
+    const double* skxx;          // (m vx) vx   (NULL when the frame has no velocities)
+    const double* skxy;          // (m vx) vy
+    const double* skyy;          // (m vy) vy
+    const int* sorig;            // original particle index
+    const int* cell_start;       // ncx*ncy + 1
+    const int* hb_off;           // n + 1  : half-bond CSR offsets
+    const double2* hb_b;         // r_j(image) - r_i
+    const double* hb_f;          // -phi'(r)/r
+    const int* hb_j;             // sorted index of j
+};
+
+struct PgtGridView {
+    int mode;                    // 0 cartesian, 1 point list
+    int nx, ny;
+    const double* xs;            // cartesian axes
+    const double* ys;
+    const double* pts;           // G x 3
+    long long g0, g1;            // shard
+};
+
+struct PgtIKArgs {
+    PgtFrameView fr;
+    PgtGridView grid;
+    PgtBox box;
+    PgtCells cells;
+    PgtCG cg;
+    double inv_rcutsq;           // 1 / R^2
+    int nq;                      // quadrature nodes (generic path)
+    double* out_virial;          // (g1-g0) x 4
+    double* out_kinetic;         // (g1-g0) x 4
+    double* out_density;         // (g1-g0)
+    unsigned obs_mask;
+};
+
+struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 16 (2-D)
+
+// ---- launch wrappers (defined in pgt_kernels.cu) ---------------------------------------------
+struct PgtLaunchCounter { long long n; };
+
+cudaError_t pgt_upload_gl_tables(const double* s, const double* w, int n, cudaStream_t st);
+
+void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
+                           int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
+void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* block_sums, cudaStream_t st, PgtLaunchCounter* lc);
+long long pgt_scan_scratch_ints(long long n);
+void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_start, int* cell_fill, int* sorted_orig,
+                            cudaStream_t st, PgtLaunchCounter* lc);
+void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc);
+void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
+                              const int* sorted_orig, int n_live, double* sx, double* sy, double* sd, double* skxx,
+                              double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
+// mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
+// mode 2/3: same for plain neighbours within max_rcut (export only).
+void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
+                      double2* hb_b, double* hb_f, int* hb_j, cudaStream_t st, PgtLaunchCounter* lc);
+cudaError_t pgt_launch_ik(const PgtIKArgs& a, int lanes, cudaStream_t st, PgtLaunchCounter* lc);
+void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
+                       double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
+int pgt_thermo_blocks(int n);
+void pgt_launch_fp64_probe(double* out, int iters, int blocks, int threads, cudaStream_t st, PgtLaunchCounter* lc);

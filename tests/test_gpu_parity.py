@@ -1,0 +1,353 @@
+"""GPU parity tests: the CUDA path (through the C-ABI) against the CPU oracle on the same inputs.
+
+Tolerances are BASELINE.json's: bit-exact neighbour / bond sets; stress and energy within 1e-10
+relative (1e-12 absolute for near-zero components).
+"""
+import numpy as np
+import pytest
+
+from pyglasstools_b200 import _capi, synth
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-10, 1e-12
+
+
+def assert_close(a, b, rtol=RTOL, atol=ATOL, scale=None):
+    a, b = np.asarray(a), np.asarray(b)
+    s = np.abs(b) if scale is None else scale
+    err = np.abs(a - b)
+    bad = err > (atol + rtol * s)
+    assert not bad.any(), "max abs err %.3e, max rel err %.3e at %d entries" % (
+        err.max(), (err / np.maximum(np.abs(b), 1e-300)).max(), int(bad.sum()))
+
+
+def setup_ctx(ctx, orc, P, name, pos, diam, box, vel=None, mass=None):
+    S = orc.System(box, pos, diam, vel=vel, mass=mass)
+    ctx.set_potential(name, P.scaled_rcut, orc.pot_params(P))
+    ctx.set_max_rcut(S.max_rcut(P))
+    ctx.upload(pos, diam, box, mass=mass, vel=vel)
+    ctx.build_cells()
+    return S
+
+
+GPU_NAME = {"poly12": "poly12", "poly18": "poly18", "poly10": "poly10", "poly106": "poly106",
+            "polyyukawa": "polyyukawa", "polylj": "polylj", "lj": "lj", "fslj": "forceshifted-lj"}
+
+
+def pairs_key(i, j):
+    return set(zip(i.tolist(), j.tolist()))
+
+
+@pytest.mark.parametrize("frame", [0, 180, 199])
+def test_fixture_neighbor_and_bond_sets_bit_exact(gpu_ctx, orc, fixture_frames, frame):
+    P = orc.potential("poly12")
+    pos, diam, box = fixture_frames.position(frame), fixture_frames.diameter, fixture_frames.box
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    oi, oj, orij, ofl = S.neighbor_pairs(P)
+    gi, gj = gpu_ctx.export_neighbors()
+    assert len(gi) == len(oi)
+    assert pairs_key(gi, gj) == pairs_key(oi, oj)
+    bi, bj, brij, bf = gpu_ctx.export_bonds()
+    m = ofl.astype(bool)
+    assert len(bi) == int(m.sum())
+    assert pairs_key(bi, bj) == pairs_key(oi[m], oj[m])
+    # r_ij and f of every bond, matched by (i,j)
+    ref = {(a, b): (r, k) for a, b, r, k in zip(oi[m].tolist(), oj[m].tolist(), orij[m], range(int(m.sum())))}
+    fd = orc.pair_table(P, orij[m], S_diam(S, oi[m], diam), S_diam(S, oj[m], diam))["fdivr"]
+    for a, b, r, f in zip(bi.tolist(), bj.tolist(), brij, bf):
+        rr, k = ref[(a, b)]
+        assert r[0] == rr[0] and r[1] == rr[1]          # bit-exact image-resolved separation
+        assert f == fd[k]                               # bit-exact force (same operation order)
+
+
+def S_diam(S, idx, diam):
+    return np.asarray(diam, np.float64)[idx]
+
+
+@pytest.mark.parametrize("frame", [180, 190, 199])
+def test_fixture_ik_virial_field(gpu_ctx, orc, fixture_frames, frame):
+    """cfg1: example_scripts/irvingkirkwood on the shipped frames (octic R=2, GL-5, dx=0.25)."""
+    P = orc.potential("poly12")
+    cg = orc.cgfunc("octic", 2.0, 5)
+    pos, diam, box = fixture_frames.position(frame), fixture_frames.diameter, fixture_frames.box
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    nmax = int(L / 0.25)
+    axis = synth.linspace_axis(L, nmax)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_DENSITY)
+    got = gpu_ctx.ik_download(_capi.FIELD_VIRIAL)
+    grid, n2 = orc.cartesian_grid(L, 0.25)
+    assert n2 == nmax == 127
+    want = S.ik(P, cg, grid, obs_mask=1 | 4)
+    assert_close(got, want["virial"], scale=np.abs(want["virial"]).max(axis=1, keepdims=True))
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_DENSITY), want["density"])
+
+
+@pytest.mark.parametrize("frame", [0, 57, 199])
+def test_fixture_thermo(gpu_ctx, orc, fixture_frames, frame):
+    P = orc.potential("poly12")
+    pos, diam, box = fixture_frames.position(frame), fixture_frames.diameter, fixture_frames.box
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    got = gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY | _capi.OBS_BORN | _capi.OBS_KINETIC)
+    want = S.thermo(P)
+    assert_close(got["virial"], want["virial"], scale=np.abs(want["virial"]).max())
+    assert_close(got["energy"], want["energy"])
+    assert_close(got["born"], want["born"], scale=np.abs(want["born"]).max())
+    assert np.all(got["kinetic"] == 0)
+
+
+def test_born_known_answer_on_gpu(gpu_ctx, orc, fixture_frames):
+    """The reference README's only known-answer value (README.md:149-172), computed on the GPU."""
+    P = orc.potential("poly12")
+    b0101, bdiff = [], []
+    D = 2
+    idx = lambda i, j, k, l: l + D * (k + D * (j + D * i))      # io.py:78
+    rd = lambda v: float("%f" % v)                              # std::to_string, ThermoProperty.h:196
+    for f in range(200):
+        setup_ctx(gpu_ctx, orc, P, "poly12", fixture_frames.position(f), fixture_frames.diameter, fixture_frames.box)
+        r = gpu_ctx.thermo(_capi.OBS_BORN)
+        b0101.append(rd(r["born"][idx(0, 1, 0, 1)]))
+        bdiff.append(rd(r["born"][idx(0, 0, 0, 0)]) - rd(r["born"][idx(0, 0, 1, 1)]))
+    assert abs(np.mean(b0101) - 14.89655895) < 5e-9
+    assert abs(0.5 * np.mean(bdiff) - 14.8769594875) < 5e-9
+
+
+@pytest.mark.parametrize("model", ["poly18", "poly10", "poly106", "polylj", "polyyukawa", "lj", "fslj"])
+def test_other_potentials_ik_and_thermo(gpu_ctx, orc, model):
+    fr = synth.synth_frame(32, 77)
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential(model)
+    S = setup_ctx(gpu_ctx, orc, P, GPU_NAME[model], pos, diam, box)
+    gpu_ctx.build_bonds()
+    oi, oj, orij, ofl = S.neighbor_pairs(P)
+    bi, bj, _, _ = gpu_ctx.export_bonds()
+    m = ofl.astype(bool)
+    assert pairs_key(bi, bj) == pairs_key(oi[m], oj[m])
+    got = gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY | _capi.OBS_BORN)
+    want = S.thermo(P)
+    assert_close(got["virial"], want["virial"], scale=np.abs(want["virial"]).max())
+    assert_close(got["energy"], want["energy"])
+    assert_close(got["born"], want["born"], scale=np.abs(want["born"]).max())
+    cg = orc.cgfunc("octic", 2.0, 5)
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 40)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    grid = np.zeros((1600, 3)); grid[:, 0] = np.repeat(axis, 40); grid[:, 1] = np.tile(axis, 40)
+    wantf = S.ik(P, cg, grid)["virial"]
+    assert_close(gpu_ctx.ik_download(), wantf, scale=np.abs(wantf).max(axis=1, keepdims=True))
+
+
+@pytest.mark.parametrize("kernel,order,R", [("octic", 1, 2.0), ("octic", 2, 2.5), ("octic", 8, 2.0), ("octic", 20, 3.0),
+                                             ("octic", 7, 4.0), ("mollifier", 5, 2.0), ("mollifier", 12, 2.5),
+                                             ("rect", 5, 2.0)])
+def test_cg_kernels_and_orders(gpu_ctx, orc, kernel, order, R):
+    fr = synth.synth_frame(24, 5)
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    cg = orc.cgfunc(kernel, R, order)
+    gpu_ctx.set_cg(kernel, R, order)
+    rng = np.random.default_rng(3)
+    L = float(box[0])
+    pts = np.zeros((500, 3)); pts[:, :2] = rng.uniform(-L / 2, L / 2, (500, 2))
+    gpu_ctx.set_grid_points(pts)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_DENSITY)
+    want = S.ik(P, cg, pts, obs_mask=1 | 4)
+    got = gpu_ctx.ik_download()
+    if kernel == "rect":
+        # discontinuous kernel: a quadrature node within rounding of the disc edge may flip; allow a handful
+        err = np.abs(got - want["virial"]) > (ATOL + RTOL * np.abs(want["virial"]).max(axis=1, keepdims=True))
+        assert err.any(axis=1).sum() <= 2
+    else:
+        assert_close(got, want["virial"], scale=np.abs(want["virial"]).max(axis=1, keepdims=True))
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_DENSITY), want["density"], scale=np.abs(want["density"]).max())
+
+
+def test_kinetic_field_and_thermo_kinetic(gpu_ctx, orc):
+    fr = synth.synth_frame(24, 11, velocities=True)
+    pos, diam, box, vel = fr["position"], fr["diameter"], fr["box"], fr["velocity"]
+    mass = (1.0 + np.arange(len(diam)) % 3).astype(np.float32)
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box, vel=vel, mass=mass)
+    gpu_ctx.build_bonds()
+    cg = orc.cgfunc("octic", 2.0, 5)
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 30)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_KINETIC)
+    grid = np.zeros((900, 3)); grid[:, 0] = np.repeat(axis, 30); grid[:, 1] = np.tile(axis, 30)
+    want = S.ik(P, cg, grid, obs_mask=1 | 2, kinetic_mode=0)
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_KINETIC), want["kinetic"], scale=np.abs(want["kinetic"]).max(axis=1, keepdims=True))
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_VIRIAL), want["virial"], scale=np.abs(want["virial"]).max(axis=1, keepdims=True))
+    t = gpu_ctx.thermo(_capi.OBS_KINETIC)
+    assert_close(t["kinetic"], S.thermo(P)["kinetic"], scale=np.abs(S.thermo(P)["kinetic"]).max())
+
+
+def test_edge_cases_seam_disc_edge_and_outside_points(gpu_ctx, orc):
+    """Particles on the periodic seam, exactly on the disc edge (||r-x|| == R), exactly at the pair
+    cut-off, a deleted particle (z outside the slab), unwrapped inputs, grid points at +-L/2."""
+    L = 16.0
+    box = np.array([L, L, 1.0])
+    pos = []
+    rng = np.random.default_rng(9)
+    for i in range(8):
+        for j in range(8):
+            pos.append([-8 + 2 * i + 0.25 + 0.5 * rng.random(), -8 + 2 * j + 0.25 + 0.5 * rng.random(), 0.0])
+    pos += [[-8.0, 0.0, 0.0], [7.99999, 0.5, 0.0], [0.0, -8.0, 0.0], [0.3, 7.9999, 0.0]]      # seam
+    pos += [[2.0, 0.0, 0.0], [0.0, -2.0, 0.0]]                  # exactly R=2 from the grid point (0,0)
+    pos += [[24.5, 1.0, 0.0], [-17.0, -9.5, 0.0]]               # need wrapping by one / two box lengths
+    pos += [[1.0, 1.0, 0.75]]                                   # outside the z slab: deleted by Aboria
+    pos = np.array(pos, np.float64)
+    diam = np.full(len(pos), 1.0); diam[::3] = 1.25; diam[1::5] = 0.8
+    # a pair exactly at the cut-off: sigma = 1 (d=1,1), rcut = 1.25 -> r = 1.25 gives rsq == rcut^2 sigma^2 (strict <: no bond)
+    pos = np.vstack([pos, [[5.0, 5.0, 0.0], [6.25, 5.0, 0.0]]])
+    diam = np.concatenate([diam, [1.0, 1.0]])
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    assert gpu_ctx.counts()["n_live"] == S.n == len(pos) - 1
+    wp, ids = S.wrapped()
+    gxy, alive = gpu_ctx.export_wrapped(len(pos))
+    assert alive.sum() == S.n and not alive[len(pos) - 3]
+    assert np.array_equal(gxy[ids], wp[:, :2])
+    gpu_ctx.build_bonds()
+    oi, oj, orij, ofl = S.neighbor_pairs(P, brute=True)
+    gi, gj = gpu_ctx.export_neighbors()
+    assert pairs_key(gi, gj) == pairs_key(oi, oj)
+    bi, bj, _, _ = gpu_ctx.export_bonds()
+    m = ofl.astype(bool)
+    assert pairs_key(bi, bj) == pairs_key(oi[m], oj[m])
+    n = len(pos)
+    assert (n - 2, n - 1) in pairs_key(gi, gj) and (n - 2, n - 1) not in pairs_key(bi, bj)
+    cg = orc.cgfunc("octic", 2.0, 5)
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    pts = np.array([[0, 0, 0], [8.0, 8.0, 0], [-8.0, -8.0, 0], [8.0, 0.1, 0], [-8.0, 3.0, 0], [7.5, -7.5, 0],
+                    [0.0, 8.0, 0], [3.0, 3.0, 0], [12.0, 0.0, 0], [-30.0, 2.0, 0]], np.float64)
+    gpu_ctx.set_grid_points(pts)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_DENSITY)
+    want = S.ik(P, cg, pts, obs_mask=1 | 4, brute=True, counts=True)
+    assert want["counts"][0, 0] >= 2       # the two edge particles are inside (inclusive <=)
+    assert_close(gpu_ctx.ik_download(), want["virial"], scale=np.abs(want["virial"]).max(axis=1, keepdims=True) + 1e-300)
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_DENSITY), want["density"])
+    # the periodic duplicates: the field at +L/2 equals the field at -L/2
+    f = gpu_ctx.ik_download()
+    assert_close(f[1], f[2], scale=np.abs(f[1]).max())
+
+
+def test_empty_and_tiny_inputs(gpu_ctx, orc):
+    P = orc.potential("poly12")
+    box = np.array([12.0, 12.0, 1.0])
+    pos = np.array([[0.0, 0.0, 0.0], [0.9, 0.1, 0.0]])
+    diam = np.array([1.0, 1.1])
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    assert gpu_ctx.counts()["n_halfbonds"] == 2
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    gpu_ctx.set_grid_points(np.zeros((0, 3)))
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    assert gpu_ctx.ik_download().shape == (0, 4)
+    pts = np.array([[0.3, 0.0, 0.0], [5.0, 5.0, 0.0]])
+    gpu_ctx.set_grid_points(pts)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    cg = orc.cgfunc("octic", 2.0, 5)
+    want = S.ik(P, cg, pts)["virial"]
+    got = gpu_ctx.ik_download()
+    assert_close(got, want, scale=np.abs(want).max())
+    assert np.all(got[1] == 0)
+    t = gpu_ctx.thermo()
+    assert_close(t["energy"], S.thermo(P)["energy"])
+    # a frame with no force-carrying pair at all
+    pos2 = np.array([[0.0, 0.0, 0.0], [4.0, 4.0, 0.0]])
+    setup_ctx(gpu_ctx, orc, P, "poly12", pos2, diam, box)
+    gpu_ctx.build_bonds()
+    assert gpu_ctx.counts()["n_halfbonds"] == 0
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    assert np.all(gpu_ctx.ik_download() == 0)
+
+
+def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames):
+    """np.array_split shards (irvingkirkwood/__init__.py:53-60) reproduce the unsharded field bit for bit."""
+    P = orc.potential("poly12")
+    pos, diam, box = fixture_frames.position(185), fixture_frames.diameter, fixture_frames.box
+    setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 127)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    full = gpu_ctx.ik_download()
+    G = 127 * 127
+    for nshard in (2, 5, 8):
+        sizes = [len(c) for c in np.array_split(np.arange(G), nshard)]
+        parts, g0 = [], 0
+        for s in sizes:
+            gpu_ctx.set_shard(g0, g0 + s)
+            gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+            parts.append(gpu_ctx.ik_download())
+            g0 += s
+        assert np.array_equal(np.vstack(parts), full)
+    gpu_ctx.set_shard(0, G)
+
+
+@pytest.mark.parametrize("lanes", [8, 16, 32])
+def test_group_width_variants(orc, fixture_frames, lanes, monkeypatch):
+    monkeypatch.setenv("PGT_IK_LANES", str(lanes))
+    ctx = _capi.Context(0)
+    try:
+        P = orc.potential("poly12")
+        cg = orc.cgfunc("octic", 2.0, 5)
+        pos, diam, box = fixture_frames.position(181), fixture_frames.diameter, fixture_frames.box
+        S = setup_ctx(ctx, orc, P, "poly12", pos, diam, box)
+        ctx.build_bonds()
+        ctx.set_cg("octic", 2.0, 5)
+        L = float(box[0])
+        axis = synth.linspace_axis(L, 60)
+        ctx.set_grid_cartesian(axis, axis)
+        ctx.ik_compute(_capi.OBS_VIRIAL)
+        grid = np.zeros((3600, 3)); grid[:, 0] = np.repeat(axis, 60); grid[:, 1] = np.tile(axis, 60)
+        want = S.ik(P, cg, grid)["virial"]
+        assert_close(ctx.ik_download(), want, scale=np.abs(want).max(axis=1, keepdims=True))
+    finally:
+        ctx.close()
+
+
+def test_synthetic_large_frame_properties(gpu_ctx, orc):
+    """N = 65536 (cfg2 size): full thermo parity, IK parity on a strided subsample of a 256^2 grid, and
+    the size-independent checks: bond symmetry (every (i,j) has its (j,i)) and the IK field summed
+    against the oracle's own sum."""
+    fr = synth.synth_frame(256, synth.SEEDS["cfg2"])
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    bi, bj, brij, bf = gpu_ctx.export_bonds()
+    fwd = dict(zip(zip(bi.tolist(), bj.tolist()), range(len(bi))))
+    for (a, b), k in list(fwd.items())[:: max(1, len(fwd) // 5000)]:
+        k2 = fwd[(b, a)]
+        assert bf[k] == bf[k2] and np.array_equal(brij[k], -brij[k2])
+    got = gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY)
+    want = S.thermo(P, born=False)
+    assert_close(got["virial"], want["virial"], scale=np.abs(want["virial"]).max())
+    assert_close(got["energy"], want["energy"])
+    cg = orc.cgfunc("octic", 2.0, 5)
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 256)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    full = gpu_ctx.ik_download().reshape(256, 256, 4)
+    ii = np.arange(0, 256, 5)
+    grid = np.zeros((len(ii) ** 2, 3)); grid[:, 0] = np.repeat(axis[ii], len(ii)); grid[:, 1] = np.tile(axis[ii], len(ii))
+    wantf = S.ik(P, cg, grid)["virial"]
+    gotf = full[np.ix_(ii, ii)].reshape(-1, 4)
+    assert_close(gotf, wantf, scale=np.abs(wantf).max(axis=1, keepdims=True))
+    assert np.array_equal(full[0], full[-1]) or np.allclose(full[0], full[-1], rtol=1e-12, atol=1e-12)
