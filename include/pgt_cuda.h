@@ -131,6 +131,18 @@ double pgt_cg_delta(int kernel_id, double cg_rcut, double dr_sq);
 double pgt_cg_bond(int kernel_id, double cg_rcut, int order, const double x[3], const double ri[3], const double rij[3]);
 /* FP64 FMA peak probe: runs a dependent-chain DFMA kernel, returns achieved TFLOP/s.            */
 int pgt_fp64_peak_probe(pgt_ctx* ctx, double* tflops);
+/* Algorithmic work of the IK gather: sum over the local shard of U(x), the
+ * number of unique force-carrying bonds with at least one endpoint within cg_rcut of x; also the
+ * number of (grid point, half-bond) items the gather kernel actually integrates.                */
+int pgt_ik_count_work(pgt_ctx* ctx, int64_t* sum_unique_bonds, int64_t* sum_halfbond_items, int64_t* sum_particles);
+/* User events on the ctx stream (slots 0..15) for timing several stages as one region.          */
+int pgt_event_record(pgt_ctx* ctx, int slot);
+int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
+/* Page-locked host memory for the caller's frame / field buffers (cudaHostAlloc / cudaFreeHost). */
+int pgt_host_alloc(void** ptr, uint64_t bytes);
+int pgt_host_free(void* ptr);
+/* Tuning knobs: "ik_lanes" (8, 16 or 32 threads per grid point).                                */
+int pgt_set_option(pgt_ctx* ctx, const char* name, double value);
 
 /* ---- multi-GPU (NCCL over NVLink) ---------------------------------------------------------- */
 /* 128-byte NCCL unique id, to be broadcast by the caller's own plumbing.                       */

@@ -25,7 +25,8 @@ EXPORTED = [
     "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_device_ptr",
     "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
     "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
-    "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
+    "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
+    "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
 ]
 
 _lib = None
@@ -84,6 +85,12 @@ def lib():
         L.pgt_export_wrapped.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         L.pgt_stage_time_ms.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_float)]
         L.pgt_fp64_peak_probe.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.pgt_ik_count_work.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
+        L.pgt_event_record.argtypes = [C.c_void_p, C.c_int]
+        L.pgt_event_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
+        L.pgt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
+        L.pgt_host_free.argtypes = [C.c_void_p]
+        L.pgt_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
         L.pgt_comm_unique_id.argtypes = [C.c_void_p]
         L.pgt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         L.pgt_comm_allgather_field.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p]
@@ -252,6 +259,22 @@ class Context:
     def launches(self):
         return lib().pgt_kernel_launches(self._h)
 
+    def ik_count_work(self):
+        u, it, pa = C.c_int64(), C.c_int64(), C.c_int64()
+        self._ck(lib().pgt_ik_count_work(self._h, C.byref(u), C.byref(it), C.byref(pa)))
+        return dict(unique_bonds=u.value, halfbond_items=it.value, particles=pa.value)
+
+    def event_record(self, slot):
+        self._ck(lib().pgt_event_record(self._h, int(slot)))
+
+    def event_elapsed_ms(self, a, b):
+        ms = C.c_float()
+        self._ck(lib().pgt_event_elapsed_ms(self._h, int(a), int(b), C.byref(ms)))
+        return ms.value
+
+    def set_option(self, name, value):
+        self._ck(lib().pgt_set_option(self._h, name.encode(), float(value)))
+
     def fp64_peak(self):
         t = C.c_double()
         self._ck(lib().pgt_fp64_peak_probe(self._h, C.byref(t)))
@@ -278,6 +301,33 @@ class Context:
         a = np.ascontiguousarray(arr, np.float64)
         self._ck(lib().pgt_comm_allreduce_sum(self._h, _dp(a), a.size))
         return a
+
+
+class PinnedArray:
+    """A numpy view over page-locked host memory (cudaHostAlloc) owned by this object."""
+
+    def __init__(self, shape, dtype):
+        self.shape = tuple(int(x) for x in np.atleast_1d(shape))
+        self.dtype = np.dtype(dtype)
+        nbytes = int(np.prod(self.shape)) * self.dtype.itemsize
+        self._p = C.c_void_p()
+        rc = lib().pgt_host_alloc(C.byref(self._p), max(nbytes, 1))
+        if rc != 0:
+            raise PgtError(rc, lib().pgt_last_error(None).decode())
+        buf = (C.c_char * max(nbytes, 1)).from_address(self._p.value)
+        self.array = np.frombuffer(buf, dtype=self.dtype, count=int(np.prod(self.shape))).reshape(self.shape)
+
+    def free(self):
+        if self._p:
+            self.array = None
+            lib().pgt_host_free(self._p)
+            self._p = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
 
 
 def pair_eval(model, scaled_rcut, params, rij, di, dj, what):

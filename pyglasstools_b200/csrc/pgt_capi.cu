@@ -149,8 +149,10 @@ struct pgt_ctx {
     cudaEvent_t ev0[PGT_STAGE_COUNT]{}, ev1[PGT_STAGE_COUNT]{};
     bool ev_valid[PGT_STAGE_COUNT]{};
 
+    cudaEvent_t user_ev[16]{};
+
     // tuning
-    int ik_lanes = 32;
+    int ik_lanes = 8;
 
     // nccl
     pgtNcclComm comm = nullptr;
@@ -307,6 +309,8 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
         cudaEventDestroy(ctx->ev1[s]);
     }
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
+    for (auto& e : ctx->user_ev)
+        if (e) cudaEventDestroy(e);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PGT_OK;
@@ -627,6 +631,8 @@ int pgt_grid_set_shard(pgt_ctx* ctx, int64_t g0, int64_t g1)
 }
 
 // ---------------------------------------------------------------------------------- compute
+static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask);
+#define ik_args ik_args_impl
 int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
 {
     if (!ctx) return PGT_ERR_ARG;
@@ -644,6 +650,16 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 4 * n);
     if (obs_mask & PGT_OBS_DENSITY) ENSURE(ctx->out_density, sizeof(double) * n);
 
+    PgtIKArgs a = ik_args(ctx, obs_mask);
+    stage_begin(ctx, PGT_STAGE_IK);
+    if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_lanes, ctx->stream, &ctx->launches));
+    stage_end(ctx, PGT_STAGE_IK);
+    ctx->last_ik_mask = obs_mask;
+    return PGT_OK;
+}
+
+static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
+{
     PgtIKArgs a{};
     a.fr = frame_view(ctx);
     a.grid.mode = ctx->grid_mode;
@@ -663,11 +679,71 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     a.out_kinetic = ctx->out_kinetic.as<double>();
     a.out_density = ctx->out_density.as<double>();
     a.obs_mask = obs_mask;
-    stage_begin(ctx, PGT_STAGE_IK);
-    if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_lanes, ctx->stream, &ctx->launches));
-    stage_end(ctx, PGT_STAGE_IK);
-    ctx->last_ik_mask = obs_mask;
+    return a;
+}
+
+int pgt_ik_count_work(pgt_ctx* ctx, int64_t* sum_unique_bonds, int64_t* sum_halfbond_items, int64_t* sum_particles)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!ctx->bonds_built || !ctx->have_cg || ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_count_work: frame, bonds, cg and grid required");
+    CK(cudaSetDevice(ctx->device));
+    DevBuf out;
+    ENSURE(out, sizeof(unsigned long long) * 4);
+    CK(cudaMemsetAsync(out.p, 0, sizeof(unsigned long long) * 4, ctx->stream));
+    PgtIKArgs a = ik_args_impl(ctx, PGT_OBS_VIRIAL);
+    pgt_launch_ik_count(a, out.as<unsigned long long>(), ctx->stream, &ctx->launches);
+    unsigned long long h[3] = { 0, 0, 0 };
+    CK(cudaMemcpyAsync(h, out.p, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    cudaFree(out.p);
+    if (sum_unique_bonds) *sum_unique_bonds = (int64_t)h[0];
+    if (sum_halfbond_items) *sum_halfbond_items = (int64_t)h[1];
+    if (sum_particles) *sum_particles = (int64_t)h[2];
     return PGT_OK;
+}
+
+int pgt_event_record(pgt_ctx* ctx, int slot)
+{
+    if (!ctx || slot < 0 || slot >= 16) return fail(ctx, PGT_ERR_ARG, "pgt_event_record: slot out of range");
+    CK(cudaSetDevice(ctx->device));
+    if (!ctx->user_ev[slot]) CK(cudaEventCreate(&ctx->user_ev[slot]));
+    CK(cudaEventRecord(ctx->user_ev[slot], ctx->stream));
+    return PGT_OK;
+}
+
+int pgt_event_elapsed_ms(pgt_ctx* ctx, int a, int b, float* ms)
+{
+    if (!ctx || !ms || a < 0 || a >= 16 || b < 0 || b >= 16 || !ctx->user_ev[a] || !ctx->user_ev[b])
+        return fail(ctx, PGT_ERR_ARG, "pgt_event_elapsed_ms: bad slots");
+    CK(cudaEventSynchronize(ctx->user_ev[b]));
+    CK(cudaEventElapsedTime(ms, ctx->user_ev[a], ctx->user_ev[b]));
+    return PGT_OK;
+}
+
+int pgt_host_alloc(void** ptr, uint64_t bytes)
+{
+    if (!ptr) return PGT_ERR_ARG;
+    cudaError_t e = cudaHostAlloc(ptr, bytes ? bytes : 1, cudaHostAllocDefault);
+    if (e != cudaSuccess) { g_create_error = cudaGetErrorString(e); *ptr = nullptr; return PGT_ERR_CUDA; }
+    return PGT_OK;
+}
+
+int pgt_host_free(void* ptr)
+{
+    if (ptr && cudaFreeHost(ptr) != cudaSuccess) return PGT_ERR_CUDA;
+    return PGT_OK;
+}
+
+int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
+{
+    if (!ctx || !name) return PGT_ERR_ARG;
+    if (!strcmp(name, "ik_lanes")) {
+        const int l = (int)value;
+        if (l != 8 && l != 16 && l != 32) return fail(ctx, PGT_ERR_ARG, "ik_lanes must be 8, 16 or 32");
+        ctx->ik_lanes = l;
+        return PGT_OK;
+    }
+    return fail(ctx, PGT_ERR_ARG, "unknown option %s", name);
 }
 
 static int field_info(pgt_ctx* ctx, int field_id, DevBuf** buf, int* ncomp)

@@ -810,6 +810,84 @@ cudaError_t pgt_launch_ik(const PgtIKArgs& a, int lanes, cudaStream_t st, PgtLau
 }
 
 // ------------------------------------------------------------------------------------------
+// Work counter for the roofline numerator (not on the hot path): one thread per grid point.
+//   out[0] += U(x): unique force-carrying bonds with >= 1 endpoint in the disc (both tests exact)
+//   out[1] += half-bond items the gather integrates,  out[2] += particles in the disc
+__device__ __forceinline__ bool in_disc_exact(double px, double py, double gx, double gy, const PgtBox& box, double R2)
+{
+    // at most one image can be within R < L/2: the nearest one
+    const double ddx = px - gx, ddy = py - gy;
+    const int kx = ddx > 0.5 * box.L[0] ? +1 : (ddx < -0.5 * box.L[0] ? -1 : 0);
+    const int ky = ddy > 0.5 * box.L[1] ? +1 : (ddy < -0.5 * box.L[1] ? -1 : 0);
+    const double ax = px - (gx + kx * box.L[0]), ay = py - (gy + ky * box.L[1]);
+    return !(ax * ax + ay * ay > R2);
+}
+
+__global__ void __launch_bounds__(128) k_ik_count(const PgtIKArgs A, unsigned long long* __restrict__ out)
+{
+    const long long g = A.grid.g0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long u = 0, items = 0, parts = 0;
+    if (g < A.grid.g1) {
+        double gx, gy;
+        if (A.grid.mode == 0) { gx = A.grid.xs[g / A.grid.ny]; gy = A.grid.ys[g % A.grid.ny]; }
+        else { gx = A.grid.pts[3 * g]; gy = A.grid.pts[3 * g + 1]; }
+        const PgtFrameView& fr = A.fr;
+        const double R = A.cg.rcut, R2 = A.cg.rcutsq;
+        const int ncx = A.cells.ncx, ncy = A.cells.ncy;
+        const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
+        int ux0 = max(__double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx), -ncx);
+        int ux1 = min(__double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx), 2 * ncx - 1);
+        int uy0 = max(__double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy), -ncy);
+        int uy1 = min(__double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy), 2 * ncy - 1);
+        Seg seg[3];
+        const int nseg = split_segments(ux0, ux1, ncx, seg);
+        for (int uy = uy0; uy <= uy1; ++uy) {
+            int ky = 0, row = uy;
+            if (uy < 0) { ky = +1; row += ncy; } else if (uy >= ncy) { ky = -1; row -= ncy; }
+            const double cpy = gy + ky * A.box.L[1];
+            for (int s = 0; s < nseg; ++s) {
+                const double cpx = gx + seg[s].k * A.box.L[0];
+                const int qb = fr.cell_start[row * ncx + seg[s].c0], qe = fr.cell_start[row * ncx + seg[s].c1 + 1];
+                for (int q = qb; q < qe; ++q) {
+                    const double ax = fr.sx[q] - cpx, ay = fr.sy[q] - cpy;
+                    if (ax * ax + ay * ay > R2) continue;
+                    ++parts;
+                    for (int e = fr.hb_off[q]; e < fr.hb_off[q + 1]; ++e) {
+                        ++items;
+                        const int j = fr.hb_j[e];
+                        const bool j_in = in_disc_exact(fr.sx[j], fr.sy[j], gx, gy, A.box, R2);
+                        if (!j_in || fr.sorig[q] < fr.sorig[j]) ++u;
+                    }
+                }
+            }
+        }
+    }
+    // block reduce
+    __shared__ unsigned long long red[3][4];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 16; d >= 1; d >>= 1) {
+        u += __shfl_xor_sync(FULL_MASK, u, d);
+        items += __shfl_xor_sync(FULL_MASK, items, d);
+        parts += __shfl_xor_sync(FULL_MASK, parts, d);
+    }
+    if (lane == 0) { red[0][w] = u; red[1][w] = items; red[2][w] = parts; }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        unsigned long long s = red[threadIdx.x][0] + red[threadIdx.x][1] + red[threadIdx.x][2] + red[threadIdx.x][3];
+        atomicAdd(out + threadIdx.x, s);     // integer counters: exact in any order
+    }
+}
+
+void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    const long long n = a.grid.g1 - a.grid.g0;
+    if (n <= 0) return;
+    k_ik_count<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(a, out3);
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
 // FP64 FMA peak probe: 8 independent dependent-chains per thread.
 __global__ void __launch_bounds__(256) k_fp64_probe(double* out, int iters)
 {
