@@ -152,7 +152,7 @@ struct pgt_ctx {
     cudaEvent_t user_ev[16]{};
 
     // tuning
-    int ik_lanes = 8;
+    int ik_lanes = 0;     // 0: two-phase gather; 8/16/32: group-per-point gather with that many lanes
 
     // nccl
     pgtNcclComm comm = nullptr;
@@ -285,7 +285,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocDefault);
     if (const char* env = getenv("PGT_IK_LANES")) {
         int l = atoi(env);
-        if (l == 8 || l == 16 || l == 32) ctx->ik_lanes = l;
+        if (l == 0 || l == 8 || l == 16 || l == 32) ctx->ik_lanes = l;
     }
     *out = ctx;
     return PGT_OK;
@@ -739,7 +739,7 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
     if (!ctx || !name) return PGT_ERR_ARG;
     if (!strcmp(name, "ik_lanes")) {
         const int l = (int)value;
-        if (l != 8 && l != 16 && l != 32) return fail(ctx, PGT_ERR_ARG, "ik_lanes must be 8, 16 or 32");
+        if (l != 0 && l != 8 && l != 16 && l != 32) return fail(ctx, PGT_ERR_ARG, "ik_lanes must be 0, 8, 16 or 32");
         ctx->ik_lanes = l;
         return PGT_OK;
     }

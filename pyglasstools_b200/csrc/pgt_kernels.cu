@@ -761,6 +761,301 @@ __global__ void __launch_bounds__(IK_THREADS) k_ik_gather(const PgtIKArgs A)
     }
 }
 
+// ------------------------------------------------------------------------------------------
+// Stage 4/5, second formulation ("two-phase"): the kernel above spends ~3/4 of its issue slots on
+// per-grid-point bookkeeping executed by a whole group.  Here a warp owns a patch of 32 grid points:
+//
+//  phase 1  thread <-> grid point.  Every thread walks the cell rows of ITS disc and tests its candidate
+//           particles exactly as Aboria does (dx = r_p - (x + kL), dx^2+dy^2 <= R^2); hits are appended
+//           to a per-grid-point slot list in shared memory (particle index + image code).  The loops run
+//           on warp-uniform trip counts (REDUX max), so the 32 searches cost one instruction stream.
+//  phase 2  half-warp <-> grid point, 2 grid points at a time.  Lanes take the slots of the grid point
+//           (recomputing a = r_p - c bit-identically), prefix-sum their half-bond counts, publish
+//           (2a/R^2, |a|^2/R^2) and an owner table, and then stride over the flattened half-bond list:
+//           t(s) = c0 + s (c1 + s c2), Gauss-Legendre sum of the shape, B f b(x)b into 3 registers.
+//           A 16-lane shuffle tree reduces; the owning thread adds the result to its totals.
+//  store    thread <-> grid point again: one 32-byte store per point.
+// All loop bounds in phase 2 are warp-uniform (max over the two halves) so the halves stay converged.
+#define IK2_WARPS 4
+#define IK2_THREADS (IK2_WARPS * 32)
+#define IK2_TILE_I (IK2_WARPS * 2)
+#define IK2_TILE_J 16
+#define IK2_MAXS 32            // slots buffered per grid point per pass
+#define IK2_OWNER_CAP 256      // owner-table entries per half-warp window
+
+struct IK2WarpSmem {
+    unsigned list[IK2_MAXS * 33];          // [slot][grid point], row padded to 33 words
+    double2 s_a[2][16];                    // 2 a / R^2
+    double s_c0[2][16];                    // |a|^2 / R^2
+    int s_rel[2][16];                      // first half-bond of the slot minus its queue offset
+    unsigned char owner[2][IK2_OWNER_CAP];
+};
+
+template <int KERNEL, int Q, bool LOCAL>
+__global__ void __launch_bounds__(IK2_THREADS) k_ik_gather2(const PgtIKArgs A, const int tile_i_begin)
+{
+    __shared__ IK2WarpSmem smem_all[IK2_WARPS];
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, half = lane >> 4, l16 = lane & 15;
+    const unsigned hmask = half ? 0xffff0000u : 0x0000ffffu;
+    IK2WarpSmem& sm = smem_all[warp];
+
+    const PgtFrameView& fr = A.fr;
+    const double R = A.cg.rcut, R2 = A.cg.rcutsq, iR2 = A.inv_rcutsq;
+    const double Lx = A.box.L[0], Ly = A.box.L[1];
+    const int ncx = A.cells.ncx, ncy = A.cells.ncy;
+
+    // ---- my grid point
+    bool valid;
+    long long g = 0;
+    double gx = 0.0, gy = 0.0;
+    if (A.grid.mode == 0) {
+        const int tiles_j = (A.grid.ny + IK2_TILE_J - 1) / IK2_TILE_J;
+        const int ti = tile_i_begin + blockIdx.x / tiles_j, tj = blockIdx.x % tiles_j;
+        const int i = ti * IK2_TILE_I + warp * 2 + half, j = tj * IK2_TILE_J + l16;
+        valid = i < A.grid.nx && j < A.grid.ny;
+        if (valid) {
+            g = (long long)i * A.grid.ny + j;
+            valid = g >= A.grid.g0 && g < A.grid.g1;
+            gx = __ldg(A.grid.xs + i);
+            gy = __ldg(A.grid.ys + j);
+        }
+    } else {
+        g = A.grid.g0 + (long long)blockIdx.x * IK2_THREADS + tid;
+        valid = g < A.grid.g1;
+        if (valid) { gx = __ldg(A.grid.pts + 3 * g); gy = __ldg(A.grid.pts + 3 * g + 1); }
+    }
+
+    // ---- my cell window (unwrapped cell coordinates; k = +1 left of the box, -1 right of it)
+    int uy0 = 0, nrows = 0, nseg = 0;
+    Seg seg[3];
+    if (valid) {
+        const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
+        int ux0 = __double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx);
+        int ux1 = __double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx);
+        int uy1;
+        uy0 = __double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy);
+        uy1 = __double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy);
+        ux0 = max(ux0, -ncx); ux1 = min(ux1, 2 * ncx - 1);
+        uy0 = max(uy0, -ncy); uy1 = min(uy1, 2 * ncy - 1);
+        nseg = split_segments(ux0, ux1, ncx, seg);
+        nrows = nseg > 0 ? max(0, uy1 - uy0 + 1) : 0;
+    }
+    const int nrows_w = __reduce_max_sync(FULL_MASK, nrows);
+    const int nseg_w = __reduce_max_sync(FULL_MASK, nseg);
+
+    double txx = 0.0, txy = 0.0, tyy = 0.0;                 // totals of MY grid point
+    double tkxx = 0.0, tkxy = 0.0, tkyy = 0.0, trho = 0.0;
+
+    int r = 0, s = 0;                                       // warp-uniform cursor over (row, segment)
+    bool range_loaded = false, finished = (nrows_w == 0 || nseg_w == 0);
+    int q = 0, qe = 0;                                      // my range within the current (row, segment)
+    unsigned kcode = 0;
+    double cpx = 0.0, cpy = 0.0;
+
+    while (!finished) {
+        // ================= phase 1: thread <-> grid point, collect in-disc particles =================
+        int ns = 0;
+        bool flush = false;
+        while (!flush) {
+            if (!range_loaded) {
+                if (r >= nrows_w) { finished = true; break; }
+                q = qe = 0;
+                if (r < nrows && s < nseg) {
+                    int uy = uy0 + r, ky = 0;
+                    if (uy < 0) { ky = +1; uy += ncy; }
+                    else if (uy >= ncy) { ky = -1; uy -= ncy; }
+                    Seg sg = seg[0];                         // select, not index: keeps seg[] in registers
+                    if (s == 1) sg = seg[1];
+                    if (s == 2) sg = seg[2];
+                    const int rbase = uy * ncx;
+                    q = __ldg(fr.cell_start + rbase + sg.c0);
+                    qe = __ldg(fr.cell_start + rbase + sg.c1 + 1);
+                    cpx = gx + sg.k * Lx;                    // x + k (bmax - bmin), Search.h:186-189
+                    cpy = gy + ky * Ly;
+                    kcode = ((unsigned)(sg.k + 1) << 28) | ((unsigned)(ky + 1) << 30);
+                }
+                range_loaded = true;
+            }
+            const int take = min(qe - q, IK2_MAXS - ns);
+            const int trip = __reduce_max_sync(FULL_MASK, take);
+            for (int it = 0; it < trip; ++it) {
+                if (it < take) {
+                    const int p = q + it;
+                    const double ax = __ldg(fr.sx + p) - cpx;
+                    const double ay = __ldg(fr.sy + p) - cpy;
+                    const double d2 = ax * ax + ay * ay;
+                    if (!(d2 > R2)) {
+                        sm.list[ns * 33 + lane] = (unsigned)p | kcode;
+                        ++ns;
+                    }
+                }
+            }
+            q += take;
+            if (__any_sync(FULL_MASK, q < qe)) flush = true;          // some list is full: drain first
+            else {
+                range_loaded = false;
+                if (++s >= nseg_w) { s = 0; ++r; }
+            }
+        }
+        __syncwarp();
+
+        // ================= phase 2: half-warp <-> grid point =================
+        if (__any_sync(FULL_MASK, ns > 0)) {
+            for (int pp = 0; pp < 16; ++pp) {
+                const int src = half * 16 + pp;                       // lane owning this half's grid point
+                const int ns_g = __shfl_sync(FULL_MASK, ns, src);
+                const int ns_max = __reduce_max_sync(FULL_MASK, ns_g);
+                if (ns_max == 0) continue;
+                const double gxg = __shfl_sync(FULL_MASK, gx, src), gyg = __shfl_sync(FULL_MASK, gy, src);
+                double axx = 0.0, axy = 0.0, ayy = 0.0, kxx = 0.0, kxy = 0.0, kyy = 0.0, rho = 0.0;
+
+                for (int sr = 0; sr * 16 < ns_max; ++sr) {
+                    const int slot = sr * 16 + l16;
+                    const bool have = slot < ns_g;
+                    int nb = 0, hb0 = 0;
+                    double a2x = 0.0, a2y = 0.0, c0 = 0.0;
+                    if (have) {
+                        const unsigned e = sm.list[slot * 33 + src];
+                        const int p = (int)(e & 0x0FFFFFFFu);
+                        const int kx = (int)((e >> 28) & 3u) - 1, ky = (int)(e >> 30) - 1;
+                        const double ax = __ldg(fr.sx + p) - (gxg + kx * Lx);
+                        const double ay = __ldg(fr.sy + p) - (gyg + ky * Ly);
+                        const double d2 = ax * ax + ay * ay;
+                        if (LOCAL) {
+                            const double cgval = pgt_cg_delta_exact(A.cg, d2);
+                            rho += cgval;
+                            if (fr.skxx) {
+                                kxx = fma(__ldg(fr.skxx + p), cgval, kxx);
+                                kxy = fma(__ldg(fr.skxy + p), cgval, kxy);
+                                kyy = fma(__ldg(fr.skyy + p), cgval, kyy);
+                            }
+                        }
+                        if (A.obs_mask & PGT_OBS_VIRIAL) {
+                            hb0 = __ldg(fr.hb_off + p);
+                            nb = __ldg(fr.hb_off + p + 1) - hb0;
+                        }
+                        a2x = ax * (2.0 * iR2);
+                        a2y = ay * (2.0 * iR2);
+                        c0 = d2 * iR2;
+                    }
+                    // prefix sum of the half-bond counts inside each half
+                    int tin = nb;
+#pragma unroll
+                    for (int d = 1; d < 16; d <<= 1) {
+                        const int t = __shfl_up_sync(FULL_MASK, tin, d, 16);
+                        if (l16 >= d) tin += t;
+                    }
+                    const int T_g = __shfl_sync(FULL_MASK, tin, 15, 16);
+                    const int off = tin - nb;
+                    const int T_max = __reduce_max_sync(FULL_MASK, T_g);
+                    if (T_max == 0) continue;
+                    const int nb_max = __reduce_max_sync(FULL_MASK, nb);
+                    __syncwarp();                                      // previous consumers are done with the tables
+                    sm.s_a[half][l16] = make_double2(a2x, a2y);
+                    sm.s_c0[half][l16] = c0;
+                    sm.s_rel[half][l16] = hb0 - off;
+
+                    for (int T0 = 0; T0 < T_max; T0 += IK2_OWNER_CAP) {
+                        if (T0 > 0) __syncwarp();
+                        for (int k = 0; k < nb_max; ++k) {
+                            const int idx = off + k - T0;
+                            if (k < nb && idx >= 0 && idx < IK2_OWNER_CAP) sm.owner[half][idx] = (unsigned char)l16;
+                        }
+                        __syncwarp();
+                        const int Tw_g = min(IK2_OWNER_CAP, T_g - T0), Tw_max = min(IK2_OWNER_CAP, T_max - T0);
+                        for (int t0 = 0; t0 < Tw_max; t0 += 16) {
+                            const int t = t0 + l16;
+                            if (t < Tw_g) {
+                                const int o = sm.owner[half][t];
+                                const int rec = sm.s_rel[half][o] + T0 + t;
+                                const double2 b = __ldg(fr.hb_b + rec);
+                                const double f = __ldg(fr.hb_f + rec);
+                                const double2 a2 = sm.s_a[half][o];
+                                const double c1 = fma(a2.x, b.x, a2.y * b.y);
+                                const double c2 = fma(b.x, b.x, b.y * b.y) * iR2;
+                                const double B = bond_quadrature<KERNEL, Q>(sm.s_c0[half][o], c1, c2, A.nq);
+                                const double wf = B * f;
+                                const double tx = wf * b.x, ty = wf * b.y;
+                                axx = fma(tx, b.x, axx);
+                                axy = fma(tx, b.y, axy);
+                                ayy = fma(ty, b.y, ayy);
+                            }
+                        }
+                    }
+                }
+                // 16-lane reduction; the result lands in every lane of the half, lane `src` keeps it
+#pragma unroll
+                for (int d = 8; d >= 1; d >>= 1) {
+                    axx += __shfl_xor_sync(FULL_MASK, axx, d, 16);
+                    axy += __shfl_xor_sync(FULL_MASK, axy, d, 16);
+                    ayy += __shfl_xor_sync(FULL_MASK, ayy, d, 16);
+                    if (LOCAL) {
+                        kxx += __shfl_xor_sync(FULL_MASK, kxx, d, 16);
+                        kxy += __shfl_xor_sync(FULL_MASK, kxy, d, 16);
+                        kyy += __shfl_xor_sync(FULL_MASK, kyy, d, 16);
+                        rho += __shfl_xor_sync(FULL_MASK, rho, d, 16);
+                    }
+                }
+                if (lane == src) {
+                    txx += axx; txy += axy; tyy += ayy;
+                    if (LOCAL) { tkxx += kxx; tkxy += kxy; tkyy += kyy; trho += rho; }
+                }
+            }
+        }
+        __syncwarp();
+    }
+
+    // ---- store: thread <-> grid point
+    if (valid) {
+        const long long lg = g - A.grid.g0;
+        if (A.out_virial && (A.obs_mask & PGT_OBS_VIRIAL)) {
+            const double scale = 0.5 * A.cg.norm;               // val += 0.5 * bondval * (f rij (x) rij)
+            *reinterpret_cast<double4*>(A.out_virial + 4 * lg) = make_double4(scale * txx, scale * txy, scale * txy, scale * tyy);
+        }
+        if (LOCAL && A.out_kinetic && (A.obs_mask & PGT_OBS_KINETIC))
+            *reinterpret_cast<double4*>(A.out_kinetic + 4 * lg) = make_double4(tkxx, tkxy, tkxy, tkyy);
+        if (LOCAL && A.out_density && (A.obs_mask & PGT_OBS_DENSITY)) A.out_density[lg] = trho;
+    }
+    (void)hmask;
+}
+
+template <int KERNEL, int Q>
+static cudaError_t launch_ik2_t(const PgtIKArgs& a, cudaStream_t st)
+{
+    long long blocks;
+    int tile_i_begin = 0;
+    if (a.grid.mode == 0) {
+        if (a.grid.g1 <= a.grid.g0) return cudaSuccess;
+        const int tiles_j = (a.grid.ny + IK2_TILE_J - 1) / IK2_TILE_J;
+        const int i_lo = (int)(a.grid.g0 / a.grid.ny), i_hi = (int)((a.grid.g1 - 1) / a.grid.ny);
+        tile_i_begin = i_lo / IK2_TILE_I;
+        blocks = (long long)(i_hi / IK2_TILE_I - tile_i_begin + 1) * tiles_j;
+    } else {
+        blocks = (a.grid.g1 - a.grid.g0 + IK2_THREADS - 1) / IK2_THREADS;
+    }
+    if (blocks <= 0) return cudaSuccess;
+    const bool local = (a.obs_mask & (PGT_OBS_KINETIC | PGT_OBS_DENSITY)) != 0;
+    if (local) k_ik_gather2<KERNEL, Q, true><<<(unsigned)blocks, IK2_THREADS, 0, st>>>(a, tile_i_begin);
+    else k_ik_gather2<KERNEL, Q, false><<<(unsigned)blocks, IK2_THREADS, 0, st>>>(a, tile_i_begin);
+    return cudaGetLastError();
+}
+
+template <int KERNEL>
+static cudaError_t launch_ik2_q(const PgtIKArgs& a, cudaStream_t st)
+{
+    if (a.nq == 5) return launch_ik2_t<KERNEL, 5>(a, st);
+    return launch_ik2_t<KERNEL, 0>(a, st);
+}
+
+static cudaError_t launch_ik2(const PgtIKArgs& a, cudaStream_t st)
+{
+    switch (a.cg.kernel) {
+    case PGT_CG_OCTIC: return launch_ik2_q<PGT_CG_OCTIC>(a, st);
+    case PGT_CG_RECT: return launch_ik2_q<PGT_CG_RECT>(a, st);
+    default: return launch_ik2_q<PGT_CG_MOLLIFIER>(a, st);
+    }
+}
+
 template <int KERNEL, int Q, int LANES>
 static cudaError_t launch_ik_t(const PgtIKArgs& a, cudaStream_t st)
 {
@@ -803,6 +1098,7 @@ cudaError_t pgt_launch_ik(const PgtIKArgs& a, int lanes, cudaStream_t st, PgtLau
 {
     lc->n++;
     switch (lanes) {
+    case 0: return launch_ik2(a, st);            // two-phase kernel (default)
     case 8: return launch_ik_k<8>(a, st);
     case 16: return launch_ik_k<16>(a, st);
     default: return launch_ik_k<32>(a, st);

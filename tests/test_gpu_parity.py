@@ -298,7 +298,7 @@ def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames):
     gpu_ctx.set_shard(0, G)
 
 
-@pytest.mark.parametrize("lanes", [8, 16, 32])
+@pytest.mark.parametrize("lanes", [0, 8, 16, 32])
 def test_group_width_variants(orc, fixture_frames, lanes, monkeypatch):
     monkeypatch.setenv("PGT_IK_LANES", str(lanes))
     ctx = _capi.Context(0)
