@@ -4,6 +4,7 @@
 // explicitly, so every discrete test below is the reference's ISO-C arithmetic.
 #include "pgt_kernels.cuh"
 #include <math_constants.h>
+#include <limits.h>
 
 #define FULL_MASK 0xffffffffu
 
@@ -337,12 +338,12 @@ __device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const 
     }
 }
 
-// Stage 2/3.  MODE 0: count force-carrying half-bonds; 1: fill CSR (b, f, j);
-//             MODE 2: count neighbours within max_rcut; 3: fill j only.
+// Stage 2/3.  MODE 0: count force-carrying half-bonds; 1: fill the CSR records;
+//             MODE 2: count neighbours within max_rcut; 3: fill j only (parity export).
 template <int MODEL, int MODE>
 __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
-                                               int* __restrict__ counts, double2* __restrict__ hb_b, double* __restrict__ hb_f,
-                                               int* __restrict__ hb_j)
+                                               int* __restrict__ counts, double2* __restrict__ hb_rec, double cscale,
+                                               int* __restrict__ nbr_j)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= fr.n) return;
@@ -351,16 +352,20 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
     int w = (MODE == 1 || MODE == 3) ? counts[p] : 0;
     for_each_neighbor(fr, box, cells, p, xi, yi, rc2, [&](int q, double dx, double dy, double rsq) {
         if (MODE >= 2) {
-            if (MODE == 3) hb_j[w++] = q;
+            if (MODE == 3) nbr_j[w++] = q;
             ++n;
             return;
         }
         const double dj = __ldg(fr.sd + q);
         if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
         if (MODE == 1) {
-            hb_b[w] = make_double2(dx, dy);
-            hb_f[w] = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_FDIVR);
-            hb_j[w] = q;
+            const double f = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_FDIVR);
+            const double fx = f * dx, fy = f * dy;                 // F = fdivr * rij  (ListofCommonObservables.h:58-60)
+            double2* r = hb_rec + (size_t)w * PGT_REC_STRIDE;
+            r[0] = make_double2(dx, dy);
+            r[1] = make_double2(fma(dx, dx, dy * dy) * cscale, fx * dx);
+            r[2] = make_double2(fx * dy, fy * dy);
+            r[3] = make_double2(f, __hiloint2double(0, q));
             ++w;
         }
         ++n;
@@ -370,23 +375,38 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
 
 template <int MODEL>
 static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, int* counts,
-                               double2* hb_b, double* hb_f, int* hb_j, cudaStream_t st)
+                               double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st)
 {
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
-    case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
-    case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
-    case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
-    default: k_bonds<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j); break;
+    case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
+    case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
+    case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
+    default: k_bonds<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
     }
 }
 
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
-                      double2* hb_b, double* hb_f, int* hb_j, cudaStream_t st, PgtLaunchCounter* lc)
+                      double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (fr.n <= 0) return;
     const double rc2 = max_rcut * max_rcut;   // std::pow(max_distance, 2)
-    PGT_DISPATCH_MODEL(pot.model, (launch_bonds_model<M>(mode, pot, fr, box, cells, rc2, counts, hb_b, hb_f, hb_j, st)));
+    PGT_DISPATCH_MODEL(pot.model, (launch_bonds_model<M>(mode, pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j, st)));
+    lc->n++;
+}
+
+__global__ void __launch_bounds__(256) k_rescale_bonds(double2* __restrict__ hb_rec, long long n_hb, double cscale)
+{
+    const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_hb) return;
+    const double2 b = hb_rec[e * PGT_REC_STRIDE];
+    hb_rec[e * PGT_REC_STRIDE + 1].x = fma(b.x, b.x, b.y * b.y) * cscale;
+}
+
+void pgt_launch_rescale_bonds(double2* hb_rec, long long n_hb, double cscale, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (n_hb <= 0) return;
+    k_rescale_bonds<<<(unsigned)((n_hb + 255) / 256), 256, 0, st>>>(hb_rec, n_hb, cscale);
     lc->n++;
 }
 
@@ -496,47 +516,13 @@ void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells 
 }
 
 // ------------------------------------------------------------------------------------------
-// Stage 4/5: the IK gather.
+// Stage 4/5: the IK gather.  Shared pieces first.
 //
-// A group of LANES threads owns one grid point x.  Per grid point:
-//  (1) candidate particles = the contiguous sorted ranges of the cell rows overlapping the disc's
-//      bounding box, one (row, x-segment) range per lane, flattened by a prefix sum;
-//  (2) each lane tests one candidate exactly as Aboria does for the outer search
-//      (dx = r_p - (x + kL); dx^2+dy^2 <= R^2, IrvingKirkwood.h:80-87), accumulates the local
-//      observables, and the in-disc lanes publish (2a/R^2, |a|^2/R^2, first half-bond) to shared memory;
-//  (3) the half-bonds of all in-disc particles are flattened into a work queue (prefix sum of the
-//      per-particle counts) and the lanes stride over it: per half-bond the squared distance along
-//      the bond is the quadratic  t(s) = c0 + s (c1 + s c2)  in units of R^2, the coarse-graining
-//      shape is summed at the Gauss-Legendre nodes, and  B f b(x)b  goes into three register
-//      accumulators;
-//  (4) a shuffle tree reduces the group, lane 0 stores 0.5 norm sum  (VirialStress::compute_cg).
-// No atomics anywhere; the result for a grid point is independent of how the grid is sharded.
-#define IK_THREADS 256
-#define IK_TILE_I 8
-#define IK_TILE_J 8
-#define IK_TILE (IK_TILE_I * IK_TILE_J)
-#define IK_QCAP_PER_LANE 16   // queue entries per group pass = 16 * LANES
-#define IK_MAX_RANGES 32
-
-template <int LANES>
-struct IKGroupSmem {
-    int rng_start[IK_MAX_RANGES];
-    int rng_cum[IK_MAX_RANGES + 1];
-    int rng_k[IK_MAX_RANGES];
-    double s_ax[LANES];
-    double s_ay[LANES];
-    double s_c0[LANES];
-    int s_hb0[LANES];
-    unsigned short queue[IK_QCAP_PER_LANE * LANES];
-};
-
-template <int LANES>
-__device__ __forceinline__ unsigned group_mask(int lane_in_warp)
-{
-    if constexpr (LANES >= 32) return FULL_MASK;
-    else return ((1u << LANES) - 1u) << ((lane_in_warp / LANES) * LANES);
-}
-
+// Per (grid point x, half-bond i->j with i inside the disc of x) the squared distance along the bond, in
+// units of R^2, is the quadratic  t(s) = c0 + s (c1 + s c2)  with c0 = |a|^2/R^2, c1 = 2 a.b/R^2,
+// c2 = |b|^2/R^2, a = r_i - x; the coarse-graining shape is summed at the Gauss-Legendre nodes in GSL's
+// order (FixedPointQuadrature.h:35-45) and  B S  (S = f b(x)b, precomputed per bond) goes into three
+// accumulators; 0.5 norm sum is VirialStress::compute_cg.  No global atomics anywhere.
 template <int KERNEL, int Q>
 __device__ __forceinline__ double bond_quadrature(double c0, double c1, double c2, int nq)
 {
@@ -557,208 +543,6 @@ __device__ __forceinline__ double bond_quadrature(double c0, double c1, double c
         }
     }
     return B;
-}
-
-template <int KERNEL, int Q, int LANES, bool LOCAL>
-__global__ void __launch_bounds__(IK_THREADS) k_ik_gather(const PgtIKArgs A)
-{
-    constexpr int GROUPS = IK_THREADS / LANES;
-    constexpr int IK_QCAP = IK_QCAP_PER_LANE * LANES;
-    __shared__ IKGroupSmem<LANES> smem_all[GROUPS];
-
-    const int tid = threadIdx.x;
-    const int group = tid / LANES;
-    const int lane = tid % LANES;
-    const unsigned gmask = group_mask<LANES>(tid & 31);
-    IKGroupSmem<LANES>& sm = smem_all[group];
-
-    const PgtFrameView& fr = A.fr;
-    const double R = A.cg.rcut, R2 = A.cg.rcutsq, iR2 = A.inv_rcutsq;
-    const double Lx = A.box.L[0], Ly = A.box.L[1];
-    const int ncx = A.cells.ncx, ncy = A.cells.ncy;
-
-    // tile -> grid points
-    int tile_i0 = 0, tile_j0 = 0;
-    long long tile_base = 0;
-    if (A.grid.mode == 0) {
-        const int tiles_j = (A.grid.ny + IK_TILE_J - 1) / IK_TILE_J;
-        tile_i0 = (blockIdx.x / tiles_j) * IK_TILE_I;
-        tile_j0 = (blockIdx.x % tiles_j) * IK_TILE_J;
-    } else {
-        tile_base = A.grid.g0 + (long long)blockIdx.x * IK_TILE;
-    }
-
-    for (int it = group; it < IK_TILE; it += GROUPS) {
-        long long g;
-        double gx, gy;
-        if (A.grid.mode == 0) {
-            const int i = tile_i0 + it / IK_TILE_J, j = tile_j0 + it % IK_TILE_J;
-            if (i >= A.grid.nx || j >= A.grid.ny) continue;
-            g = (long long)i * A.grid.ny + j;
-            if (g < A.grid.g0 || g >= A.grid.g1) continue;
-            gx = __ldg(A.grid.xs + i);
-            gy = __ldg(A.grid.ys + j);
-        } else {
-            g = tile_base + it;
-            if (g >= A.grid.g1) continue;
-            gx = __ldg(A.grid.pts + 3 * g);
-            gy = __ldg(A.grid.pts + 3 * g + 1);
-        }
-
-        // image centres x + kL, k = -1, 0, +1 (Search.h:186-189)
-        const double cxm = gx + (-1) * Lx, cxp = gx + (+1) * Lx;
-        const double cym = gy + (-1) * Ly, cyp = gy + (+1) * Ly;
-
-        // unwrapped cell window of the disc's bounding box (padded against rounding at cell edges)
-        const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
-        int ux0 = __double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx);
-        int ux1 = __double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx);
-        int uy0 = __double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy);
-        int uy1 = __double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy);
-        ux0 = max(ux0, -ncx); ux1 = min(ux1, 2 * ncx - 1);
-        uy0 = max(uy0, -ncy); uy1 = min(uy1, 2 * ncy - 1);
-        Seg seg[3];
-        const int nseg = split_segments(ux0, ux1, ncx, seg);
-
-        double axx = 0.0, axy = 0.0, ayy = 0.0;          // virial accumulators (un-normalised)
-        double kxx = 0.0, kxy = 0.0, kyy = 0.0, rho = 0.0;
-
-        const int rows_per_batch = (nseg > 0) ? min(IK_MAX_RANGES, LANES) / nseg : 1;
-        for (int row0 = uy0; row0 <= uy1 && nseg > 0; row0 += rows_per_batch) {
-            const int nrows = min(rows_per_batch, uy1 - row0 + 1);
-            const int nrng = nrows * nseg;
-            // (1) one range per lane, prefix-summed
-            int cnt = 0;
-            if (lane < nrng) {
-                const int row = lane / nseg, sg = lane - row * nseg;
-                int uy = row0 + row, ky = 0;
-                if (uy < 0) { ky = +1; uy += ncy; }
-                else if (uy >= ncy) { ky = -1; uy -= ncy; }
-                const int rbase = uy * ncx;
-                const int qb = __ldg(fr.cell_start + rbase + seg[sg].c0);
-                const int qe = __ldg(fr.cell_start + rbase + seg[sg].c1 + 1);
-                cnt = qe - qb;
-                sm.rng_start[lane] = qb;
-                sm.rng_k[lane] = (seg[sg].k + 1) | ((ky + 1) << 2);
-            }
-            int inc = cnt;
-#pragma unroll
-            for (int d = 1; d < LANES; d <<= 1) {
-                const int t = __shfl_up_sync(gmask, inc, d, LANES);
-                if (lane >= d) inc += t;
-            }
-            if (lane < nrng) sm.rng_cum[lane] = inc - cnt;
-            const int C = __shfl_sync(gmask, inc, LANES - 1, LANES);
-            if (lane == 0) sm.rng_cum[nrng] = C;
-            __syncwarp(gmask);
-
-            // (2) candidate rounds
-            for (int ubase = 0; ubase < C; ubase += LANES) {
-                const int u = ubase + lane;
-                bool in = false;
-                int q = 0, nb = 0, hb0 = 0;
-                double ax = 0.0, ay = 0.0, d2 = 0.0;
-                if (u < C) {
-                    int r = 0;
-#pragma unroll
-                    for (int step = IK_MAX_RANGES / 2; step >= 1; step >>= 1) {
-                        const int m = r + step;
-                        if (m < nrng && sm.rng_cum[m] <= u) r = m;
-                    }
-                    q = sm.rng_start[r] + (u - sm.rng_cum[r]);
-                    const int kk = sm.rng_k[r];
-                    const int kx = (kk & 3) - 1, ky = (kk >> 2) - 1;
-                    const double cpx = kx == 0 ? gx : (kx < 0 ? cxm : cxp);
-                    const double cpy = ky == 0 ? gy : (ky < 0 ? cym : cyp);
-                    ax = __ldg(fr.sx + q) - cpx;
-                    ay = __ldg(fr.sy + q) - cpy;
-                    d2 = ax * ax + ay * ay;
-                    in = !(d2 > R2);
-                }
-                if (LOCAL && in) {
-                    const double cgval = pgt_cg_delta_exact(A.cg, d2);
-                    rho += cgval;
-                    if (fr.skxx) {
-                        kxx = fma(__ldg(fr.skxx + q), cgval, kxx);
-                        kxy = fma(__ldg(fr.skxy + q), cgval, kxy);
-                        kyy = fma(__ldg(fr.skyy + q), cgval, kyy);
-                    }
-                }
-                if (!(A.obs_mask & PGT_OBS_VIRIAL)) continue;
-                if (in) {
-                    hb0 = __ldg(fr.hb_off + q);
-                    nb = __ldg(fr.hb_off + q + 1) - hb0;
-                    sm.s_ax[lane] = ax * (2.0 * iR2);
-                    sm.s_ay[lane] = ay * (2.0 * iR2);
-                    sm.s_c0[lane] = d2 * iR2;
-                    sm.s_hb0[lane] = hb0;
-                }
-                // (3) flatten the half-bonds of the in-disc lanes
-                int tin = nb;
-#pragma unroll
-                for (int d = 1; d < LANES; d <<= 1) {
-                    const int t = __shfl_up_sync(gmask, tin, d, LANES);
-                    if (lane >= d) tin += t;
-                }
-                const int T = __shfl_sync(gmask, tin, LANES - 1, LANES);
-                const int off = tin - nb;
-                for (int T0 = 0; T0 < T; T0 += IK_QCAP) {
-                    __syncwarp(gmask);
-                    {   // producer: lane writes (lane, k) for its own half-bonds that fall in this window
-                        const int k_lo = max(0, T0 - off), k_hi = min(nb, T0 + IK_QCAP - off);
-                        for (int k = k_lo; k < k_hi; ++k) sm.queue[off + k - T0] = (unsigned short)((k << 5) | lane);
-                    }
-                    __syncwarp(gmask);
-                    const int Tw = min(IK_QCAP, T - T0);
-                    for (int t = lane; t < Tw; t += LANES) {
-                        const unsigned e = sm.queue[t];
-                        const int o = e & 31, k = e >> 5;
-                        const int rec = sm.s_hb0[o] + k;
-                        const double2 b = __ldg(fr.hb_b + rec);
-                        const double f = __ldg(fr.hb_f + rec);
-                        const double c0 = sm.s_c0[o];
-                        const double c1 = fma(sm.s_ax[o], b.x, sm.s_ay[o] * b.y);
-                        const double c2 = fma(b.x, b.x, b.y * b.y) * iR2;
-                        const double B = bond_quadrature<KERNEL, Q>(c0, c1, c2, A.nq);
-                        const double wf = B * f;
-                        const double tx = wf * b.x, ty = wf * b.y;
-                        axx = fma(tx, b.x, axx);
-                        axy = fma(tx, b.y, axy);
-                        ayy = fma(ty, b.y, ayy);
-                    }
-                }
-                __syncwarp(gmask);
-            }
-            __syncwarp(gmask);
-        }
-
-        // (4) group reduction and store
-#pragma unroll
-        for (int d = LANES / 2; d >= 1; d >>= 1) {
-            axx += __shfl_xor_sync(gmask, axx, d, LANES);
-            axy += __shfl_xor_sync(gmask, axy, d, LANES);
-            ayy += __shfl_xor_sync(gmask, ayy, d, LANES);
-            if (LOCAL) {
-                kxx += __shfl_xor_sync(gmask, kxx, d, LANES);
-                kxy += __shfl_xor_sync(gmask, kxy, d, LANES);
-                kyy += __shfl_xor_sync(gmask, kyy, d, LANES);
-                rho += __shfl_xor_sync(gmask, rho, d, LANES);
-            }
-        }
-        if (lane == 0) {
-            const long long lg = g - A.grid.g0;
-            if (A.out_virial && (A.obs_mask & PGT_OBS_VIRIAL)) {
-                const double scale = 0.5 * A.cg.norm;       // val += 0.5 * bondval * (f rij (x) rij)
-                double4 v = make_double4(scale * axx, scale * axy, scale * axy, scale * ayy);
-                *reinterpret_cast<double4*>(A.out_virial + 4 * lg) = v;
-            }
-            if (LOCAL && A.out_kinetic && (A.obs_mask & PGT_OBS_KINETIC)) {
-                double4 v = make_double4(kxx, kxy, kxy, kyy);
-                *reinterpret_cast<double4*>(A.out_kinetic + 4 * lg) = v;
-            }
-            if (LOCAL && A.out_density && (A.obs_mask & PGT_OBS_DENSITY)) A.out_density[lg] = rho;
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -968,8 +752,8 @@ __global__ void __launch_bounds__(IK2_THREADS) k_ik_gather2(const PgtIKArgs A, c
                             if (t < Tw_g) {
                                 const int o = sm.owner[half][t];
                                 const int rec = sm.s_rel[half][o] + T0 + t;
-                                const double2 b = __ldg(fr.hb_b + rec);
-                                const double f = __ldg(fr.hb_f + rec);
+                                const double2 b = __ldg(fr.hb_rec + (size_t)rec * PGT_REC_STRIDE);
+                                const double f = __ldg(fr.hb_rec + (size_t)rec * PGT_REC_STRIDE + 3).x;
                                 const double2 a2 = sm.s_a[half][o];
                                 const double c1 = fma(a2.x, b.x, a2.y * b.y);
                                 const double c2 = fma(b.x, b.x, b.y * b.y) * iR2;
@@ -1056,53 +840,13 @@ static cudaError_t launch_ik2(const PgtIKArgs& a, cudaStream_t st)
     }
 }
 
-template <int KERNEL, int Q, int LANES>
-static cudaError_t launch_ik_t(const PgtIKArgs& a, cudaStream_t st)
-{
-    long long blocks;
-    if (a.grid.mode == 0) {
-        // only the tile rows that intersect the shard
-        const int tiles_j = (a.grid.ny + IK_TILE_J - 1) / IK_TILE_J;
-        const int tiles_i = (a.grid.nx + IK_TILE_I - 1) / IK_TILE_I;
-        blocks = (long long)tiles_i * tiles_j;
-    } else {
-        blocks = (a.grid.g1 - a.grid.g0 + IK_TILE - 1) / IK_TILE;
-    }
-    if (blocks <= 0) return cudaSuccess;
-    const bool local = (a.obs_mask & (PGT_OBS_KINETIC | PGT_OBS_DENSITY)) != 0;
-    if (local) k_ik_gather<KERNEL, Q, LANES, true><<<(unsigned)blocks, IK_THREADS, 0, st>>>(a);
-    else k_ik_gather<KERNEL, Q, LANES, false><<<(unsigned)blocks, IK_THREADS, 0, st>>>(a);
-    return cudaGetLastError();
-}
+#include "pgt_ik_pairtile.inl"
 
-template <int KERNEL, int LANES>
-static cudaError_t launch_ik_q(const PgtIKArgs& a, cudaStream_t st)
-{
-    switch (a.nq) {
-    case 5: return launch_ik_t<KERNEL, 5, LANES>(a, st);
-    default: return launch_ik_t<KERNEL, 0, LANES>(a, st);
-    }
-}
-
-template <int LANES>
-static cudaError_t launch_ik_k(const PgtIKArgs& a, cudaStream_t st)
-{
-    switch (a.cg.kernel) {
-    case PGT_CG_OCTIC: return launch_ik_q<PGT_CG_OCTIC, LANES>(a, st);
-    case PGT_CG_RECT: return launch_ik_q<PGT_CG_RECT, LANES>(a, st);
-    default: return launch_ik_q<PGT_CG_MOLLIFIER, LANES>(a, st);
-    }
-}
-
-cudaError_t pgt_launch_ik(const PgtIKArgs& a, int lanes, cudaStream_t st, PgtLaunchCounter* lc)
+cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc)
 {
     lc->n++;
-    switch (lanes) {
-    case 0: return launch_ik2(a, st);            // two-phase kernel (default)
-    case 8: return launch_ik_k<8>(a, st);
-    case 16: return launch_ik_k<16>(a, st);
-    default: return launch_ik_k<32>(a, st);
-    }
+    if (a.grid.mode == 0 && variant != 2) return launch_ik3(a, st);     // pair-tile kernel
+    return launch_ik2(a, st);                                          // two-phase kernel (point lists)
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1150,7 +894,7 @@ __global__ void __launch_bounds__(128) k_ik_count(const PgtIKArgs A, unsigned lo
                     ++parts;
                     for (int e = fr.hb_off[q]; e < fr.hb_off[q + 1]; ++e) {
                         ++items;
-                        const int j = fr.hb_j[e];
+                        const int j = pgt_rec_j(fr.hb_rec[(size_t)e * PGT_REC_STRIDE + 3]);
                         const bool j_in = in_disc_exact(fr.sx[j], fr.sy[j], gx, gy, A.box, R2);
                         if (!j_in || fr.sorig[q] < fr.sorig[j]) ++u;
                     }

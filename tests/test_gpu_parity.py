@@ -298,9 +298,10 @@ def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames):
     gpu_ctx.set_shard(0, G)
 
 
-@pytest.mark.parametrize("lanes", [0, 8, 16, 32])
-def test_group_width_variants(orc, fixture_frames, lanes, monkeypatch):
-    monkeypatch.setenv("PGT_IK_LANES", str(lanes))
+@pytest.mark.parametrize("variant", [0, 2, 3])
+def test_gather_kernel_variants(orc, fixture_frames, variant, monkeypatch):
+    """Both gather formulations (two-phase point lists, pair-tile patches) against the oracle."""
+    monkeypatch.setenv("PGT_IK_VARIANT", str(variant))
     ctx = _capi.Context(0)
     try:
         P = orc.potential("poly12")
