@@ -99,7 +99,7 @@ void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, 
                       double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
 // rewrites [1].x of every record for a new scale (the CG radius changed after the list was built)
 void pgt_launch_rescale_bonds(double2* hb_rec, long long n_hb, double cscale, cudaStream_t st, PgtLaunchCounter* lc);
-// variant 0: automatic (pair-tile kernel for cartesian grids, two-phase kernel for point lists);
+// variant 0: automatic (currently the two-phase kernel everywhere);
 // 2: two-phase kernel; 3: pair-tile kernel (cartesian grids only)
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
