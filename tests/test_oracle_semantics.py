@@ -1,0 +1,194 @@
+"""CPU tests of the oracle's loop semantics against independent restatements (no GPU needed).
+
+The oracle's cell-list path is checked against (i) its own O(N^2)/O(N G) brute-force mode, (ii) a
+numpy transcription of IrvingKirkwood::compute (IrvingKirkwood.h:74-110) written directly from the
+formula in SURVEY.md section 8 (a12), and (iii) the reference repository's only known-answer value
+(README.md:149-172, Born shear moduli over frames 0..199 of the shipped trajectory).
+"""
+import numpy as np
+import pytest
+
+
+def numpy_ik_virial(orc, P, cg_name, R, order, box, pos, diam, grid, max_rcut):
+    """Straight numpy/python transcription of a12 for small inputs: every image, every ordered pair."""
+    L = np.asarray(box[:2], np.float64)
+    pos = np.asarray(pos, np.float64)[:, :2].copy()
+    for a in range(2):                                   # Aboria wrap into [lo, hi)
+        lo, hi = -0.5 * L[a], 0.5 * L[a]
+        while (pos[:, a] < lo).any():
+            pos[pos[:, a] < lo, a] += hi - lo
+        while (pos[:, a] >= hi).any():
+            pos[pos[:, a] >= hi, a] -= hi - lo
+    diam = np.asarray(diam, np.float64)
+    x, w = orc.gl_table(order)
+    cg = orc.cgfunc(cg_name, R, order)
+    images = [np.array([kx * L[0], ky * L[1]]) for kx in (-1, 0, 1) for ky in (-1, 0, 1)]
+    out = np.zeros((len(grid), 4))
+    n = len(pos)
+    for g, gp in enumerate(np.asarray(grid, np.float64)[:, :2]):
+        for sh in images:
+            dr = pos - (gp + sh)                         # candidate - shifted centre
+            inside = dr[:, 0] ** 2 + dr[:, 1] ** 2 <= R * R
+            for i in np.nonzero(inside)[0]:
+                a_vec = dr[i]                            # r_i - x (image-resolved)
+                for sh2 in images:
+                    dj = pos - (pos[i] + sh2)
+                    near = dj[:, 0] ** 2 + dj[:, 1] ** 2 <= max_rcut * max_rcut
+                    for j in np.nonzero(near)[0]:
+                        if j == i:
+                            continue
+                        b = dj[j]                        # r_j(image) - r_i
+                        rij3 = np.array([[-b[0], -b[1], 0.0]])
+                        f = orc.pair_table(P, rij3, diam[i:i + 1], diam[j:j + 1])["fdivr"][0]
+                        if f == 0.0:
+                            continue
+                        # GSL glfixed on [0,1] of Delta(|a + s b|^2)
+                        def dl(s):
+                            v = a_vec + s * b
+                            return orc.cg_table(cg, [v[0] * v[0] + v[1] * v[1]])[0]
+                        if order % 2:
+                            acc = w[0] * dl(0.5)
+                            idx = range(1, len(x))
+                        else:
+                            acc = 0.0
+                            idx = range(len(x))
+                        for k in idx:
+                            acc += w[k] * (dl(0.5 + 0.5 * x[k]) + dl(0.5 - 0.5 * x[k]))
+                        B = 0.5 * acc
+                        out[g, 0] += 0.5 * B * f * b[0] * b[0]
+                        out[g, 1] += 0.5 * B * f * b[1] * b[0]
+                        out[g, 2] += 0.5 * B * f * b[0] * b[1]
+                        out[g, 3] += 0.5 * B * f * b[1] * b[1]
+    return out
+
+
+def small_system(seed, n=60, L=9.0):
+    rng = np.random.default_rng(seed)
+    pos = np.zeros((n, 3))
+    pos[:, :2] = rng.uniform(-0.5 * L, 0.5 * L, (n, 2))
+    pos[:4, 0] += L                                       # some unwrapped inputs
+    diam = rng.uniform(0.8, 1.4, n)
+    return np.array([L, L, 1.0]), pos, diam
+
+
+@pytest.mark.parametrize("seed,kernel,order", [(1, "octic", 5), (2, "rect", 3), (3, "mollifier", 4)])
+def test_ik_matches_numpy_transcription(orc, seed, kernel, order):
+    box, pos, diam = small_system(seed)
+    P = orc.potential("poly12")
+    S = orc.System(box, pos, diam)
+    grid = np.array([[0.0, 0.0, 0], [4.5, 4.5, 0], [-4.5, 1.0, 0], [2.2, -3.9, 0], [4.4, -4.4, 0]])
+    R = 2.0
+    want = numpy_ik_virial(orc, P, kernel, R, order, box, pos, diam, grid, S.max_rcut(P))
+    cg = orc.cgfunc(kernel, R, order)
+    got = S.ik(P, cg, grid)["virial"]
+    scale = np.abs(want).max(axis=1, keepdims=True) + 1e-300
+    assert np.all(np.abs(got - want) <= 1e-12 + 1e-12 * scale)
+    got_b = S.ik(P, cg, grid, brute=True)["virial"]
+    assert np.all(np.abs(got_b - want) <= 1e-12 + 1e-12 * scale)
+
+
+@pytest.mark.parametrize("frame", [0, 123])
+def test_cell_search_equals_brute_force_on_fixture(orc, fixture_frames, frame):
+    P = orc.potential("poly12")
+    S = orc.System(fixture_frames.box, fixture_frames.position(frame), fixture_frames.diameter)
+    a = S.neighbor_pairs(P)
+    b = S.neighbor_pairs(P, brute=True)
+    ka = sorted(zip(a[0].tolist(), a[1].tolist()))
+    kb = sorted(zip(b[0].tolist(), b[1].tolist()))
+    assert ka == kb and len(ka) > 10000
+    # ordered pairs come in (i,j)/(j,i) couples with opposite r_ij and equal flags
+    d = {(i, j): (r, f) for i, j, r, f in zip(a[0].tolist(), a[1].tolist(), a[2], a[3])}
+    for (i, j), (r, f) in list(d.items())[::97]:
+        r2, f2 = d[(j, i)]
+        assert np.array_equal(r, -r2) and f == f2
+    t1, t2 = S.thermo(P), S.thermo(P, brute=True)
+    for k in ("virial", "born"):
+        assert np.allclose(t1[k], t2[k], rtol=1e-13, atol=1e-13)
+    assert abs(t1["energy"] - t2["energy"]) <= 1e-13 * abs(t2["energy"])
+
+
+def test_readme_known_answer_born_shear_moduli(orc, fixture_frames):
+    """README.md:149-172: thermo example on frames 0..199 then check_isotropy.py prints
+    14.89655895 14.8769594875 (means over a log written with std::to_string, 6 decimals)."""
+    P = orc.potential("poly12")
+    D = 2
+    idx = lambda i, j, k, l: l + D * (k + D * (j + D * i))      # io.py:78
+    rd = lambda v: float("%f" % v)                              # ThermoProperty.h:196
+    b0101, bdiff = [], []
+    for f in range(200):
+        S = orc.System(fixture_frames.box, fixture_frames.position(f), fixture_frames.diameter)
+        r = S.thermo(P)
+        b0101.append(rd(r["born"][idx(0, 1, 0, 1)]))
+        bdiff.append(rd(r["born"][idx(0, 0, 0, 0)]) - rd(r["born"][idx(0, 0, 1, 1)]))
+    assert abs(np.mean(b0101) - 14.89655895) < 5e-9
+    assert abs(0.5 * np.mean(bdiff) - 14.8769594875) < 5e-9
+
+
+def test_half_weight_for_bonds_with_one_endpoint_in_disc(orc):
+    """a12: a bond is visited from each endpoint inside the disc -> weights 1, 1/2, 0."""
+    box = np.array([20.0, 20.0, 1.0])
+    P = orc.potential("poly12")
+    cg = orc.cgfunc("octic", 2.0, 5)
+    diam = np.array([1.0, 1.0])
+    grid = np.array([[0.0, 0.0, 0.0]])
+    both = orc.System(box, np.array([[1.0, 0.0, 0], [1.9, 0.0, 0]]), diam).ik(P, cg, grid, counts=True)
+    one = orc.System(box, np.array([[1.5, 0.0, 0], [2.4, 0.0, 0]]), diam).ik(P, cg, grid, counts=True)
+    none = orc.System(box, np.array([[2.05, -0.45, 0], [2.05, 0.45, 0]]), diam).ik(P, cg, grid, counts=True)
+    assert both["counts"][0, 0] == 2 and one["counts"][0, 0] == 1 and none["counts"][0, 0] == 0
+    assert both["virial"][0, 0] > 0 and one["virial"][0, 0] > 0 and np.all(none["virial"] == 0)
+    # weight 1/2: recompute the one-endpoint case by hand
+    b = np.array([0.9, 0.0, 0.0])
+    f = orc.pair_table(P, -b[None, :], diam[:1], diam[1:])["fdivr"][0]
+    B = orc.bond(cg, grid[0], np.array([1.5, 0.0, 0.0]), b)
+    assert abs(one["virial"][0, 0] - 0.5 * B * f * 0.81) <= 1e-14 * abs(one["virial"][0, 0])
+
+
+def test_grid_sharding_and_duplicate_rows(orc, fixture_frames):
+    """np.array_split shards (irvingkirkwood/__init__.py:53-60) give the unsharded field bit for bit; the first
+    and last grid rows/columns are periodic duplicates (np.linspace includes both ends)."""
+    P = orc.potential("poly12")
+    cg = orc.cgfunc("octic", 2.0, 5)
+    S = orc.System(fixture_frames.box, fixture_frames.position(180), fixture_frames.diameter)
+    grid, nmax = orc.cartesian_grid(float(fixture_frames.box[0]), 1.0)
+    assert nmax == 31 and len(grid) == 961
+    full = S.ik(P, cg, grid)["virial"]
+    for nshard in (2, 5):
+        parts = [S.ik(P, cg, c)["virial"] for c in np.array_split(grid, nshard)]
+        assert np.array_equal(np.vstack(parts), full)
+    f = full.reshape(nmax, nmax, 4)
+    assert np.allclose(f[0], f[-1], rtol=1e-12, atol=1e-12) and np.allclose(f[:, 0], f[:, -1], rtol=1e-12, atol=1e-12)
+
+
+def test_kinetic_modes_and_density(orc):
+    """a10: `intended` = sum m v(x)v Delta; `refbug` reproduces the reference's order-dependent product.
+    With a single particle in the disc both agree."""
+    box = np.array([12.0, 12.0, 1.0])
+    pos = np.array([[0.5, 0.2, 0.0], [5.0, 5.0, 0.0]])
+    vel = np.array([[1.0, -2.0, 0.0], [0.3, 0.1, 0.0]])
+    mass = np.array([2.0, 1.0])
+    diam = np.array([1.0, 1.0])
+    S = orc.System(box, pos, diam, vel=vel, mass=mass)
+    P = orc.potential("poly12")
+    cg = orc.cgfunc("octic", 2.0, 5)
+    grid = np.array([[0.0, 0.0, 0.0]])
+    a = S.ik(P, cg, grid, obs_mask=2 | 4, kinetic_mode=0)
+    b = S.ik(P, cg, grid, obs_mask=2 | 4, kinetic_mode=1)
+    d = orc.delta(cg, grid[0], pos[0])
+    assert np.allclose(a["kinetic"][0], np.array([2.0, -4.0, -4.0, 8.0]) * d, rtol=1e-15)
+    assert np.array_equal(a["kinetic"], b["kinetic"])
+    assert a["density"][0] == d
+
+
+def test_thermo_divides_everything_by_volume(orc):
+    """ThermoCalculator.h:58-64,89: every observable, the potential energy included, times 1/vol."""
+    box = np.array([10.0, 8.0, 1.0])
+    pos = np.array([[0.0, 0.0, 0.0], [1.0, 0.0, 0.0]])
+    diam = np.array([1.0, 1.0])
+    P = orc.potential("poly12")
+    S = orc.System(box, pos, diam)
+    assert S.vol == 80.0
+    t = S.thermo(P)
+    tab = orc.pair_table(P, np.array([[1.0, 0.0, 0.0]]), diam[:1], diam[1:])
+    assert t["npairs"] == 1
+    assert t["energy"] == tab["energy"][0] * (1 / 80.0)
+    assert t["virial"][0] == tab["fdivr"][0] * 1.0 * 1.0 * (1 / 80.0)
