@@ -8,6 +8,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+PKG = os.path.join(ROOT, "pyglasstools_b200")      # makes `import pyglasstools` resolve to the drop-in package
+if PKG not in sys.path:
+    sys.path.insert(0, PKG)
+
 GOLDEN = os.path.join(ROOT, "tests", "golden")
 
 
@@ -48,3 +52,14 @@ def gpu_ctx():
     ctx = _capi.Context(0)          # raises without a CUDA device: there is no fallback
     yield ctx
     ctx.close()
+
+
+@pytest.fixture(scope="session")
+def fixture_gsd(tmp_path_factory, fixture_frames):
+    """The shipped trajectory re-written as a GSD file by our own writer (the reference tree is absent on the GPU box)."""
+    from pyglasstools import gsdio
+    path = str(tmp_path_factory.mktemp("gsd") / "polydisperse12.gsd")
+    frames = [dict(box=fixture_frames.box, position=fixture_frames.position(f), diameter=fixture_frames.diameter)
+              for f in range(fixture_frames.nframes)]
+    gsdio.write_trajectory(path, frames)
+    return path

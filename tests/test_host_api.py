@@ -1,0 +1,291 @@
+"""CPU tests of the host layer: the reference's Python / pybind11 surface re-exposed above the C-ABI.
+
+No compute call is made here (there is no GPU and no CPU fallback); what is covered is the class surface the
+example scripts touch, the potential factories, the scalar getters (host evaluators of the same pgt_math.cuh
+the kernels use) against the golden vectors from the reference's own headers, the box / particle-system
+semantics, grid construction and sharding, the GSD reader / writer, and the text formats of the loggers.
+"""
+import os
+
+import numpy as np
+import pytest
+
+import pyglasstools as pglass
+import pyglasstools.irvingkirkwood as ik
+import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+import pyglasstools.potential as pot
+import pyglasstools.utils as utils
+from pyglasstools import _pyglasstools, gsdio
+from pyglasstools.irvingkirkwood import _irvingkirkwood
+from pyglasstools.irvingkirkwood.cgfunc import _cgfunc
+from pyglasstools.potential import _potential
+from pyglasstools.thermo import _thermo
+
+GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+REF_GSD = "/root/reference/example_scripts/polydisperse12.gsd"
+
+
+def test_reference_class_surface_is_exported():
+    """Names and constructors listed in SURVEY.md section 8(b)."""
+    for mod, names in (
+        (_pyglasstools, ["SimBox", "ParticleSystem", "Calculator", "Observable", "Manager", "Communicator", "MPILogFile"]),
+        (_potential, ["PairPotential", "PairPotentialLJ", "PairPotentialForceShiftedLJ", "PairPotentialPoly12",
+                      "PairPotentialPoly18", "PairPotentialPoly10", "PairPotentialPoly106", "PairPotentialPolyYukawa",
+                      "PairPotentialPolyLJ"]),
+        (_cgfunc, ["CoarseGrainFunction"] + ["CGFunc%s%s" % (k, m) for k in ("Octic", "Rect", "Mollifier")
+                                             for m in ("FixedPoint", "Adaptive")]),
+        (_thermo, ["ThermoCalculator"] + ["Global%s%dD" % (k, d) for k in ("PotentialEnergy", "VirialStress",
+                                                                        "ElasticVirialStress", "BornTensor", "KineticStress")
+                                          for d in (2, 3)]),
+        (_irvingkirkwood, ["IrvingKirkwood"] + ["%sField%dD" % (k, d) for k in ("VirialStress", "ElasticVirialStress",
+                                                                               "KineticStress") for d in (2, 3)]),
+    ):
+        for n in names:
+            assert hasattr(mod, n), n
+    for n in ("getMass", "setMass", "getDiameter", "setDiameter", "getDisplacement", "setDisplacement", "setAtomPosition",
+              "setAtomVelocity", "getAtomPosition", "getAtomVelocity", "moveParticles", "getNeighbors",
+              "getNeighborsDistance", "update"):
+        assert hasattr(_pyglasstools.ParticleSystem, n), n
+    for n in ("getRank", "getNRanks", "getSizeGlobal", "getRankGlobal", "getPartition", "splitPartitions", "barrier", "abort",
+              "scatter_v", "all_gather_v", "bcast", "send", "recv"):
+        assert hasattr(_pyglasstools.Communicator, n), n
+    for n in ("comm", "rank", "size", "loggers_list", "solvers_list", "set_sysdata", "get_sysdata", "update_sysdata",
+              "set_potential", "get_potential", "reset", "analyze", "set_savemode", "DelayedInterrupt"):
+        assert hasattr(pglass, n), n
+    assert pglass.rank == 0 and pglass.size == 1
+
+
+def test_simbox_semantics():
+    b = _pyglasstools.SimBox(np.array([4.0, 6.0, 9.0]), np.zeros(3), 2)
+    assert list(b.boxsize) == [4.0, 6.0, 1.0]             # third axis flattened after the bounds were set
+    assert list(b.upperbound) == [2.0, 3.0, 4.5] and list(b.lowerbound) == [-2.0, -3.0, -4.5]
+    assert list(b.periodic) == [1, 1, 0] and b.vol == 24.0 and b.dim == 2
+    c = _pyglasstools.SimBox(5.0, np.zeros(3), 3)
+    assert list(c.boxsize) == [5.0] * 3 and c.vol == 125.0 and list(c.periodic) == [1, 1, 1]
+    w = utils.simbox(Lx=4.0, Ly=6.0, Lz=9.0, ndim=2)       # the Python wrapper forces Lz = 1 first (utils.py:15-16)
+    assert list(w.upperbound) == [2.0, 3.0, 0.5] and w.dim == 2 and w.vol == 24.0
+
+
+def make_system(pos, diam=None, L=10.0, vel=None, mass=None):
+    n = len(pos)
+    box = utils.simbox(Lx=L, Ly=L, Lz=1.0, ndim=2)
+    diam = np.ones(n) if diam is None else diam
+    vel = np.zeros((n, 3)) if vel is None else vel
+    mass = np.ones(n) if mass is None else mass
+    return _pyglasstools.ParticleSystem(box.cppsimbox, n, diam, mass, pos, vel), box
+
+
+def test_particle_system_wraps_and_deletes_like_aboria():
+    pos = np.array([[5.0, 0.0, 0.0],       # x == high -> wrapped to low
+                    [-5.0, 0.0, 0.0],      # x == low stays
+                    [12.5, -17.25, 0.0],   # several box lengths away
+                    [0.0, 0.0, 0.75],      # outside the non-periodic slab -> deleted
+                    [np.nan, 0.0, 0.0],    # not finite -> deleted
+                    [1.0, 2.0, -0.5]],     # z == low stays
+                   dtype=np.float32)
+    ps, _ = make_system(pos, diam=np.arange(1, 7, dtype=np.float32))
+    got = ps.getAtomPosition()
+    assert got.shape == (4, 3) and len(ps) == 4
+    np.testing.assert_array_equal(got, [[-5.0, 0.0, 0.0], [-5.0, 0.0, 0.0], [2.5, 2.75, 0.0], [1.0, 2.0, -0.5]])
+    assert ps.getDiameter() == [1.0, 2.0, 3.0, 6.0]        # attributes follow their particle
+    with pytest.raises(ValueError):
+        ps.setMass([1.0])
+    ps.setDisplacement(np.full((4, 3), 0.25))
+    ps.moveParticles()
+    np.testing.assert_array_equal(ps.getAtomPosition()[0], [-4.75, 0.25, 0.25])
+
+
+def test_get_neighbors_periodic_inclusive():
+    pos = np.array([[4.5, 0, 0], [-4.5, 0, 0], [0, 0, 0], [3.5, 0, 0]], dtype=np.float64)
+    ps, _ = make_system(pos)
+    assert sorted(ps.getNeighbors([4.5, 0.0, 0.0], 1.0)) == [0, 1, 3]           # 1 through the seam, 3 at exactly r
+    d = ps.getNeighborsDistance(0, 1.0)
+    assert sorted(tuple(v) for v in d) == [(-1.0, 0.0, 0.0), (1.0, 0.0, 0.0)]   # r_i - r_j(image)
+
+
+def test_max_rcut_is_frozen_at_construction():
+    pos = np.random.default_rng(0).uniform(-5, 5, (16, 3)) * [1, 1, 0]
+    ps, _ = make_system(pos, diam=np.linspace(0.8, 1.6, 16))
+    p = pot.polydisperse12()
+    calc = _pyglasstools.Calculator(ps, p.cpppairpotential)
+    assert calc.max_rcut == max(1.25 * 1.6, 1.6)
+    small, _ = make_system(pos, diam=np.full(16, 0.5))
+    calc.setSystemData(small)
+    assert calc.max_rcut == max(1.25 * 1.6, 1.6)           # Calculator.h:50-53 does not refresh it
+
+
+FACTORIES = {
+    "poly12": lambda: pot.polydisperse12(), "poly18": lambda: pot.polydisperse18(), "poly10": lambda: pot.polydisperse10(),
+    "poly106": lambda: pot.polydisperse106(), "polyyukawa": lambda: pot.polydisperseyukawa(),
+    "polylj": lambda: pot.polydisperselj(), "lj": lambda: pot.lj(1.0, 0.0, 2.5, mode="truncated"),
+    "fslj": lambda: pot.lj(1.0, 0.0, 2.5, mode="force-shifted"),
+}
+
+
+@pytest.mark.parametrize("name", sorted(FACTORIES))
+def test_potential_getters_match_reference_headers_bit_for_bit(name, orc):
+    """Golden vectors were produced by the reference's own potential/*.h (tests/golden/make_refmath_vectors.py)."""
+    z = np.load(os.path.join(GOLDEN, "refmath_vectors.npz"))
+    p = FACTORIES[name]()
+    assert pglass.get_potential() is p
+    P = orc.potential(name)
+    assert p.get_scaledrcut() == P.scaled_rcut
+    np.testing.assert_array_equal(np.asarray(p.get_params()), orc.pot_params(P))
+    pre = "pair_" + name + "_"
+    rij, di, dj = z[pre + "rij"], z[pre + "di"], z[pre + "dj"]
+    step = max(1, len(rij) // 400)
+    for k in range(0, len(rij), step):
+        c = p.cpppairpotential
+        assert c.getPairEnergy(rij[k], di[k], dj[k]) == z[pre + "energy"][k]
+        assert c.getPairForceDivR(rij[k], di[k], dj[k]) == z[pre + "fdivr"][k]
+        assert c.getRcut(rij[k], di[k], dj[k]) == z[pre + "rcutsq"][k]
+        assert c.getBondStiffness(rij[k], di[k], dj[k]) == z[pre + "stiff"][k]
+
+
+def test_potential_parameter_accessors():
+    p = pot.polydisperse10(v0=2.0)
+    assert p.get_potentialname() == "polydisperse-10" and len(p.get_params()) == 6
+    assert p.get_params('v0') == 2.0 and p.get_params(1) == 0.0416667
+    p.set_params(3.0, 'v0')
+    assert p.get_params('v0') == 3.0
+    p.set_scaledrcut(1.5)
+    assert p.get_scaledrcut() == 1.5
+    with pytest.raises(NameError):
+        pot.lj(1.0, 0.2, 2.5)
+    base = _potential.PairPotential(1.0, [1.0])
+    assert base.getPairEnergy([1.0, 0, 0], 1.0, 1.0) == 0            # abstract base returns 0 everywhere
+
+
+@pytest.mark.parametrize("kernel", ["octic", "rect", "mollifier"])
+def test_cg_getters_match_reference_headers(kernel):
+    z = np.load(os.path.join(GOLDEN, "refmath_vectors.npz"))
+    f = getattr(cgfunc, kernel)(rcut=2.0, mode="fixedpoint", order=5)
+    assert f.get_rcut() == 2.0
+    d2 = z["cg_%s_R2_d2" % kernel]
+    want = z["cg_%s_R2_delta" % kernel]
+    for k in range(0, len(d2), max(1, len(d2) // 300)):
+        if abs(d2[k] - 4.0) < 1e-9:
+            continue       # sqrt-then-square may step across the cut-off; the exact edge is covered through the C-ABI tests
+        assert f.get_deltafunc([np.sqrt(d2[k]), 0.0, 0.0], [0.0, 0.0, 0.0]) == pytest.approx(want[k], rel=1e-13, abs=1e-15)
+    x, ri, rij = [0.1, -0.2, 0.0], [0.7, 0.4, 0.0], [0.9, -0.5, 0.0]
+    s = 0.3
+    assert f.get_objfunc(s, x, ri, rij) == f.get_deltafunc(x, [ri[k] + s * rij[k] for k in range(3)])
+    # GSL glfixed rule restated: 5 nodes on [0,1]
+    xs, ws = np.polynomial.legendre.leggauss(5)
+    quad = sum(0.5 * w * f.get_objfunc(0.5 + 0.5 * t, x, ri, rij) for t, w in zip(xs, ws))
+    assert f.get_bondfunc(x, ri, rij) == pytest.approx(quad, rel=1e-14)
+    a = getattr(cgfunc, kernel)(rcut=2.0, mode="adaptive", relerr=1e-8, abserr=1e-10, maxiter=100)
+    with pytest.raises(ValueError):
+        a.get_bondfunc(x, ri, rij)                                   # constructible, but QAG is not implemented
+
+
+def test_mollifier_norm_is_frozen_at_construction():
+    f = cgfunc.mollifier(rcut=2.0, mode="fixedpoint", order=3)
+    g = cgfunc.mollifier(rcut=3.0, mode="fixedpoint", order=3)
+    f.set_rcut(3.0)
+    x, r = [0.0, 0.0, 0.0], [1.0, 0.5, 0.0]
+    assert f.get_deltafunc(x, r) == pytest.approx(g.get_deltafunc(x, r) * 9.0 / 4.0, rel=1e-15)   # CGFuncMollifier.h:12,17
+
+
+def test_shard_bounds_equal_array_split():
+    for total in (0, 1, 7, 16129, 1048576):
+        for n in (1, 2, 3, 5, 8):
+            want = np.array_split(np.arange(total), n)
+            got = ik.shard_bounds(total, n)
+            assert [(int(w[0]) if len(w) else g[0], len(w)) for w, g in zip(want, got)] == [(g[0], g[1] - g[0]) for g in got]
+
+
+def reference_grid(L, dx):
+    """The reference's own construction (irvingkirkwood/__init__.py:45-53), restated for the test."""
+    nmax = int(L / dx)
+    points = np.linspace(-L / 2.0, +L / 2.0, nmax)
+    return np.asarray([[points[i], points[j], 0.0] for i in range(nmax) for j in range(nmax)], dtype=np.float64)
+
+
+def test_ikcalculator_grid_matches_reference_construction(fixture_gsd):
+    pglass.reset()
+    pot.polydisperse12()
+    utils.read_gsd(fixture_gsd, checkpointfile=None, frame_num=180)
+    calc = ik.ikcalculator(cgfunc.octic(rcut=2.0, mode="fixedpoint", order=5), dx=0.25)
+    L = float(np.float32(31.84119))
+    want = reference_grid(pglass.get_sysdata().pysimbox.boxsize[0], 0.25)
+    assert calc.gridsize == 127 * 127 and calc.coordmode == "cartesian"
+    np.testing.assert_array_equal(calc.gridpoints, want)
+    assert abs(L - pglass.get_sysdata().pysimbox.boxsize[0]) < 1e-5
+    assert pglass.solvers_list == [calc]
+    fields = ik.initialize_field(['virialstress_00', 'virialstress_11', 'kineticstress_01'], 2, calc.gridpoints)
+    assert sorted(fields) == ['kineticstress', 'virialstress']
+    assert fields['virialstress'].values().shape == (16129, 4)
+    assert fields['virialstress'].gettostring(3, 5) == "0 "
+    pglass.reset()
+
+
+def test_gsd_roundtrip_and_fallbacks(tmp_path, fixture_frames):
+    path = str(tmp_path / "t.gsd")
+    rng = np.random.default_rng(1)
+    vel = rng.normal(size=(1024, 3)).astype(np.float32)
+    frames = [dict(box=fixture_frames.box, position=fixture_frames.position(0), diameter=fixture_frames.diameter, velocity=vel),
+              dict(box=[30.0, 31.0, 1.0], position=fixture_frames.position(1))]
+    gsdio.write_trajectory(path, frames)
+    t = gsdio.open(path, "rb")
+    assert len(t) == 2
+    np.testing.assert_array_equal(t[0].particles.position, fixture_frames.position(0))
+    np.testing.assert_array_equal(t[0].particles.velocity, vel)
+    np.testing.assert_array_equal(t[1].particles.diameter, fixture_frames.diameter)     # frame-0 fall-back
+    np.testing.assert_array_equal(t[1].particles.velocity, vel)
+    np.testing.assert_array_equal(t[1].particles.mass, np.ones(1024, np.float32))       # schema default
+    assert list(t[1].configuration.box[:3]) == [30.0, 31.0, 1.0] and t[1].configuration.step == 1
+    assert t[-1].particles.N == 1024
+    with pytest.raises(IndexError):
+        t[2]
+
+
+@pytest.mark.skipif(not os.path.exists(REF_GSD), reason="reference tree not present")
+def test_gsd_reader_on_the_shipped_trajectory(fixture_frames):
+    """HOOMD-written v1 file (64-byte name slots) against the arrays extracted with the reference's vendored pygsd."""
+    t = gsdio.open(REF_GSD, "rb")
+    assert len(t) == fixture_frames.nframes
+    for f in (0, 57, 180, 200):
+        s = t[f]
+        np.testing.assert_array_equal(s.particles.position[:, :2], fixture_frames.xy[f])
+        np.testing.assert_array_equal(s.particles.diameter, fixture_frames.diameter)
+        np.testing.assert_array_equal(s.configuration.box, fixture_frames.box)
+        assert s.particles.mass.tolist() == [1.0] * 1024 and not s.particles.velocity.any()
+
+
+def test_checkpoint_resume(tmp_path, fixture_gsd):
+    pglass.reset()
+    ck = str(tmp_path / "restart.log")
+    d = utils.read_gsd(fixture_gsd, checkpointfile=ck)
+    assert d.setup_checkpoint(range(180, 200)) == range(180, 200)
+    assert open(ck).read() == "Frame 180"
+    with open(ck, "w") as f:
+        f.write("Frame 195")
+    assert d.setup_checkpoint(range(180, 200)) == [195, 196, 197, 198, 199]
+    d.update(181)
+    assert d.frame_num == 181 and len(d.cppparticledata) == 1024
+    pglass.reset()
+
+
+def test_text_formats_match_python_and_iostream():
+    rng = np.random.default_rng(3)
+    vals = np.concatenate([rng.normal(size=200) * 10.0 ** rng.integers(-12, 18, 200),
+                           [0.0, -0.0, 1.0, -15.920595169067383, 100000.0, 1e16, 1e-5, 123456789012345680.0, 5e-324,
+                            0.1, 1 / 3, 2.5e-5, 9999999999999998.0, 0.0001, 0.00009999]])
+    for v in vals:
+        assert _pyglasstools.repr_double(float(v)) == "{}".format(np.float64(v)) == repr(float(v))
+        assert _pyglasstools.ostream_double(float(v)) == "%g" % v
+
+
+def test_field_frame_formatter_equals_reference_loop():
+    pts = reference_grid(8.0, 1.0)
+    field = _irvingkirkwood.VirialStressField2D("virialstress", "2-TENSOR", False, len(pts))
+    field.addGridpoints(pts)
+    got = _pyglasstools.format_field_frame(pts, 2, [field, field, field], [0, 3, 2])
+    want = ""
+    for index in range(len(pts)):                      # io.py:112-128
+        line = "{} ".format(1) + "{} ".format(pts[index][0]) + "{} ".format(pts[index][1])
+        for comp in (0, 3, 2):
+            line += field.gettostring(comp, index)
+        want += line + "\n"
+    assert got == want

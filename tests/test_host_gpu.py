@@ -1,0 +1,184 @@
+"""GPU tests of the drop-in Python surface: the reference's example scripts (example_scripts/thermo and
+example_scripts/irvingkirkwood), statement for statement, run against the B200 path and are compared with the
+CPU oracle -- values at 1e-10 relative / 1e-12 absolute, and the text files byte for byte against the oracle's
+values pushed through the reference's formatting rules."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+RTOL, ATOL = 1e-10, 1e-12
+
+
+@pytest.fixture()
+def workdir(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    import pyglasstools as pglass
+    pglass.reset()
+    yield tmp_path
+    pglass.reset()
+
+
+def assert_close(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    err = np.abs(a - b)
+    assert (err <= ATOL + RTOL * np.abs(b)).all(), "max abs err %.3e" % err.max()
+
+
+def test_irvingkirkwood_example_script(workdir, fixture_gsd, fixture_frames, orc):
+    """example_scripts/irvingkirkwood/test-irvingkirkwood-module.py on frames 180..182."""
+    import pyglasstools as pglass
+    import pyglasstools.io as io
+    import pyglasstools.utils as utils
+    import pyglasstools.potential as pot
+    import pyglasstools.irvingkirkwood as ik
+    import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+
+    poly12 = pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)                                    # noqa: F841
+    mycgfunc = cgfunc.octic(rcut=2.0, mode="fixedpoint", order=5)
+    mysystem = utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log")             # noqa: F841
+    MyCalculator = ik.ikcalculator(cgfunc=mycgfunc, dx=0.25)
+    names = ['virialstress_00', 'virialstress_11', 'virialstress_01']
+    mylogger = io.fieldlogger(keyword="test-dump", names=names, solver=MyCalculator)
+    frames = range(180, 183)
+    pglass.analyze(frame_list=frames)
+
+    assert open("restart.log").read() == "Frame 183"
+    P, cg = orc.potential("poly12"), orc.cgfunc("octic", 2.0, 5)
+    grid = MyCalculator.gridpoints
+    assert grid.shape == (16129, 3)
+    want_text = ""
+    for f in frames:
+        S = orc.System(fixture_frames.box, fixture_frames.position(f), fixture_frames.diameter)
+        want = S.ik(P, cg, grid)["virial"]
+        if f == frames[-1]:
+            got = mylogger.field_obs['virialstress'].values()       # the holder keeps the last frame at full precision
+            assert_close(got, want)
+        want_text += "{:d} \n".format(16129) + "#Frame {:d}  \n".format(f)
+        for g in range(len(grid)):
+            want_text += "1 {} {} ".format(grid[g][0], grid[g][1])
+            want_text += "".join("%g " % want[g][c] for c in (0, 3, 2)) + "\n"      # i + Dim*j of 00, 11, 01
+    mylogger.file.flush()
+    got_lines = open("test-dump.xyz").read().split("\n")
+    want_lines = want_text.split("\n")
+    assert len(got_lines) == len(want_lines)
+    differing = [k for k, (a, b) in enumerate(zip(got_lines, want_lines)) if a != b]
+    # 6 significant digits: a 1e-15 difference can flip the last printed digit of a few values, never more
+    assert len(differing) <= 3, differing[:5]
+    for k in differing:
+        a, b = np.array(got_lines[k].split(), float), np.array(want_lines[k].split(), float)
+        np.testing.assert_allclose(a, b, rtol=2e-5, atol=1e-12)
+
+
+def test_thermo_example_script_and_readme_known_answer(workdir, fixture_gsd, fixture_frames, orc):
+    """example_scripts/thermo/test-thermo-module.py over frames 0..199, then check_isotropy.py: README.md:149-172
+    states `14.89655895 14.8769594875`."""
+    import pyglasstools as pglass
+    import pyglasstools.utils as utils
+    import pyglasstools.io as io
+    import pyglasstools.potential as pot
+    import pyglasstools.thermo as thermo
+
+    poly12 = pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)                                    # noqa: F841
+    mysystem = utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log")             # noqa: F841
+    MyCalculator = thermo.calculator()
+    names = ['borntensor_0000', 'borntensor_0011', 'borntensor_0001', 'borntensor_1111', 'borntensor_1101', 'borntensor_0101']
+    mylogger = io.logfile(filename="borntensor.log", names=names, solver=MyCalculator)
+    names = ['virialstress_00', 'virialstress_11', 'virialstress_01']
+    mylogger1 = io.logfile(filename="virialstress.log", names=names, solver=MyCalculator)
+    pglass.analyze(frame_list=range(200))
+    del mylogger, mylogger1
+
+    borntensor = np.loadtxt('borntensor.log', skiprows=1)                                      # check_isotropy.py:4-13
+    assert borntensor.shape == (200, 7)
+    shearmod1 = np.mean(borntensor[:, 6])
+    shearmod2 = 0.5 * np.mean(borntensor[:, 1] - borntensor[:, 2])
+    assert abs(shearmod1 - 14.89655895) < 5e-9 and abs(shearmod2 - 14.8769594875) < 5e-9
+
+    assert open('virialstress.log').readline() == "Frame virialstress_00 virialstress_11 virialstress_01 \n"
+    virial = np.loadtxt('virialstress.log', skiprows=1)
+    P = orc.potential("poly12")
+    for f in (0, 99, 199):
+        S = orc.System(fixture_frames.box, fixture_frames.position(f), fixture_frames.diameter)
+        w = S.thermo(P, born=True)
+        want = [w["virial"][0], w["virial"][3], w["virial"][2]]
+        assert virial[f, 0] == f
+        np.testing.assert_allclose(virial[f, 1:], want, rtol=0, atol=1.0e-6)                   # "%f" log
+    # full-precision values of the last frame straight from the holders
+    born = MyCalculator.thermocalculator
+    assert born is not None
+    S = orc.System(fixture_frames.box, fixture_frames.position(199), fixture_frames.diameter)
+    w = S.thermo(P, born=True)
+    obs = pglass.loggers_list[0].global_obs['borntensor'].values()
+    assert_close(obs, np.asarray(w["born"]).ravel())
+    assert_close(pglass.loggers_list[1].global_obs['virialstress'].values(), np.asarray(w["virial"]).ravel())
+
+
+def test_thermo_and_ik_share_one_frame_upload(workdir, fixture_gsd):
+    """Two calculators on the same ParticleSystem upload and build the cell list once per frame."""
+    import pyglasstools as pglass
+    import pyglasstools.io as io
+    import pyglasstools.utils as utils
+    import pyglasstools.potential as pot
+    import pyglasstools.thermo as thermo
+    import pyglasstools.irvingkirkwood as ik
+    import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+    from pyglasstools import _pyglasstools
+
+    pot.polydisperse12()
+    utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log", frame_num=10)
+    t = thermo.calculator()
+    io.logfile(filename="e.log", names=['potentialenergy', 'kineticstress_00'], solver=t)
+    k = ik.ikcalculator(cgfunc=cgfunc.rect(rcut=1.5, mode="fixedpoint", order=3), dx=1.0)
+    flog = io.fieldlogger(keyword="k", names=['kineticstress_00', 'virialstress_01'], solver=k)
+    t.run()
+    n0 = _pyglasstools.device_launches()
+    k.run()
+    n1 = _pyglasstools.device_launches()
+    t.run()
+    n2 = _pyglasstools.device_launches()
+    assert n2 - n1 <= 3                   # thermo again: pair-sum + final only, no re-upload / re-sort
+    assert n1 - n0 >= 3                   # IK: bonds (count, scan, fill) + gather
+    assert not flog.field_obs['kineticstress'].values().any()        # the shipped frames carry no velocities
+    assert flog.field_obs['virialstress'].values().any()
+
+
+def test_radial_calculator_point_list(workdir, fixture_gsd, fixture_frames, orc):
+    import pyglasstools as pglass
+    import pyglasstools.io as io
+    import pyglasstools.utils as utils
+    import pyglasstools.potential as pot
+    import pyglasstools.irvingkirkwood as ik
+    import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+
+    pot.polydisperse12()
+    utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log", frame_num=42)
+    calc = ik.radialcalculator(cgfunc=cgfunc.octic(rcut=2.0, mode="fixedpoint", order=5), center=np.array([1.0, -2.0, 0.0]),
+                               rmax=6, dr=0.5)
+    log = io.fieldlogger(keyword="radial", names=['virialstress_00', 'virialstress_01'], solver=calc)
+    pglass.analyze(frame_list=[42])
+    S = orc.System(fixture_frames.box, fixture_frames.position(42), fixture_frames.diameter)
+    want = S.ik(orc.potential("poly12"), orc.cgfunc("octic", 2.0, 5), calc.gridpoints)["virial"]
+    assert_close(log.field_obs['virialstress'].values(), want)
+    log.file.flush()
+    lines = open("radial.xyz").read().split("\n")
+    assert lines[0] == "{:d} ".format(calc.gridsize) and lines[1] == "#Frame 42  "
+    assert lines[2].split()[:4] == ["1", "0", "0.0", "0.0"] and len(lines) == calc.gridsize + 3
+
+
+def test_missing_device_paths_raise(workdir, fixture_gsd):
+    """Things the device path does not implement fail loudly instead of falling back."""
+    import pyglasstools.io as io
+    import pyglasstools.utils as utils
+    import pyglasstools.potential as pot
+    import pyglasstools.irvingkirkwood as ik
+    import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+
+    pot.polydisperse12()
+    utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log")
+    calc = ik.ikcalculator(cgfunc=cgfunc.octic(rcut=2.0, mode="adaptive", relerr=1e-8, abserr=1e-10, maxiter=50), dx=2.0)
+    io.fieldlogger(keyword="x", names=['virialstress_00'], solver=calc)
+    with pytest.raises(ValueError):
+        calc.run()
