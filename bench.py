@@ -192,7 +192,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from pyglasstools_b200 import _capi, synth
+    from pyglasstools_b200 import _capi, sharding, synth
 
     torch.cuda.set_device(local_rank)
     if world > 1:
@@ -235,9 +235,9 @@ def main():
     axis = synth.linspace_axis(L, nmax)
     ctx.set_grid_cartesian(axis, axis)
     if args.shard == "grid" and world > 1:
-        sizes = [len(c) for c in np.array_split(np.arange(G), world)]
-        g0 = int(sum(sizes[:rank]))
-        ctx.set_shard(g0, g0 + sizes[rank])
+        shards = sharding.grid_shards(G, world)          # np.array_split boundaries = the reference's MPI ranks
+        sizes = [e - b for b, e in shards]
+        ctx.set_shard(*shards[rank])
         g_local = sizes[rank]
     else:
         sizes = [G]
