@@ -114,7 +114,8 @@ struct pgt_ctx {
     PgtPot pot{};
     PgtCG cg{};
     int nq = 0;
-    double gl5[7] = { 0, 0, 0, 0, 0, 0, 0 };   // symmetric 5-point rule on [0,1]: h1, h1^2, h2, h2^2, w0, w1, w2
+    double gl5[7] = { 0, 0, 0, 0, 0, 0, 0 };
+    double gl_s[5] = { 0, 0, 0, 0, 0 }, gl_w[5] = { 0, 0, 0, 0, 0 };   // symmetric 5-point rule on [0,1]: h1, h1^2, h2, h2^2, w0, w1, w2
     double max_rcut = 0.0;
     double cell_side_user = 0.0;
 
@@ -132,7 +133,7 @@ struct pgt_ctx {
     long long n_hb = 0;
     DevBuf cell_of, cell_count, cell_fill, sorted_orig, scan_scratch, eflags;
     DevBuf sx, sy, sd, skxx, skxy, skyy;
-    DevBuf hb_cnt, hb_rec;
+    DevBuf hb_cnt, hb_b, hb_cf, hb_j;
     double hb_cscale = 1.0;   // scale folded into the records' |b|^2 entry (1/R^2 of the CG function, or 1)
 
     // grid
@@ -154,7 +155,7 @@ struct pgt_ctx {
     cudaEvent_t user_ev[16]{};
 
     // tuning
-    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 3: pair-tile gather
+    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather
 
     // nccl
     pgtNcclComm comm = nullptr;
@@ -229,7 +230,9 @@ PgtFrameView frame_view(const pgt_ctx* c)
     v.sorig = c->sorted_orig.as<int>();
     v.cell_start = c->cell_count.as<int>();
     v.hb_off = c->hb_cnt.as<int>();
-    v.hb_rec = c->hb_rec.as<double2>();
+    v.hb_b = c->hb_b.as<double2>();
+    v.hb_cf = c->hb_cf.as<double2>();
+    v.hb_j = c->hb_j.as<int>();
     v.hb_cscale = c->hb_cscale;
     return v;
 }
@@ -286,7 +289,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocDefault);
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
-        if (l == 0 || l == 2 || l == 3) ctx->ik_variant = l;
+        if (l == 0 || l == 2 || l == 4) ctx->ik_variant = l;
     }
     *out = ctx;
     return PGT_OK;
@@ -300,7 +303,7 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
     DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
-                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_rec, &ctx->gxs, &ctx->gys, &ctx->gpts,
+                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->gxs, &ctx->gys, &ctx->gpts,
                        &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->thermo_partials, &ctx->thermo_out,
                        &ctx->comm_scratch };
     for (DevBuf* b : bufs)
@@ -394,6 +397,8 @@ int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int o
         const double g[7] = { h1, h1 * h1, h2, h2 * h2, 0.5 * w[0], 0.5 * w[1], 0.5 * w[2] };
         for (int k = 0; k < 7; ++k) ctx->gl5[k] = g[k];
     }
+    if (ctx->nq == 5)
+        for (int k = 0; k < 5; ++k) { ctx->gl_s[k] = s[k]; ctx->gl_w[k] = ww[k]; }
     CK(pgt_upload_gl_tables(s.data(), ww.data(), ctx->nq, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));   // s/ww are stack-owned
     ctx->have_cg = true;
@@ -562,7 +567,7 @@ int pgt_build_bonds(pgt_ctx* ctx)
     ENSURE(ctx->hb_cnt, sizeof(int) * ((size_t)n + 1));
     CK(cudaMemsetAsync(ctx->hb_cnt.as<int>() + n, 0, sizeof(int), ctx->stream));
     PgtFrameView fr = frame_view(ctx);
-    pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), nullptr, 1.0, nullptr,
+    pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), PgtBondOut{}, 1.0, nullptr,
                      ctx->stream, &ctx->launches);
     pgt_launch_scan_exclusive(ctx->hb_cnt.as<int>(), ctx->hb_cnt.as<int>(), (long long)n + 1, ctx->scan_scratch.as<int>(),
                               ctx->stream, &ctx->launches);
@@ -572,11 +577,14 @@ int pgt_build_bonds(pgt_ctx* ctx)
     if (h[0] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
     ctx->n_hb = h[0];
     const size_t nb = (size_t)std::max<long long>(ctx->n_hb, 1);
-    ENSURE(ctx->hb_rec, sizeof(double2) * PGT_REC_STRIDE * nb);
+    ENSURE(ctx->hb_b, sizeof(double2) * nb);
+    ENSURE(ctx->hb_cf, sizeof(double2) * nb);
+    ENSURE(ctx->hb_j, sizeof(int) * nb);
     ctx->hb_cscale = ctx->have_cg ? 1.0 / ctx->cg.rcutsq : 1.0;
     fr = frame_view(ctx);
-    pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), ctx->hb_rec.as<double2>(),
-                     ctx->hb_cscale, nullptr, ctx->stream, &ctx->launches);
+    pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(),
+                     PgtBondOut{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>() }, ctx->hb_cscale, nullptr,
+                     ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     stage_end(ctx, PGT_STAGE_BONDS);
     ctx->bonds_built = true;
@@ -659,7 +667,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if ((obs_mask & PGT_OBS_VIRIAL) && ctx->hb_cscale != 1.0 / ctx->cg.rcutsq) {
         // the CG radius changed after the bond list was built: refresh the records' scaled |b|^2
         ctx->hb_cscale = 1.0 / ctx->cg.rcutsq;
-        pgt_launch_rescale_bonds(ctx->hb_rec.as<double2>(), ctx->n_hb, ctx->hb_cscale, ctx->stream, &ctx->launches);
+        pgt_launch_rescale_bonds(ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->n_hb, ctx->hb_cscale, ctx->stream, &ctx->launches);
     }
     PgtIKArgs a = ik_args(ctx, obs_mask);
     if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_variant, ctx->stream, &ctx->launches));
@@ -687,6 +695,7 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.nq = ctx->nq;
     a.gl5_h1 = ctx->gl5[0]; a.gl5_h1sq = ctx->gl5[1]; a.gl5_h2 = ctx->gl5[2]; a.gl5_h2sq = ctx->gl5[3];
     a.gl5_w0 = ctx->gl5[4]; a.gl5_w1 = ctx->gl5[5]; a.gl5_w2 = ctx->gl5[6];
+    for (int k = 0; k < 5; ++k) { a.gl_s[k] = ctx->gl_s[k]; a.gl_w[k] = ctx->gl_w[k]; }
     a.out_virial = ctx->out_virial.as<double>();
     a.out_kinetic = ctx->out_kinetic.as<double>();
     a.out_density = ctx->out_density.as<double>();
@@ -751,7 +760,7 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
     if (!ctx || !name) return PGT_ERR_ARG;
     if (!strcmp(name, "ik_variant")) {
         const int l = (int)value;
-        if (l != 0 && l != 2 && l != 3) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase) or 3 (pair-tile)");
+        if (l != 0 && l != 2 && l != 4) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase) or 4 (tile)");
         ctx->ik_variant = l;
         return PGT_OK;
     }
@@ -828,7 +837,7 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
     CK(cudaSetDevice(ctx->device));
     const int np = ctx->n_live;
     std::vector<int> off((size_t)np + 1), js, orig((size_t)std::max(np, 1));
-    std::vector<double2> rec;
+    std::vector<double2> rb, rcf;
     long long total = 0;
     if (bonds) {
         if (!ctx->bonds_built) return fail(ctx, PGT_ERR_STATE, "export: bonds not built");
@@ -836,14 +845,12 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
         CK(cudaMemcpy(off.data(), ctx->hb_cnt.p, sizeof(int) * ((size_t)np + 1), cudaMemcpyDeviceToHost));
         js.resize((size_t)total);
         if (total > 0 && cap >= total) {
-            rec.resize((size_t)total * PGT_REC_STRIDE);
+            rb.resize((size_t)total);
+            rcf.resize((size_t)total);
             CK(cudaStreamSynchronize(ctx->stream));
-            CK(cudaMemcpy(rec.data(), ctx->hb_rec.p, sizeof(double2) * PGT_REC_STRIDE * (size_t)total, cudaMemcpyDeviceToHost));
-            for (long long e = 0; e < total; ++e) {
-                int64_t bits;
-                memcpy(&bits, &rec[(size_t)e * PGT_REC_STRIDE + 3].y, 8);
-                js[(size_t)e] = (int)(bits & 0xffffffffLL);
-            }
+            CK(cudaMemcpy(rb.data(), ctx->hb_b.p, sizeof(double2) * (size_t)total, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(rcf.data(), ctx->hb_cf.p, sizeof(double2) * (size_t)total, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(js.data(), ctx->hb_j.p, sizeof(int) * (size_t)total, cudaMemcpyDeviceToHost));
         }
     } else {
         // neighbours within max_rcut: a private count/scan/fill pass (export only)
@@ -851,7 +858,7 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
         ENSURE(cnt, sizeof(int) * ((size_t)np + 1));
         CK(cudaMemsetAsync(cnt.as<int>() + np, 0, sizeof(int), ctx->stream));
         PgtFrameView fr = frame_view(ctx);
-        pgt_launch_bonds(2, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), nullptr, 1.0, nullptr, ctx->stream,
+        pgt_launch_bonds(2, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), PgtBondOut{}, 1.0, nullptr, ctx->stream,
                          &ctx->launches);
         pgt_launch_scan_exclusive(cnt.as<int>(), cnt.as<int>(), (long long)np + 1, ctx->scan_scratch.as<int>(), ctx->stream, &ctx->launches);
         CK(cudaStreamSynchronize(ctx->stream));
@@ -859,7 +866,7 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
         total = off[np];
         if (total > 0 && cap >= total) {
             ENSURE(jbuf, sizeof(int) * (size_t)total);
-            pgt_launch_bonds(3, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), nullptr, 1.0, jbuf.as<int>(),
+            pgt_launch_bonds(3, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, cnt.as<int>(), PgtBondOut{}, 1.0, jbuf.as<int>(),
                              ctx->stream, &ctx->launches);
             CK(cudaStreamSynchronize(ctx->stream));
             js.resize((size_t)total);
@@ -877,10 +884,10 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
             oi[e] = orig[p];
             oj[e] = orig[js[e]];
             if (bonds && rij_xy) {   // rij = -dx (IrvingKirkwood.h:101)
-                rij_xy[2 * e] = -rec[(size_t)e * PGT_REC_STRIDE].x;
-                rij_xy[2 * e + 1] = -rec[(size_t)e * PGT_REC_STRIDE].y;
+                rij_xy[2 * e] = -rb[(size_t)e].x;
+                rij_xy[2 * e + 1] = -rb[(size_t)e].y;
             }
-            if (bonds && fdivr) fdivr[e] = rec[(size_t)e * PGT_REC_STRIDE + 3].x;
+            if (bonds && fdivr) fdivr[e] = rcf[(size_t)e].y;
         }
     return PGT_OK;
 }

@@ -342,7 +342,7 @@ __device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const 
 //             MODE 2: count neighbours within max_rcut; 3: fill j only (parity export).
 template <int MODEL, int MODE>
 __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
-                                               int* __restrict__ counts, double2* __restrict__ hb_rec, double cscale,
+                                               int* __restrict__ counts, PgtBondOut out, double cscale,
                                                int* __restrict__ nbr_j)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
@@ -360,12 +360,9 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
         if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
         if (MODE == 1) {
             const double f = pgt_pair_eval_t<MODEL>(pot, rsq, di, dj, PGT_WANT_FDIVR);
-            const double fx = f * dx, fy = f * dy;                 // F = fdivr * rij  (ListofCommonObservables.h:58-60)
-            double2* r = hb_rec + (size_t)w * PGT_REC_STRIDE;
-            r[0] = make_double2(dx, dy);
-            r[1] = make_double2(fma(dx, dx, dy * dy) * cscale, fx * dx);
-            r[2] = make_double2(fx * dy, fy * dy);
-            r[3] = make_double2(f, __hiloint2double(0, q));
+            out.b[w] = make_double2(dx, dy);
+            out.cf[w] = make_double2(fma(dx, dx, dy * dy) * cscale, f);
+            out.j[w] = q;
             ++w;
         }
         ++n;
@@ -375,38 +372,40 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
 
 template <int MODEL>
 static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, int* counts,
-                               double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st)
+                               PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st)
 {
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
-    case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
-    case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
-    case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
-    default: k_bonds<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j); break;
+    case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
+    case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
+    case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
+    default: k_bonds<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
     }
 }
 
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
-                      double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc)
+                      PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (fr.n <= 0) return;
     const double rc2 = max_rcut * max_rcut;   // std::pow(max_distance, 2)
-    PGT_DISPATCH_MODEL(pot.model, (launch_bonds_model<M>(mode, pot, fr, box, cells, rc2, counts, hb_rec, cscale, nbr_j, st)));
+    PGT_DISPATCH_MODEL(pot.model, (launch_bonds_model<M>(mode, pot, fr, box, cells, rc2, counts, out, cscale, nbr_j, st)));
     lc->n++;
 }
 
-__global__ void __launch_bounds__(256) k_rescale_bonds(double2* __restrict__ hb_rec, long long n_hb, double cscale)
+__global__ void __launch_bounds__(256) k_rescale_bonds(const double2* __restrict__ hb_b, double2* __restrict__ hb_cf, long long n_hb,
+                                                       double cscale)
 {
     const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n_hb) return;
-    const double2 b = hb_rec[e * PGT_REC_STRIDE];
-    hb_rec[e * PGT_REC_STRIDE + 1].x = fma(b.x, b.x, b.y * b.y) * cscale;
+    const double2 b = hb_b[e];
+    hb_cf[e].x = fma(b.x, b.x, b.y * b.y) * cscale;
 }
 
-void pgt_launch_rescale_bonds(double2* hb_rec, long long n_hb, double cscale, cudaStream_t st, PgtLaunchCounter* lc)
+void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_hb, double cscale, cudaStream_t st,
+                              PgtLaunchCounter* lc)
 {
     if (n_hb <= 0) return;
-    k_rescale_bonds<<<(unsigned)((n_hb + 255) / 256), 256, 0, st>>>(hb_rec, n_hb, cscale);
+    k_rescale_bonds<<<(unsigned)((n_hb + 255) / 256), 256, 0, st>>>(hb_b, hb_cf, n_hb, cscale);
     lc->n++;
 }
 
@@ -752,13 +751,12 @@ __global__ void __launch_bounds__(IK2_THREADS) k_ik_gather2(const PgtIKArgs A, c
                             if (t < Tw_g) {
                                 const int o = sm.owner[half][t];
                                 const int rec = sm.s_rel[half][o] + T0 + t;
-                                const double2 b = __ldg(fr.hb_rec + (size_t)rec * PGT_REC_STRIDE);
-                                const double f = __ldg(fr.hb_rec + (size_t)rec * PGT_REC_STRIDE + 3).x;
+                                const double2 b = __ldg(fr.hb_b + rec);
+                                const double2 cf = __ldg(fr.hb_cf + rec);
                                 const double2 a2 = sm.s_a[half][o];
                                 const double c1 = fma(a2.x, b.x, a2.y * b.y);
-                                const double c2 = fma(b.x, b.x, b.y * b.y) * iR2;
-                                const double B = bond_quadrature<KERNEL, Q>(sm.s_c0[half][o], c1, c2, A.nq);
-                                const double wf = B * f;
+                                const double B = bond_quadrature<KERNEL, Q>(sm.s_c0[half][o], c1, cf.x, A.nq);
+                                const double wf = B * cf.y;
                                 const double tx = wf * b.x, ty = wf * b.y;
                                 axx = fma(tx, b.x, axx);
                                 axy = fma(tx, b.y, axy);
@@ -840,14 +838,15 @@ static cudaError_t launch_ik2(const PgtIKArgs& a, cudaStream_t st)
     }
 }
 
-#include "pgt_ik_pairtile.inl"
+#include "pgt_ik_tile.inl"
 
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc)
 {
     lc->n++;
-    // measured on B200 (cfg3, 1024^2): two-phase 0.555 ms, pair-tile 0.728 ms -> automatic = two-phase
-    if (a.grid.mode == 0 && variant == 3) return launch_ik3(a, st);     // pair-tile kernel (cartesian grids only)
-    return launch_ik2(a, st);                                          // two-phase kernel
+    // measured on B200 (cfg5, 2048^2): two-phase 1.85 ms, tile 3.5 ms (its integer bookkeeping -- staging, bitmap walks --
+    // outweighs the 1.5x fewer quadratures) -> automatic = two-phase; the tile kernel stays selectable (variant 4)
+    if (variant == 4 && ik_tile_applicable(a)) return launch_ik_tile(a, st);   // Cartesian grids, virial field only
+    return launch_ik2(a, st);                                                  // two-phase kernel (any point list, local fields)
 }
 
 // ------------------------------------------------------------------------------------------
@@ -895,7 +894,7 @@ __global__ void __launch_bounds__(128) k_ik_count(const PgtIKArgs A, unsigned lo
                     ++parts;
                     for (int e = fr.hb_off[q]; e < fr.hb_off[q + 1]; ++e) {
                         ++items;
-                        const int j = pgt_rec_j(fr.hb_rec[(size_t)e * PGT_REC_STRIDE + 3]);
+                        const int j = fr.hb_j[e];
                         const bool j_in = in_disc_exact(fr.sx[j], fr.sy[j], gx, gy, A.box, R2);
                         if (!j_in || fr.sorig[q] < fr.sorig[j]) ++u;
                     }

@@ -3,7 +3,7 @@
 // Stage map (BASELINE.json north_star):
 //   0/1  k_wrap_count, scan, k_scatter_ids, k_cell_sort, k_gather_sorted   (cell list, counting sort)
 //   2/3  k_bonds<MODEL, COUNT|FILL>                                        (pair force + compacted half-bonds)
-//   4/5  k_ik_gather3<KERNEL, Q, LOCAL> (pair-tile), k_ik_gather2 (point lists)   (IK field gather + local observables)
+//   4/5  k_ik_tile<KERNEL, Q> (Cartesian grids), k_ik_gather2 (point lists, local observables)   (IK field gather)
 //   6    k_thermo_pairs<MODEL>, k_thermo_final                             (global virial / energy / Born / kinetic)
 // All arithmetic is FP64; no tensor cores (there is no dense contraction on this path).
 #pragma once
@@ -40,16 +40,19 @@ struct PgtFrameView {
     const int* sorig;            // original particle index
     const int* cell_start;       // ncx*ncy + 1
     const int* hb_off;           // n + 1  : half-bond CSR offsets
-    // One 64-byte record (4 x double2) per half-bond i -> j, everything the gather needs per bond
-    // precomputed once instead of once per (grid point, bond):
-    //   [0] b = r_j(image) - r_i            [1] (|b|^2 * cscale, S_xx)
-    //   [2] (S_xy, S_yy),  S = f b (x) b     [3] (f = -phi'(r)/r, sorted index of j in the low word)
-    const double2* hb_rec;
-    double hb_cscale;            // scale folded into [1].x: 1/R^2 of the CG function the list was built for
+    // Half-bond i -> j records, structure of arrays (36 B per half-bond), everything the gather needs per
+    // bond computed once instead of once per (grid point, bond):
+    const double2* hb_b;         // b = r_j(image) - r_i, exactly as the reference's inner search forms it
+    const double2* hb_cf;        // (|b|^2 * cscale,  f = -phi'(r)/r)
+    const int* hb_j;             // sorted index of j
+    double hb_cscale;            // scale folded into hb_cf.x: 1/R^2 of the CG function the list was built for
 };
 
-#define PGT_REC_STRIDE 4         // double2 per half-bond record
-__device__ __forceinline__ int pgt_rec_j(const double2& r3) { return __double2loint(r3.y); }
+struct PgtBondOut {              // destination of k_bonds<.,FILL>
+    double2* b;
+    double2* cf;
+    int* j;
+};
 
 struct PgtGridView {
     int mode;                    // 0 cartesian, 1 point list
@@ -70,6 +73,7 @@ struct PgtIKArgs {
     int nq;                      // quadrature nodes (generic path)
     // 5-point rule in symmetric form on [0,1]: nodes 0.5 +- h_k, weights w_k (already times (b-a)/2)
     double gl5_h1, gl5_h1sq, gl5_h2, gl5_h2sq, gl5_w0, gl5_w1, gl5_w2;
+    double gl_s[5], gl_w[5];     // the 5-point rule in GSL's visiting order (valid when nq == 5), for constant-bank operands
     double* out_virial;          // (g1-g0) x 4
     double* out_kinetic;         // (g1-g0) x 4
     double* out_density;         // (g1-g0)
@@ -96,11 +100,12 @@ void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mas
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
 // mode 2/3: same for plain neighbours within max_rcut (export only).
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
-                      double2* hb_rec, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
-// rewrites [1].x of every record for a new scale (the CG radius changed after the list was built)
-void pgt_launch_rescale_bonds(double2* hb_rec, long long n_hb, double cscale, cudaStream_t st, PgtLaunchCounter* lc);
-// variant 0: automatic (currently the two-phase kernel everywhere);
-// 2: two-phase kernel; 3: pair-tile kernel (cartesian grids only)
+                      PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
+// rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)
+void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_hb, double cscale, cudaStream_t st,
+                              PgtLaunchCounter* lc);
+// variant 0: automatic (= two-phase, measured faster); 2: two-phase kernel;
+// 4: tile kernel (Cartesian grids + virial only, else two-phase)
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
                        double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);

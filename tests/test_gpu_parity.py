@@ -273,8 +273,11 @@ def test_empty_and_tiny_inputs(gpu_ctx, orc):
     assert np.all(gpu_ctx.ik_download() == 0)
 
 
-def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames):
-    """np.array_split shards (irvingkirkwood/__init__.py:53-60) reproduce the unsharded field bit for bit."""
+@pytest.mark.parametrize("variant", [2, 4])
+def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames, variant):
+    """np.array_split shards (irvingkirkwood/__init__.py:53-60) reproduce the unsharded field bit for bit,
+    with either gather kernel."""
+    gpu_ctx.set_option("ik_variant", variant)
     P = orc.potential("poly12")
     pos, diam, box = fixture_frames.position(185), fixture_frames.diameter, fixture_frames.box
     setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
@@ -296,11 +299,12 @@ def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames):
             g0 += s
         assert np.array_equal(np.vstack(parts), full)
     gpu_ctx.set_shard(0, G)
+    gpu_ctx.set_option("ik_variant", 0)
 
 
-@pytest.mark.parametrize("variant", [0, 2, 3])
+@pytest.mark.parametrize("variant", [0, 2, 4])
 def test_gather_kernel_variants(orc, fixture_frames, variant, monkeypatch):
-    """Both gather formulations (two-phase point lists, pair-tile patches) against the oracle."""
+    """Both gather formulations (two-phase point lists, shared-memory tiles) against the oracle."""
     monkeypatch.setenv("PGT_IK_VARIANT", str(variant))
     ctx = _capi.Context(0)
     try:
