@@ -103,6 +103,12 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask);
 /* Copies a field of the local shard to host: (g1-g0) x Dim*Dim doubles, col-major per point
  * (index a + Dim*b, CoarseGrainedField.h:160-183), or (g1-g0) doubles for the density.         */
 int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out);
+/* Same copy, enqueued on the ctx stream without waiting: `out` (page-locked, see pgt_host_alloc) is valid after
+ * pgt_synchronize(ctx).  With two contexts used alternately, frame k+1's upload and compute overlap frame k's
+ * read-back (PCIe is full duplex) -- the trajectory loop of pyglasstools.analyze, double-buffered.              */
+int pgt_ik_download_async(pgt_ctx* ctx, int field_id, double* out);
+/* Waits for the read-backs enqueued by pgt_ik_download_async only (not for kernels of later frames).        */
+int pgt_ik_download_wait(pgt_ctx* ctx);
 /* Device pointer of a field of the local shard (for NCCL / zero-copy consumers).               */
 int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubles);
 /* Stage 6.  Replaces ThermoCalculator::compute + divideByVolume (thermo/ThermoCalculator.h:58-90).

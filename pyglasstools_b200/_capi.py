@@ -22,7 +22,7 @@ EXPORTED = [
     "pgt_ctx_create", "pgt_ctx_destroy", "pgt_last_error", "pgt_device_count", "pgt_synchronize", "pgt_stream",
     "pgt_potential_set", "pgt_cg_set", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
     "pgt_frame_set_device", "pgt_build_cells", "pgt_build_bonds", "pgt_frame_counts", "pgt_grid_set_cartesian",
-    "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_device_ptr",
+    "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_download_async", "pgt_ik_download_wait", "pgt_ik_device_ptr",
     "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
     "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
@@ -205,6 +205,14 @@ class Context:
             out = np.empty(shape, np.float64)
         self._ck(lib().pgt_ik_download(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
         return out
+
+    def ik_download_async(self, field, out):
+        """Enqueues the read-back into the page-locked array `out`; valid after sync()."""
+        self._ck(lib().pgt_ik_download_async(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def ik_download_wait(self):
+        self._ck(lib().pgt_ik_download_wait(self._h))
 
     def ik_device_ptr(self, field=FIELD_VIRIAL):
         p, n = C.c_void_p(), C.c_int64()

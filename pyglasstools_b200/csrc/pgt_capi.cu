@@ -106,6 +106,10 @@ void gauss_legendre_half(int n, std::vector<double>& x, std::vector<double>& w)
 struct pgt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t dl_stream = nullptr;      // read-backs issued by pgt_ik_download_async (overlap the next upload)
+    cudaEvent_t ev_field_ready = nullptr;  // main stream: the field of the last gather is complete
+    cudaEvent_t ev_dl_done = nullptr;      // dl_stream: the last asynchronous read-back is complete
+    bool dl_pending = false;
     std::string err;
     PgtLaunchCounter launches{ 0 };
 
@@ -146,7 +150,8 @@ struct pgt_ctx {
     DevBuf out_virial, out_kinetic, out_density;
     unsigned last_ik_mask = 0;
     DevBuf thermo_partials, thermo_out;
-    double* h_small = nullptr;   // pinned scratch for small read-backs
+    double* h_small = nullptr;   // mapped page-locked scratch for small read-backs (written by k_publish)
+    void* d_small = nullptr;     // its device alias
 
     // timing
     cudaEvent_t ev0[PGT_STAGE_COUNT]{}, ev1[PGT_STAGE_COUNT]{};
@@ -282,11 +287,15 @@ int pgt_ctx_create(int device, pgt_ctx** out)
         delete ctx;
         return PGT_ERR_CUDA;
     }
+    cudaStreamCreateWithFlags(&ctx->dl_stream, cudaStreamNonBlocking);
+    cudaEventCreateWithFlags(&ctx->ev_field_ready, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&ctx->ev_dl_done, cudaEventDisableTiming);
     for (int s = 0; s < PGT_STAGE_COUNT; ++s) {
         cudaEventCreate(&ctx->ev0[s]);
         cudaEventCreate(&ctx->ev1[s]);
     }
-    cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocDefault);
+    cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocMapped);
+    cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0);
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
         if (l == 0 || l == 2 || l == 4) ctx->ik_variant = l;
@@ -315,6 +324,9 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     if (ctx->h_small) cudaFreeHost(ctx->h_small);
     for (auto& e : ctx->user_ev)
         if (e) cudaEventDestroy(e);
+    if (ctx->ev_field_ready) cudaEventDestroy(ctx->ev_field_ready);
+    if (ctx->ev_dl_done) cudaEventDestroy(ctx->ev_dl_done);
+    if (ctx->dl_stream) cudaStreamDestroy(ctx->dl_stream);
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PGT_OK;
@@ -326,6 +338,10 @@ int pgt_synchronize(pgt_ctx* ctx)
 {
     if (!ctx) return PGT_ERR_ARG;
     CK(cudaStreamSynchronize(ctx->stream));
+    if (ctx->dl_pending) {
+        CK(cudaStreamSynchronize(ctx->dl_stream));
+        ctx->dl_pending = false;
+    }
     return PGT_OK;
 }
 
@@ -528,8 +544,7 @@ int pgt_build_cells(pgt_ctx* ctx)
 
     // live count and error flags (two ints) back to the host
     int* h = reinterpret_cast<int*>(ctx->h_small);
-    CK(cudaMemcpyAsync(h, ctx->cell_count.as<int>() + ncells, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(h + 1, ctx->eflags.p, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    pgt_launch_publish(ctx->cell_count.as<int>() + ncells, 1, ctx->eflags.p, 1, ctx->d_small, ctx->stream, &ctx->launches);
     CK(cudaStreamSynchronize(ctx->stream));
     ctx->n_live = h[0];
     int rc = check_eflags(ctx, h[1]);
@@ -572,7 +587,7 @@ int pgt_build_bonds(pgt_ctx* ctx)
     pgt_launch_scan_exclusive(ctx->hb_cnt.as<int>(), ctx->hb_cnt.as<int>(), (long long)n + 1, ctx->scan_scratch.as<int>(),
                               ctx->stream, &ctx->launches);
     int* h = reinterpret_cast<int*>(ctx->h_small);
-    CK(cudaMemcpyAsync(h, ctx->hb_cnt.as<int>() + n, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    pgt_launch_publish(ctx->hb_cnt.as<int>() + n, 1, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
     CK(cudaStreamSynchronize(ctx->stream));
     if (h[0] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
     ctx->n_hb = h[0];
@@ -663,6 +678,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 4 * n);
     if (obs_mask & PGT_OBS_DENSITY) ENSURE(ctx->out_density, sizeof(double) * n);
 
+    if (ctx->dl_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_dl_done, 0));   // the field buffers are still being read back
     stage_begin(ctx, PGT_STAGE_IK);
     if ((obs_mask & PGT_OBS_VIRIAL) && ctx->hb_cscale != 1.0 / ctx->cg.rcutsq) {
         // the CG radius changed after the bond list was built: refresh the records' scaled |b|^2
@@ -777,7 +793,11 @@ static int field_info(pgt_ctx* ctx, int field_id, DevBuf** buf, int* ncomp)
     return -2;
 }
 
-int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out)
+static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait);
+int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out) { return ik_download_impl(ctx, field_id, out, true); }
+int pgt_ik_download_async(pgt_ctx* ctx, int field_id, double* out) { return ik_download_impl(ctx, field_id, out, false); }
+
+static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
 {
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_ik_download: null argument");
     DevBuf* b;
@@ -787,10 +807,30 @@ int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out)
     if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
     CK(cudaSetDevice(ctx->device));
     const long long gl = ctx->g1 - ctx->g0;
-    stage_begin(ctx, PGT_STAGE_DOWNLOAD);
-    if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->stream));
-    stage_end(ctx, PGT_STAGE_DOWNLOAD);
-    CK(cudaStreamSynchronize(ctx->stream));
+    if (wait) {
+        stage_begin(ctx, PGT_STAGE_DOWNLOAD);
+        if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->stream));
+        stage_end(ctx, PGT_STAGE_DOWNLOAD);
+        CK(cudaStreamSynchronize(ctx->stream));
+        return PGT_OK;
+    }
+    // asynchronous: the copy runs on its own stream behind the gather, so that the next frame's upload and
+    // stages (main stream) are not queued behind it
+    CK(cudaEventRecord(ctx->ev_field_ready, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_field_ready, 0));
+    if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
+    CK(cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
+    ctx->dl_pending = true;
+    return PGT_OK;
+}
+
+int pgt_ik_download_wait(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (ctx->dl_pending) {
+        CK(cudaStreamSynchronize(ctx->dl_stream));
+        ctx->dl_pending = false;
+    }
     return PGT_OK;
 }
 
@@ -821,7 +861,7 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
                       ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     stage_end(ctx, PGT_STAGE_THERMO);
-    CK(cudaMemcpyAsync(ctx->h_small, ctx->thermo_out.p, sizeof(double) * 25, cudaMemcpyDeviceToHost, ctx->stream));
+    pgt_launch_publish(ctx->thermo_out.p, 50, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
     CK(cudaStreamSynchronize(ctx->stream));
     const double* h = ctx->h_small;
     // device order: virial 4 | kinetic 4 | energy | born 16  ->  API order (same, documented in the header)

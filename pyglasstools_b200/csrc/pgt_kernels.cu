@@ -928,6 +928,23 @@ void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStrea
 }
 
 // ------------------------------------------------------------------------------------------
+// Small results (counts, flags, the 25 thermo sums) reach the host through MAPPED page-locked memory written by
+// this kernel, not through a device-to-host memcpy: a memcpy would queue in the copy engine behind a field
+// read-back of another frame (134 MB at cfg5) and stall the stage that waits for it.
+__global__ void k_publish(const void* __restrict__ s0, int n0, const void* __restrict__ s1, int n1, int* __restrict__ dst)
+{
+    const int t = threadIdx.x;
+    if (t < n0) dst[t] = static_cast<const int*>(s0)[t];
+    else if (t < n0 + n1) dst[t] = static_cast<const int*>(s1)[t - n0];
+}
+
+void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    k_publish<<<1, 64, 0, st>>>(s0, nwords0, s1, nwords1, static_cast<int*>(dst_mapped));
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
 // FP64 FMA peak probe: 8 independent dependent-chains per thread.
 __global__ void __launch_bounds__(256) k_fp64_probe(double* out, int iters)
 {

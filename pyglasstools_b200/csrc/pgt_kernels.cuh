@@ -111,4 +111,6 @@ void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells 
                        double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
 int pgt_thermo_blocks(int n);
 void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStream_t st, PgtLaunchCounter* lc);
+// copies nwords0 + nwords1 (<= 64) 32-bit words to mapped host memory
+void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_fp64_probe(double* out, int iters, int blocks, int threads, cudaStream_t st, PgtLaunchCounter* lc);
