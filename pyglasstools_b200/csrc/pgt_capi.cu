@@ -137,7 +137,8 @@ struct pgt_ctx {
     long long n_hb = 0;
     DevBuf cell_of, cell_count, cell_fill, sorted_orig, scan_scratch, eflags;
     DevBuf sx, sy, sd, skxx, skxy, skyy;
-    DevBuf hb_cnt, hb_b, hb_cf, hb_j;
+    DevBuf hb_cnt, hb_b, hb_cf, hb_j, nb_list;
+    bool bond_single_search = true;   // option "bond_single_search"
     double hb_cscale = 1.0;   // scale folded into the records' |b|^2 entry (1/R^2 of the CG function, or 1)
 
     // grid
@@ -312,7 +313,7 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
     DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
-                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->gxs, &ctx->gys, &ctx->gpts,
+                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->nb_list, &ctx->gxs, &ctx->gys, &ctx->gpts,
                        &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->thermo_partials, &ctx->thermo_out,
                        &ctx->comm_scratch };
     for (DevBuf* b : bufs)
@@ -582,14 +583,28 @@ int pgt_build_bonds(pgt_ctx* ctx)
     ENSURE(ctx->hb_cnt, sizeof(int) * ((size_t)n + 1));
     CK(cudaMemsetAsync(ctx->hb_cnt.as<int>() + n, 0, sizeof(int), ctx->stream));
     PgtFrameView fr = frame_view(ctx);
-    pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), PgtBondOut{}, 1.0, nullptr,
-                     ctx->stream, &ctx->launches);
+    int* h = reinterpret_cast<int*>(ctx->h_small);
+    // single search: count and keep the neighbours; a particle with more than PGT_NB_SLOTS bonds sends the frame
+    // down the two-search path below
+    bool listed = ctx->bond_single_search && n > 0 && n < (1 << 28);
+    if (listed) {
+        ENSURE(ctx->nb_list, sizeof(unsigned) * PGT_NB_SLOTS * (size_t)n);
+        CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
+        pgt_launch_bonds(4, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(),
+                         PgtBondOut{ nullptr, nullptr, ctx->eflags.as<int>() }, 1.0, ctx->nb_list.as<int>(), ctx->stream, &ctx->launches);
+    } else {
+        pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), PgtBondOut{}, 1.0, nullptr,
+                         ctx->stream, &ctx->launches);
+    }
     pgt_launch_scan_exclusive(ctx->hb_cnt.as<int>(), ctx->hb_cnt.as<int>(), (long long)n + 1, ctx->scan_scratch.as<int>(),
                               ctx->stream, &ctx->launches);
-    int* h = reinterpret_cast<int*>(ctx->h_small);
-    pgt_launch_publish(ctx->hb_cnt.as<int>() + n, 1, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
+    pgt_launch_publish(ctx->hb_cnt.as<int>() + n, 1, ctx->eflags.p, 1, ctx->d_small, ctx->stream, &ctx->launches);
     CK(cudaStreamSynchronize(ctx->stream));
     if (h[0] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
+    if (listed && (h[1] & PGT_EFLAG_BOND_OVERFLOW)) {
+        // the counts are right, the kept lists are truncated: fill by a second search
+        listed = false;
+    }
     ctx->n_hb = h[0];
     const size_t nb = (size_t)std::max<long long>(ctx->n_hb, 1);
     ENSURE(ctx->hb_b, sizeof(double2) * nb);
@@ -597,9 +612,13 @@ int pgt_build_bonds(pgt_ctx* ctx)
     ENSURE(ctx->hb_j, sizeof(int) * nb);
     ctx->hb_cscale = ctx->have_cg ? 1.0 / ctx->cg.rcutsq : 1.0;
     fr = frame_view(ctx);
-    pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(),
-                     PgtBondOut{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>() }, ctx->hb_cscale, nullptr,
-                     ctx->stream, &ctx->launches);
+    const PgtBondOut out{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>() };
+    if (listed)
+        pgt_launch_bonds(5, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale,
+                         ctx->nb_list.as<int>(), ctx->stream, &ctx->launches);
+    else
+        pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale, nullptr,
+                         ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     stage_end(ctx, PGT_STAGE_BONDS);
     ctx->bonds_built = true;
@@ -778,6 +797,11 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
         const int l = (int)value;
         if (l != 0 && l != 2 && l != 4) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase) or 4 (tile)");
         ctx->ik_variant = l;
+        return PGT_OK;
+    }
+    if (!strcmp(name, "bond_single_search")) {
+        ctx->bond_single_search = value != 0.0;
+        ctx->bonds_built = false;
         return PGT_OK;
     }
     return fail(ctx, PGT_ERR_ARG, "unknown option %s", name);

@@ -309,9 +309,10 @@ __device__ __forceinline__ int split_segments(int u0, int u1, int nc, Seg seg[3]
     return n;
 }
 
+// visit(q, dx, dy, accum, code): code = (kx + 1) | (ky + 1) << 2 names the periodic image the hit was found under
 template <class F>
-__device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, int p,
-                                                  double xi, double yi, double rc2, F&& visit)
+__device__ __forceinline__ void for_each_neighbor_img(const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, int p,
+                                                      double xi, double yi, double rc2, F&& visit)
 {
     const int cx = cell_coord(xi, box.lo[0], cells.inv_cwx, cells.ncx);
     const int cy = cell_coord(yi, box.lo[1], cells.inv_cwy, cells.ncy);
@@ -332,10 +333,17 @@ __device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const 
                 const double dx = __ldg(fr.sx + q) - cpx;
                 const double dy = __ldg(fr.sy + q) - cpy;
                 const double accum = dx * dx + dy * dy;
-                if (!(accum > rc2)) visit(q, dx, dy, accum);
+                if (!(accum > rc2)) visit(q, dx, dy, accum, (unsigned)(seg[s].k + 1) | ((unsigned)(ky + 1) << 2));
             }
         }
     }
+}
+
+template <class F>
+__device__ __forceinline__ void for_each_neighbor(const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, int p,
+                                                  double xi, double yi, double rc2, F&& visit)
+{
+    for_each_neighbor_img(fr, box, cells, p, xi, yi, rc2, [&](int q, double dx, double dy, double accum, unsigned) { visit(q, dx, dy, accum); });
 }
 
 // Stage 2/3.  MODE 0: count force-carrying half-bonds; 1: fill the CSR records;
@@ -370,12 +378,59 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
     if (MODE == 0 || MODE == 2) counts[p] = n;
 }
 
+// Stage 2/3, single search: k_bonds_find keeps the force-carrying neighbours of every particle (index + image code,
+// in the search's visiting order) in a [slot][particle] scratch list and counts them; after the scan
+// k_bonds_fill_list re-forms dx exactly as the search did (same operands, same operations -> same bits) and writes
+// the records.  Halves the neighbour searches of the count + fill pair above, which stays as the path for frames
+// where some particle has more than PGT_NB_SLOTS bonds.
+template <int MODEL>
+__global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
+                                                    int* __restrict__ counts, unsigned* __restrict__ nb_list, int* __restrict__ eflags)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= fr.n) return;
+    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+    int n = 0;
+    for_each_neighbor_img(fr, box, cells, p, xi, yi, rc2, [&](int q, double, double, double rsq, unsigned code) {
+        const double dj = __ldg(fr.sd + q);
+        if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
+        if (n < PGT_NB_SLOTS) nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
+        ++n;
+    });
+    counts[p] = n;
+    if (n > PGT_NB_SLOTS) atomicOr(eflags, PGT_EFLAG_BOND_OVERFLOW);
+}
+
+template <int MODEL>
+__global__ void __launch_bounds__(128) k_bonds_fill_list(PgtPot pot, PgtFrameView fr, PgtBox box, const int* __restrict__ hb_off,
+                                                         const unsigned* __restrict__ nb_list, PgtBondOut out, double cscale)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= fr.n) return;
+    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+    const int w0 = hb_off[p], n = hb_off[p + 1] - w0;
+    for (int k = 0; k < n; ++k) {
+        const unsigned e = __ldg(nb_list + (size_t)k * fr.n + p);
+        const int q = (int)(e & 0x0FFFFFFFu);
+        const int kx = (int)((e >> 28) & 3u) - 1, ky = (int)(e >> 30) - 1;
+        const double dx = __ldg(fr.sx + q) - (xi + kx * box.L[0]);
+        const double dy = __ldg(fr.sy + q) - (yi + ky * box.L[1]);
+        const double rsq = dx * dx + dy * dy;
+        const double f = pgt_pair_eval_t<MODEL>(pot, rsq, di, __ldg(fr.sd + q), PGT_WANT_FDIVR);
+        out.b[w0 + k] = make_double2(dx, dy);
+        out.cf[w0 + k] = make_double2(fma(dx, dx, dy * dy) * cscale, f);
+        out.j[w0 + k] = q;
+    }
+}
+
 template <int MODEL>
 static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, int* counts,
                                PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st)
 {
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
+    case 4: k_bonds_find<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, reinterpret_cast<unsigned*>(nbr_j), out.j); break;
+    case 5: k_bonds_fill_list<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
     case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
     case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;

@@ -12,6 +12,7 @@
 #include "pgt_math.cuh"
 
 #define PGT_MAX_GL 1024          // quadrature nodes kept in constant memory
+#define PGT_NB_SLOTS 16          // force-carrying neighbours per particle kept by the single-search bond path
 #define PGT_WRAP_MAX_ITERS 4096  // a position further than this many box lengths outside is a data error
 
 // error bits raised by kernels (checked by the host after each stage)
@@ -98,7 +99,9 @@ void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mas
                               const int* sorted_orig, int n_live, double* sx, double* sy, double* sd, double* skxx,
                               double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
-// mode 2/3: same for plain neighbours within max_rcut (export only).
+// mode 2/3: same for plain neighbours within max_rcut (export only);
+// mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word);
+// mode 5: fill the CSR arrays from that scratch (counts = scanned offsets).
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
                       PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
 // rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)

@@ -302,6 +302,25 @@ def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames, variant):
     gpu_ctx.set_option("ik_variant", 0)
 
 
+def test_bond_list_single_search_equals_two_search(gpu_ctx, orc, fixture_frames):
+    """The one-search bond builder (neighbours kept, dx re-formed from the same operands) writes the same records,
+    bit for bit and in the same order, as the count + fill pair; so does the path taken when a particle has more
+    bonds than the kept list holds (poly106, rc = 3: ~28 bonds per particle)."""
+    for model in ("poly12", "poly106"):
+        P = orc.potential(model)
+        pos, diam, box = fixture_frames.position(33), fixture_frames.diameter, fixture_frames.box
+        got = []
+        for single in (1, 0):
+            gpu_ctx.set_option("bond_single_search", single)
+            setup_ctx(gpu_ctx, orc, P, GPU_NAME[model], pos, diam, box)
+            gpu_ctx.build_bonds()
+            got.append(gpu_ctx.export_bonds())
+        gpu_ctx.set_option("bond_single_search", 1)
+        for a, b in zip(got[0], got[1]):
+            assert np.array_equal(a, b)
+        assert len(got[0][0]) > (20000 if model == "poly106" else 5000)
+
+
 @pytest.mark.parametrize("variant", [0, 2, 4])
 def test_gather_kernel_variants(orc, fixture_frames, variant, monkeypatch):
     """Both gather formulations (two-phase point lists, shared-memory tiles) against the oracle."""
