@@ -368,6 +368,15 @@ def main():
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
+    # DRAM bytes of one gather launch from the committed `ncu --set full` capture of this workload (profiles/)
+    traffic = None
+    try:
+        if args.workload == "cfg5" and args.shard == "frames":
+            for line in open(os.path.join(ROOT, "profiles", "r1_ik_gather2_full_cfg5.txt")):
+                if line.startswith("traffic"):
+                    traffic = float(line.split()[-1])
+    except Exception:
+        pass
     h2d = N * 3 * 4 + N * 4
     d2h = g_local * 4 * 8
 
@@ -381,7 +390,7 @@ def main():
                        "cg": {"kernel": wl["cg"][0], "rcut": wl["cg"][1], "order": q}, "shard": args.shard,
                        "frames_per_step_per_gpu": 1 if args.shard == "frames" else 1.0 / world, "frame_pool": pool,
                        "l2": "inputs larger than L2: each step rebuilds and streams a %.0f MB half-bond list + %.0f MB sorted frame"
-                             % (np.mean(hb_per_frame) * 28 / 1e6, N * 28 / 1e6),
+                             % (np.mean(hb_per_frame) * 36 / 1e6, N * 28 / 1e6),
                        "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
             "clocks": sampler.summary([(w0, w1), (w2, w3)]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -396,7 +405,7 @@ def main():
                          "work": "sum_x U(x)*(15q+9) flops, U counted on device (pgt_ik_count_work), %.4g flops per launch"
                                  % flops_avg,
                          "items_per_unique_bond": float(np.mean(items_per_frame)) / max(1.0, float(np.mean(flops_per_frame)) / (15 * q + 9)),
-                         "traffic": None,
+                         "traffic": traffic,
                          "hbm_peak_gbs": peaks.get("hbm_gbs")},
         }
         if world == 1 and not args.no_cpu_baseline:
