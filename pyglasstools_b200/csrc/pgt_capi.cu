@@ -161,7 +161,9 @@ struct pgt_ctx {
     cudaEvent_t user_ev[16]{};
 
     // tuning
-    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather
+    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather; 5: walk gather
+    bool grid_monotone = false;
+    double tspan_x = -1.0, tspan_y = -1.0;   // extent of the walk gather's grid tile (cartesian grids)
 
     // nccl
     pgtNcclComm comm = nullptr;
@@ -239,6 +241,7 @@ PgtFrameView frame_view(const pgt_ctx* c)
     v.hb_b = c->hb_b.as<double2>();
     v.hb_cf = c->hb_cf.as<double2>();
     v.hb_j = c->hb_j.as<int>();
+    v.n_hb = c->n_hb;
     v.hb_cscale = c->hb_cscale;
     return v;
 }
@@ -299,7 +302,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0);
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
-        if (l == 0 || l == 2 || l == 4) ctx->ik_variant = l;
+        if (l == 0 || l == 2 || l == 4 || l == 5) ctx->ik_variant = l;
     }
     *out = ctx;
     return PGT_OK;
@@ -644,6 +647,19 @@ int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double*
     CK(cudaMemcpyAsync(ctx->gxs.p, xs, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->gys.p, ys, sizeof(double) * ny, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    // largest extent of an aligned 16 x 8 tile of grid points (sizes the walk gather's shared-memory rectangle)
+    auto span = [](const double* v, int n, int t) {
+        double s = 0.0;
+        for (int a = 0; a < n; a += t) {
+            double lo = v[a], hi = v[a];
+            for (int k = a + 1; k < std::min(a + t, n); ++k) { lo = std::min(lo, v[k]); hi = std::max(hi, v[k]); }
+            s = std::max(s, hi - lo);
+        }
+        return s;
+    };
+    ctx->grid_monotone = std::is_sorted(xs, xs + nx) && std::is_sorted(ys, ys + ny);
+    ctx->tspan_x = span(xs, nx, 16);
+    ctx->tspan_y = span(ys, ny, 8);
     ctx->grid_mode = 0;
     ctx->nx = nx;
     ctx->ny = ny;
@@ -723,6 +739,9 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.grid.pts = ctx->gpts.as<double>();
     a.grid.g0 = ctx->g0;
     a.grid.g1 = ctx->g1;
+    a.grid.monotone = ctx->grid_monotone ? 1 : 0;
+    a.grid.tspan_x = ctx->tspan_x;
+    a.grid.tspan_y = ctx->tspan_y;
     a.box = ctx->box;
     a.cells = ctx->cells;
     a.cg = ctx->cg;
@@ -795,7 +814,7 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
     if (!ctx || !name) return PGT_ERR_ARG;
     if (!strcmp(name, "ik_variant")) {
         const int l = (int)value;
-        if (l != 0 && l != 2 && l != 4) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase) or 4 (tile)");
+        if (l != 0 && l != 2 && l != 4 && l != 5) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase), 4 (tile) or 5 (walk)");
         ctx->ik_variant = l;
         return PGT_OK;
     }

@@ -46,6 +46,7 @@ struct PgtFrameView {
     const double2* hb_b;         // b = r_j(image) - r_i, exactly as the reference's inner search forms it
     const double2* hb_cf;        // (|b|^2 * cscale,  f = -phi'(r)/r)
     const int* hb_j;             // sorted index of j
+    long long n_hb;              // half-bonds in the list (host-side sizing of the walk gather's tiles)
     double hb_cscale;            // scale folded into hb_cf.x: 1/R^2 of the CG function the list was built for
 };
 
@@ -62,6 +63,8 @@ struct PgtGridView {
     const double* ys;
     const double* pts;           // G x 3
     long long g0, g1;            // shard
+    int monotone;                // cartesian: both axes non-decreasing (np.linspace)
+    double tspan_x, tspan_y;     // cartesian: largest extent of an aligned 16 (x) by 8 (y) tile of grid points; < 0 unknown
 };
 
 struct PgtIKArgs {
@@ -107,8 +110,7 @@ void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, 
 // rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)
 void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_hb, double cscale, cudaStream_t st,
                               PgtLaunchCounter* lc);
-// variant 0: automatic (= two-phase, measured faster); 2: two-phase kernel;
-// 4: tile kernel (Cartesian grids + virial only, else two-phase)
+// variant 0: automatic; 2: two-phase kernel; 4: tile kernel, 5: walk kernel (Cartesian grids + virial only, else two-phase)
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
                        double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);

@@ -273,7 +273,7 @@ def test_empty_and_tiny_inputs(gpu_ctx, orc):
     assert np.all(gpu_ctx.ik_download() == 0)
 
 
-@pytest.mark.parametrize("variant", [2, 4])
+@pytest.mark.parametrize("variant", [2, 4, 5])
 def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames, variant):
     """np.array_split shards (irvingkirkwood/__init__.py:53-60) reproduce the unsharded field bit for bit,
     with either gather kernel."""
@@ -321,9 +321,9 @@ def test_bond_list_single_search_equals_two_search(gpu_ctx, orc, fixture_frames)
         assert len(got[0][0]) > (20000 if model == "poly106" else 5000)
 
 
-@pytest.mark.parametrize("variant", [0, 2, 4])
+@pytest.mark.parametrize("variant", [0, 2, 4, 5])
 def test_gather_kernel_variants(orc, fixture_frames, variant, monkeypatch):
-    """Both gather formulations (two-phase point lists, shared-memory tiles) against the oracle."""
+    """Every gather formulation (two-phase point lists, shared-memory tiles, per-thread walk) against the oracle."""
     monkeypatch.setenv("PGT_IK_VARIANT", str(variant))
     ctx = _capi.Context(0)
     try:
@@ -375,3 +375,35 @@ def test_synthetic_large_frame_properties(gpu_ctx, orc):
     gotf = full[np.ix_(ii, ii)].reshape(-1, 4)
     assert_close(gotf, wantf, scale=np.abs(wantf).max(axis=1, keepdims=True))
     assert np.array_equal(full[0], full[-1]) or np.allclose(full[0], full[-1], rtol=1e-12, atol=1e-12)
+
+
+@pytest.mark.parametrize("kernel,order,R,nmax,model", [("octic", 5, 2.0, 97, "poly12"), ("octic", 5, 4.0, 64, "poly10"),
+                                                       ("octic", 3, 1.0, 200, "poly12"), ("mollifier", 5, 2.5, 50, "poly12"),
+                                                       ("octic", 8, 3.0, 31, "poly106")])
+def test_walk_gather_on_cartesian_grids(gpu_ctx, orc, kernel, order, R, nmax, model):
+    """The walk gather (variant 5: unique bonds, weights 1 and 1/2) on Cartesian grids whose tiles are interior, on the
+    periodic seam and partial (nmax not a multiple of the tile), for several radii / quadratures / potentials:
+    against the oracle on a subsample and against the two-phase kernel everywhere."""
+    fr = synth.synth_frame(48, 17)
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential(model)
+    S = setup_ctx(gpu_ctx, orc, P, GPU_NAME[model], pos, diam, box)
+    gpu_ctx.build_bonds()
+    cg = orc.cgfunc(kernel, R, order)
+    gpu_ctx.set_cg(kernel, R, order)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, nmax)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    fields = {}
+    for variant in (2, 5):
+        gpu_ctx.set_option("ik_variant", variant)
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        fields[variant] = gpu_ctx.ik_download()
+    gpu_ctx.set_option("ik_variant", 0)
+    scale = np.abs(fields[2]).max(axis=1, keepdims=True)
+    assert_close(fields[5], fields[2], scale=scale)
+    ii = np.unique(np.concatenate([np.arange(0, nmax, 7), [nmax - 1]]))
+    grid = np.zeros((len(ii) ** 2, 3)); grid[:, 0] = np.repeat(axis[ii], len(ii)); grid[:, 1] = np.tile(axis[ii], len(ii))
+    want = S.ik(P, cg, grid)["virial"]
+    got = fields[5].reshape(nmax, nmax, 4)[np.ix_(ii, ii)].reshape(-1, 4)
+    assert_close(got, want, scale=np.abs(want).max(axis=1, keepdims=True))
