@@ -139,6 +139,7 @@ struct pgt_ctx {
     DevBuf sx, sy, sd, skxx, skxy, skyy;
     DevBuf hb_cnt, hb_b, hb_cf, hb_j, nb_list;
     bool bond_single_search = true;   // option "bond_single_search"
+    bool bond_fill_flat = true;       // option "bond_fill_flat": warp-flattened record writer (else thread per particle)
     double hb_cscale = 1.0;   // scale folded into the records' |b|^2 entry (1/R^2 of the CG function, or 1)
 
     // grid
@@ -300,6 +301,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     }
     cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocMapped);
     cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0);
+    if (const char* env = getenv("PGT_BOND_FILL_FLAT")) ctx->bond_fill_flat = atoi(env) != 0;
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
         if (l == 0 || l == 2 || l == 4 || l == 5) ctx->ik_variant = l;
@@ -617,7 +619,7 @@ int pgt_build_bonds(pgt_ctx* ctx)
     fr = frame_view(ctx);
     const PgtBondOut out{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>() };
     if (listed)
-        pgt_launch_bonds(5, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale,
+        pgt_launch_bonds(ctx->bond_fill_flat ? 5 : 6, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale,
                          ctx->nb_list.as<int>(), ctx->stream, &ctx->launches);
     else
         pgt_launch_bonds(1, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale, nullptr,
@@ -816,6 +818,11 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
         const int l = (int)value;
         if (l != 0 && l != 2 && l != 4 && l != 5) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase), 4 (tile) or 5 (walk)");
         ctx->ik_variant = l;
+        return PGT_OK;
+    }
+    if (!strcmp(name, "bond_fill_flat")) {
+        ctx->bond_fill_flat = value != 0.0;
+        ctx->bonds_built = false;
         return PGT_OK;
     }
     if (!strcmp(name, "bond_single_search")) {

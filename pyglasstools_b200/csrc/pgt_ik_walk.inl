@@ -53,6 +53,30 @@ struct IKWStatic {
     double2 shift[IKW_MAXRUNS];          // (kx Lx, ky Ly) of the run's periodic image
 };
 
+// Gauss-Legendre sum of the shape along the bond.  5-point octic: g = 1 - t^2 is positive exactly when the node lies
+// inside the disc (t < 1), so the reference's `if (d^2 < R^2)` is a clamp of g at zero -- done on the sign word with two
+// integer instructions instead of a compare and two selects (a cleared high word leaves at most a denormal, whose
+// square is zero).
+template <int KERNEL, int Q>
+__device__ __forceinline__ double ikw_quadrature(const PgtIKArgs& A, double c0, double c1, double c2)
+{
+    if (KERNEL == PGT_CG_OCTIC && Q == 5) {
+        double B0 = 0.0, B1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const double s = A.gl_s[k];
+            const double t = fma(fma(c2, s, c1), s, c0);
+            const double g = fma(-t, t, 1.0);
+            const int hi = __double2hiint(g);
+            const double gc = __hiloint2double(hi & ~(hi >> 31), __double2loint(g));
+            const double gg = gc * gc;
+            if (k & 1) B1 = fma(A.gl_w[k], gg, B1); else B0 = fma(A.gl_w[k], gg, B0);
+        }
+        return B0 + B1;
+    }
+    return bond_quadrature<KERNEL, Q>(c0, c1, c2, A.nq);
+}
+
 template <int KERNEL, int Q, bool STAGE>
 __global__ void __launch_bounds__(IKW_THREADS) k_ik_walk(const PgtIKArgs A, const int tile_i_begin, const IKWCaps caps)
 {
@@ -346,7 +370,7 @@ __global__ void __launch_bounds__(IKW_THREADS) k_ik_walk(const PgtIKArgs A, cons
             const double ax = p.x - gx, ay = p.y - gy;
             const double c0 = fma(ax, ax, ay * ay) * iR2;
             const double c1 = fma(ax, b.x, ay * b.y) * iR2x2;
-            const double wf = ikt_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * (cf.y * wgt);
+            const double wf = ikw_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * (cf.y * wgt);
             const double tx = wf * b.x, ty = wf * b.y;
             txx = fma(tx, b.x, txx);
             txy = fma(tx, b.y, txy);
@@ -374,7 +398,7 @@ static bool ikw_pick_caps(const PgtIKArgs& a, IKWCaps* caps, size_t* dyn_bytes, 
         cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
         cudaDeviceGetAttribute(&smem_cta, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     }
-    static int want_ctas = -1, margin_pct = 30, want_stage = 1, want_list = 0;
+    static int want_ctas = -1, margin_pct = 15, want_stage = 0, want_list = 0;
     if (want_ctas < 0) {
         const char* e = getenv("PGT_IKW_CTAS");
         want_ctas = e ? atoi(e) : 0;
@@ -404,7 +428,7 @@ static bool ikw_pick_caps(const PgtIKArgs& a, IKWCaps* caps, size_t* dyn_bytes, 
         const long long avail = std::min<long long>(smem_sm / ctas, smem_cta) - stat - base;
         const long long lc = avail / (2 * IKW_THREADS);
         const long long need = (ctas == 1 || ctas == want_ctas) ? 8 : 32;
-        if (lc >= need) list_cap = (int)std::min<long long>(lc, want_list > 0 ? want_list : 64);
+        if (lc >= need) list_cap = (int)std::min<long long>(lc, want_list > 0 ? want_list : 32);
     }
     if (list_cap == 0) return false;
     caps->rows_cap = rows_cap;

@@ -425,6 +425,48 @@ __global__ void __launch_bounds__(128) k_bonds_fill_list(PgtPot pot, PgtFrameVie
     }
 }
 
+// Same records, written by a warp that FLATTENS the half-bonds of its 32 consecutive particles: lane <-> record, so
+// every lane evaluates one pair force per step whatever the particles' bond counts (thread-per-particle runs at
+// ~3.6/7 lanes), two steps are in flight at once, and the 36-byte records leave as coalesced stores.  The owner of
+// record e is the last lane whose first record is <= e (offsets are non-decreasing): a 5-step shuffle search.
+template <int MODEL>
+__global__ void __launch_bounds__(128) k_bonds_fill_flat(PgtPot pot, PgtFrameView fr, PgtBox box, const int* __restrict__ hb_off,
+                                                         const unsigned* __restrict__ nb_list, PgtBondOut out, double cscale)
+{
+    const int lane = threadIdx.x & 31;
+    const int p0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31;
+    if (p0 >= fr.n) return;
+    const bool have = p0 + lane < fr.n;
+    const int p = have ? p0 + lane : fr.n - 1;
+    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+    const int w0 = have ? hb_off[p] : hb_off[fr.n];
+    const int w1 = have ? hb_off[p + 1] : w0;
+    const int W0 = __shfl_sync(FULL_MASK, w0, 0), W1 = __shfl_sync(FULL_MASK, w1, 31);
+    for (int base = W0; base < W1; base += 32) {
+        const int e = base + lane;
+        int o = 0;
+#pragma unroll
+        for (int step = 16; step >= 1; step >>= 1) {
+            const int v = __shfl_sync(FULL_MASK, w0, o + step);       // o + step <= 31 always
+            if (v <= e) o += step;
+        }
+        const int k = e - __shfl_sync(FULL_MASK, w0, o);
+        const double xo = __shfl_sync(FULL_MASK, xi, o), yo = __shfl_sync(FULL_MASK, yi, o), dio = __shfl_sync(FULL_MASK, di, o);
+        if (e < W1) {
+            const unsigned en = __ldg(nb_list + (size_t)k * fr.n + (p0 + o));
+            const int q = (int)(en & 0x0FFFFFFFu);
+            const int kx = (int)((en >> 28) & 3u) - 1, ky = (int)(en >> 30) - 1;
+            const double dx = __ldg(fr.sx + q) - (xo + kx * box.L[0]);
+            const double dy = __ldg(fr.sy + q) - (yo + ky * box.L[1]);
+            const double rsq = dx * dx + dy * dy;
+            const double f = pgt_pair_eval_t<MODEL>(pot, rsq, dio, __ldg(fr.sd + q), PGT_WANT_FDIVR);
+            out.b[e] = make_double2(dx, dy);
+            out.cf[e] = make_double2(fma(dx, dx, dy * dy) * cscale, f);
+            out.j[e] = q;
+        }
+    }
+}
+
 template <int MODEL>
 static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, int* counts,
                                PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st)
@@ -432,7 +474,8 @@ static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, Pgt
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
     case 4: k_bonds_find<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, reinterpret_cast<unsigned*>(nbr_j), out.j); break;
-    case 5: k_bonds_fill_list<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
+    case 5: k_bonds_fill_flat<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
+    case 6: k_bonds_fill_list<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
     case 1: k_bonds<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
     case 2: k_bonds<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;

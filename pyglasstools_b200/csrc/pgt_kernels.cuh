@@ -104,7 +104,7 @@ void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mas
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
 // mode 2/3: same for plain neighbours within max_rcut (export only);
 // mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word);
-// mode 5: fill the CSR arrays from that scratch (counts = scanned offsets).
+// mode 5: fill the CSR arrays from that scratch (counts = scanned offsets), warp-flattened; mode 6: same, thread per particle.
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
                       PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
 // rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)

@@ -310,14 +310,17 @@ def test_bond_list_single_search_equals_two_search(gpu_ctx, orc, fixture_frames)
         P = orc.potential(model)
         pos, diam, box = fixture_frames.position(33), fixture_frames.diameter, fixture_frames.box
         got = []
-        for single in (1, 0):
+        for single, flat in ((1, 1), (1, 0), (0, 1)):
             gpu_ctx.set_option("bond_single_search", single)
+            gpu_ctx.set_option("bond_fill_flat", flat)       # warp-flattened writer vs thread per particle
             setup_ctx(gpu_ctx, orc, P, GPU_NAME[model], pos, diam, box)
             gpu_ctx.build_bonds()
             got.append(gpu_ctx.export_bonds())
         gpu_ctx.set_option("bond_single_search", 1)
-        for a, b in zip(got[0], got[1]):
-            assert np.array_equal(a, b)
+        gpu_ctx.set_option("bond_fill_flat", 1)
+        for other in got[1:]:
+            for a, b in zip(got[0], other):
+                assert np.array_equal(a, b)
         assert len(got[0][0]) > (20000 if model == "poly106" else 5000)
 
 
