@@ -331,11 +331,11 @@ __device__ __forceinline__ void for_each_neighbor_img(const PgtFrameView& fr, co
             const int qb = __ldg(fr.cell_start + rbase + seg[s].c0);
             const int qe = __ldg(fr.cell_start + rbase + seg[s].c1 + 1);
             for (int q = qb; q < qe; ++q) {
-                if (q == p) continue;
                 const double dx = __ldg(fr.sx + q) - cpx;
                 const double dy = __ldg(fr.sy + q) - cpy;
                 const double accum = dx * dx + dy * dy;
-                if (!(accum > rc2)) visit(q, dx, dy, accum, (unsigned)(seg[s].k + 1) | ((unsigned)(ky + 1) << 2));
+                // the particle itself is skipped (IrvingKirkwood.h:97, ThermoCalculator.h:81), tested on hits only
+                if (!(accum > rc2) && q != p) visit(q, dx, dy, accum, (unsigned)(seg[s].k + 1) | ((unsigned)(ky + 1) << 2));
             }
         }
     }
