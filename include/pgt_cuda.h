@@ -65,6 +65,11 @@ int pgt_potential_set(pgt_ctx* ctx, int model_id, double scaled_rcut, const doub
 /* Replaces: FixedPointCGFunc<D>(order, rcut) (cgfunc/CoarseGrainFunction.h:56-92) and the GSL
  * glfixed table (cgfunc/FixedPointQuadrature.h:35).                                            */
 int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int order);
+/* Replaces: AdaptiveCGFunc<D>(maxiter, relerr, abserr, rcut) (cgfunc/CoarseGrainFunction.h:94-134) and its
+ * gsl_integration_qag(.., epsabs, epsrel, limit, key = 1, ..) call (cgfunc/Quadrature.h:39-51): global adaptive
+ * bisection with the 15-point Gauss-Kronrod pair.  A bond on which GSL would exit through its error handler (the
+ * reference aborts there) makes pgt_ik_compute return PGT_ERR_DATA.                                              */
+int pgt_cg_set_adaptive(pgt_ctx* ctx, int kernel_id, double cg_rcut, double epsabs, double epsrel, int limit);
 /* Replaces: Calculator::max_rcut, frozen at construction (Calculator.h:37-46).                 */
 int pgt_set_max_rcut(pgt_ctx* ctx, double max_rcut);
 /* Optional tuning: target cell side of the device cell list (default max_rcut/2).              */
@@ -135,6 +140,9 @@ double pgt_pair_eval(int model_id, double scaled_rcut, const double* params, int
                      const double rij[3], double di, double dj, int what);
 double pgt_cg_delta(int kernel_id, double cg_rcut, double dr_sq);
 double pgt_cg_bond(int kernel_id, double cg_rcut, int order, const double x[3], const double ri[3], const double rij[3]);
+/* AdaptiveCGFunc::getBondFunc (CoarseGrainFunction.h:123-126); *status (may be NULL) receives 0 or the QAG exit code */
+double pgt_cg_bond_adaptive(int kernel_id, double cg_rcut, double epsabs, double epsrel, int limit, const double x[3],
+                            const double ri[3], const double rij[3], int* status);
 /* FP64 FMA peak probe: runs a dependent-chain DFMA kernel, returns achieved TFLOP/s.            */
 int pgt_fp64_peak_probe(pgt_ctx* ctx, double* tflops);
 /* Algorithmic work of the IK gather: sum over the local shard of U(x), the

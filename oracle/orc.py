@@ -21,7 +21,8 @@ class OrcPot(C.Structure):
 
 
 class OrcCG(C.Structure):
-    _fields_ = [("kernel", C.c_int), ("rcut", C.c_double), ("order", C.c_int), ("mollifier_norm", C.c_double)]
+    _fields_ = [("kernel", C.c_int), ("rcut", C.c_double), ("order", C.c_int), ("mollifier_norm", C.c_double),
+                ("adaptive", C.c_int), ("epsabs", C.c_double), ("epsrel", C.c_double), ("limit", C.c_int)]
 
 
 def build(force=False):
@@ -149,6 +150,37 @@ def cgfunc(name, rcut, order):
     cg = OrcCG()
     lib().orc_cg_init(C.byref(cg), KERNEL_IDS[name], C.c_double(rcut), int(order))
     return cg
+
+
+def cgfunc_adaptive(name, rcut, relerr=1e-9, abserr=1e-9, maxiter=100):
+    """cgfunc.<kernel>(rcut, mode="adaptive", relerr=, abserr=, maxiter=) -> CGFunc*Adaptive(maxiter, relerr, abserr, rcut)
+    (cgfunc/__init__.py:37-44): GSL QAG with the 15-point Gauss-Kronrod rule."""
+    cg = OrcCG()
+    L = lib()
+    L.orc_cg_init_adaptive.argtypes = [C.POINTER(OrcCG), C.c_int, C.c_double, C.c_double, C.c_double, C.c_int]
+    L.orc_cg_init_adaptive.restype = None
+    L.orc_cg_init_adaptive(C.byref(cg), KERNEL_IDS[name], rcut, relerr, abserr, int(maxiter))
+    return cg
+
+
+def qag_test(which, a, b, epsabs, epsrel, limit):
+    """The QAG (GK15) restatement on a closed-form integrand: returns (value, status, abserr)."""
+    L = lib()
+    L.orc_qag_test.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_int, C.POINTER(C.c_int),
+                               C.POINTER(C.c_double)]
+    L.orc_qag_test.restype = C.c_double
+    st, err = C.c_int(0), C.c_double(0.0)
+    v = L.orc_qag_test(which, a, b, epsabs, epsrel, limit, C.byref(st), C.byref(err))
+    return v, st.value, err.value
+
+
+def gk15_tables():
+    L = lib()
+    xgk, wg, wgk = np.empty(8), np.empty(4), np.empty(8)
+    L.orc_gk15_tables.argtypes = [C.c_void_p] * 3
+    L.orc_gk15_tables.restype = None
+    L.orc_gk15_tables(xgk.ctypes.data, wg.ctypes.data, wgk.ctypes.data)
+    return xgk, wg, wgk
 
 
 def pair_table(P, rij, di, dj):

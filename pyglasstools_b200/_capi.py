@@ -20,7 +20,7 @@ STAGES = {"upload": 0, "cells": 1, "bonds": 2, "ik": 3, "thermo": 4, "download":
 
 EXPORTED = [
     "pgt_ctx_create", "pgt_ctx_destroy", "pgt_last_error", "pgt_device_count", "pgt_synchronize", "pgt_stream",
-    "pgt_potential_set", "pgt_cg_set", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
+    "pgt_potential_set", "pgt_cg_set", "pgt_cg_set_adaptive", "pgt_cg_bond_adaptive", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
     "pgt_frame_set_device", "pgt_build_cells", "pgt_build_bonds", "pgt_frame_counts", "pgt_grid_set_cartesian",
     "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_download_async", "pgt_ik_download_wait", "pgt_ik_device_ptr",
     "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
@@ -30,6 +30,16 @@ EXPORTED = [
 ]
 
 _lib = None
+
+
+def cg_bond_adaptive(kernel, rcut, relerr, abserr, maxiter, x, ri, rij):
+    """AdaptiveCGFunc::getBondFunc on the host side of the library: (value, QAG exit code)."""
+    kid = CG_IDS[kernel] if isinstance(kernel, str) else int(kernel)
+    a = [np.ascontiguousarray(v, np.float64) for v in (x, ri, rij)]
+    st = C.c_int(0)
+    v = lib().pgt_cg_bond_adaptive(kid, float(rcut), float(abserr), float(relerr), int(maxiter), a[0].ctypes.data,
+                                   a[1].ctypes.data, a[2].ctypes.data, C.byref(st))
+    return v, st.value
 
 
 class PgtError(RuntimeError):
@@ -64,6 +74,10 @@ def lib():
         L.pgt_synchronize.argtypes = [C.c_void_p]
         L.pgt_potential_set.argtypes = [C.c_void_p, C.c_int, C.c_double, C.POINTER(C.c_double), C.c_int]
         L.pgt_cg_set.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_int, C.c_int]
+        L.pgt_cg_set_adaptive.argtypes = [C.c_void_p, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int]
+        L.pgt_cg_bond_adaptive.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_int, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.POINTER(C.c_int)]
+        L.pgt_cg_bond_adaptive.restype = C.c_double
         L.pgt_set_max_rcut.argtypes = [C.c_void_p, C.c_double]
         L.pgt_set_cell_size.argtypes = [C.c_void_p, C.c_double]
         L.pgt_frame_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64,
@@ -139,6 +153,11 @@ class Context:
     def set_cg(self, kernel, rcut, order, mode=0):
         kid = CG_IDS[kernel] if isinstance(kernel, str) else int(kernel)
         self._ck(lib().pgt_cg_set(self._h, kid, float(rcut), int(mode), int(order)))
+
+    def set_cg_adaptive(self, kernel, rcut, relerr=1e-9, abserr=1e-9, maxiter=100):
+        """cgfunc.<kernel>(rcut, mode="adaptive", ...): GSL QAG / 15-point Gauss-Kronrod bond quadrature."""
+        kid = CG_IDS[kernel] if isinstance(kernel, str) else int(kernel)
+        self._ck(lib().pgt_cg_set_adaptive(self._h, kid, float(rcut), float(abserr), float(relerr), int(maxiter)))
 
     def set_max_rcut(self, v):
         self._ck(lib().pgt_set_max_rcut(self._h, float(v)))

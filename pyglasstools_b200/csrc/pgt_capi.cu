@@ -163,6 +163,9 @@ struct pgt_ctx {
 
     // tuning
     int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather; 5: walk gather
+    int quad_mode = PGT_QUAD_FIXEDPOINT;     // PGT_QUAD_ADAPTIVE: QAG / GK15 bond quadrature
+    double qag_epsabs = 0.0, qag_epsrel = 0.0;
+    int qag_limit = 0;
     bool grid_monotone = false;
     double tspan_x = -1.0, tspan_y = -1.0;   // extent of the walk gather's grid tile (cartesian grids)
 
@@ -393,7 +396,7 @@ int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int o
     if (!ctx) return PGT_ERR_ARG;
     if (kernel_id < PGT_CG_OCTIC || kernel_id > PGT_CG_MOLLIFIER) return fail(ctx, PGT_ERR_ARG, "unknown CG kernel %d", kernel_id);
     if (quad_mode != PGT_QUAD_FIXEDPOINT)
-        return fail(ctx, PGT_ERR_UNSUPPORTED, "adaptive (GSL QAG) bond quadrature is not implemented on device");
+        return fail(ctx, PGT_ERR_ARG, "adaptive bond quadrature takes tolerances: use pgt_cg_set_adaptive");
     if (order < 1 || order > PGT_MAX_GL) return fail(ctx, PGT_ERR_UNSUPPORTED, "quadrature order %d outside [1,%d]", order, PGT_MAX_GL);
     if (!(cg_rcut > 0)) return fail(ctx, PGT_ERR_ARG, "cg_rcut must be positive");
     CK(cudaSetDevice(ctx->device));
@@ -423,7 +426,27 @@ int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int o
         for (int k = 0; k < 5; ++k) { ctx->gl_s[k] = s[k]; ctx->gl_w[k] = ww[k]; }
     CK(pgt_upload_gl_tables(s.data(), ww.data(), ctx->nq, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));   // s/ww are stack-owned
+    ctx->quad_mode = PGT_QUAD_FIXEDPOINT;
     ctx->have_cg = true;
+    return PGT_OK;
+}
+
+int pgt_cg_set_adaptive(pgt_ctx* ctx, int kernel_id, double cg_rcut, double epsabs, double epsrel, int limit)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (kernel_id < PGT_CG_OCTIC || kernel_id > PGT_CG_MOLLIFIER) return fail(ctx, PGT_ERR_ARG, "unknown CG kernel %d", kernel_id);
+    if (!(cg_rcut > 0)) return fail(ctx, PGT_ERR_ARG, "cg_rcut must be positive");
+    // gsl_integration_qag: "tolerance cannot be achieved with given epsabs and epsrel" (GSL_EBADTOL), limit > workspace
+    if (epsabs <= 0 && (epsrel < 50 * 2.2204460492503131e-16 || epsrel < 0.5e-28))
+        return fail(ctx, PGT_ERR_ARG, "tolerance cannot be achieved with given epsabs and epsrel");
+    if (limit < 1) return fail(ctx, PGT_ERR_ARG, "maxiter must be >= 1");
+    // the fixed-point tables keep a valid (1-point) rule so that stages that only need Delta() are unaffected
+    const int rc = pgt_cg_set(ctx, kernel_id, cg_rcut, PGT_QUAD_FIXEDPOINT, 1);
+    if (rc != PGT_OK) return rc;
+    ctx->quad_mode = PGT_QUAD_ADAPTIVE;
+    ctx->qag_epsabs = epsabs;
+    ctx->qag_epsrel = epsrel;
+    ctx->qag_limit = limit;
     return PGT_OK;
 }
 
@@ -723,8 +746,31 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
         pgt_launch_rescale_bonds(ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->n_hb, ctx->hb_cscale, ctx->stream, &ctx->launches);
     }
     PgtIKArgs a = ik_args(ctx, obs_mask);
-    if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_variant, ctx->stream, &ctx->launches));
+    bool check_qag = false;
+    if (ctx->quad_mode == PGT_QUAD_ADAPTIVE && (obs_mask & PGT_OBS_VIRIAL)) {
+        // local observables only need Delta(): the regular kernel; the virial field: the QAG kernel
+        if (gl > 0 && (obs_mask & ~PGT_OBS_VIRIAL)) {
+            PgtIKArgs al = a;
+            al.obs_mask = obs_mask & ~PGT_OBS_VIRIAL;
+            CK(pgt_launch_ik(al, 2, ctx->stream, &ctx->launches));
+        }
+        if (gl > 0) {
+            CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
+            CK(pgt_launch_ik_adaptive(a, ctx->eflags.as<int>(), ctx->stream, &ctx->launches));
+            check_qag = true;
+        }
+    } else if (gl > 0) CK(pgt_launch_ik(a, ctx->ik_variant, ctx->stream, &ctx->launches));
     stage_end(ctx, PGT_STAGE_IK);
+    if (check_qag) {
+        pgt_launch_publish(ctx->eflags.p, 1, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
+        CK(cudaStreamSynchronize(ctx->stream));
+        const int fl = reinterpret_cast<int*>(ctx->h_small)[0];
+        if (fl & PGT_EFLAG_QAG_CAPACITY)
+            return fail(ctx, PGT_ERR_UNSUPPORTED, "adaptive bond quadrature: a bond needs more than %d intervals on device", PGT_QAG_CAP);
+        if (fl & PGT_EFLAG_QAG_FAILED)
+            return fail(ctx, PGT_ERR_DATA, "adaptive bond quadrature did not reach the tolerance within maxiter = %d intervals "
+                        "(GSL's error handler aborts the reference here)", ctx->qag_limit);
+    }
     ctx->last_ik_mask = obs_mask;
     return PGT_OK;
 }
@@ -749,6 +795,9 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.cg = ctx->cg;
     a.inv_rcutsq = 1.0 / ctx->cg.rcutsq;
     a.nq = ctx->nq;
+    a.qag_epsabs = ctx->qag_epsabs;
+    a.qag_epsrel = ctx->qag_epsrel;
+    a.qag_limit = ctx->qag_limit;
     a.gl5_h1 = ctx->gl5[0]; a.gl5_h1sq = ctx->gl5[1]; a.gl5_h2 = ctx->gl5[2]; a.gl5_h2sq = ctx->gl5[3];
     a.gl5_w0 = ctx->gl5[4]; a.gl5_w1 = ctx->gl5[5]; a.gl5_w2 = ctx->gl5[6];
     for (int k = 0; k < 5; ++k) { a.gl_s[k] = ctx->gl_s[k]; a.gl_w[k] = ctx->gl_w[k]; }
@@ -1070,6 +1119,27 @@ double pgt_cg_bond(int kernel_id, double cg_rcut, int order, const double x[3], 
         sum += gw[i] * (f(0.5 + Ax) + f(0.5 - Ax));
     }
     return 0.5 * sum;
+}
+
+double pgt_cg_bond_adaptive(int kernel_id, double cg_rcut, double epsabs, double epsrel, int limit, const double x[3],
+                            const double ri[3], const double rij[3], int* status)
+{
+    struct Integrand {                                     // getObjFunc (CoarseGrainFunction.h:42-45)
+        int kernel_id; double cg_rcut; const double *x, *ri, *rij;
+        double operator()(double s) const
+        {
+            double d2 = 0;
+            for (int k = 0; k < 3; ++k) {
+                const double d = x[k] - (ri[k] + s * rij[k]);
+                d2 += d * d;
+            }
+            return pgt_cg_delta(kernel_id, cg_rcut, d2);
+        }
+    };
+    int st = 0;
+    const double v = pgt_qag15(Integrand{ kernel_id, cg_rcut, x, ri, rij }, 0.0, 1.0, epsabs, epsrel, limit, &st);
+    if (status) *status = st;
+    return v;
 }
 
 int pgt_fp64_peak_probe(pgt_ctx* ctx, double* tflops)

@@ -957,6 +957,71 @@ cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtL
 }
 
 // ------------------------------------------------------------------------------------------
+// Stage 4 with the adaptive bond quadrature (AdaptiveCGFunc, CoarseGrainFunction.h:94-134): one thread per grid point
+// walks the reference's own loop (IrvingKirkwood.h:80-107) over the half-bond list and integrates
+// Delta(|a + s b|^2) over s in [0, 1] with QAG / GK15 (pgt_qag15).  Not a throughput path: the interval store lives in
+// local memory and the trip counts diverge; it exists so that cgfunc.*(mode="adaptive") runs on the device.
+__global__ void __launch_bounds__(128) k_ik_adaptive(const PgtIKArgs A, int* __restrict__ eflags)
+{
+    const long long g = A.grid.g0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= A.grid.g1) return;
+    double gx, gy;
+    if (A.grid.mode == 0) { gx = A.grid.xs[g / A.grid.ny]; gy = A.grid.ys[g % A.grid.ny]; }
+    else { gx = A.grid.pts[3 * g]; gy = A.grid.pts[3 * g + 1]; }
+    const PgtFrameView& fr = A.fr;
+    const PgtCG cg = A.cg;
+    const double R = cg.rcut, R2 = cg.rcutsq;
+    const int ncx = A.cells.ncx, ncy = A.cells.ncy;
+    const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
+    const int ux0 = max(__double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx), -ncx);
+    const int ux1 = min(__double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx), 2 * ncx - 1);
+    const int uy0 = max(__double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy), -ncy);
+    const int uy1 = min(__double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy), 2 * ncy - 1);
+    Seg seg[3];
+    const int nseg = split_segments(ux0, ux1, ncx, seg);
+    double axx = 0.0, axy = 0.0, ayy = 0.0;
+    int bad = 0;
+    for (int uy = uy0; uy <= uy1; ++uy) {
+        int ky = 0, row = uy;
+        if (uy < 0) { ky = +1; row += ncy; } else if (uy >= ncy) { ky = -1; row -= ncy; }
+        const double cpy = gy + ky * A.box.L[1];
+        for (int s = 0; s < nseg; ++s) {
+            const double cpx = gx + seg[s].k * A.box.L[0];
+            const int qb = fr.cell_start[row * ncx + seg[s].c0], qe = fr.cell_start[row * ncx + seg[s].c1 + 1];
+            for (int q = qb; q < qe; ++q) {
+                const double ax = fr.sx[q] - cpx, ay = fr.sy[q] - cpy;
+                if (ax * ax + ay * ay > R2) continue;
+                for (int e = fr.hb_off[q]; e < fr.hb_off[q + 1]; ++e) {
+                    const double2 b = fr.hb_b[e];
+                    int st = 0;
+                    const double B = pgt_qag15([&](double t) {
+                        const double px = ax + t * b.x, py = ay + t * b.y;
+                        return pgt_cg_delta_exact(cg, px * px + py * py);
+                    }, 0.0, 1.0, A.qag_epsabs, A.qag_epsrel, A.qag_limit, &st);
+                    if (st) bad |= (st == PGT_QAG_CAPACITY) ? PGT_EFLAG_QAG_CAPACITY : PGT_EFLAG_QAG_FAILED;
+                    const double wf = 0.5 * B * fr.hb_cf[e].y;      // val += 0.5 * bondval * (f rij (x) rij)
+                    const double tx = wf * b.x, ty = wf * b.y;
+                    axx += tx * b.x;
+                    axy += tx * b.y;
+                    ayy += ty * b.y;
+                }
+            }
+        }
+    }
+    if (bad) atomicOr(eflags, bad);
+    *reinterpret_cast<double4*>(A.out_virial + 4 * (g - A.grid.g0)) = make_double4(axx, axy, axy, ayy);
+}
+
+cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    const long long n = a.grid.g1 - a.grid.g0;
+    if (n <= 0) return cudaSuccess;
+    k_ik_adaptive<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(a, eflags);
+    lc->n++;
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
 // Work counter for the roofline numerator (not on the hot path): one thread per grid point.
 //   out[0] += U(x): unique force-carrying bonds with >= 1 endpoint in the disc (both tests exact)
 //   out[1] += half-bond items the gather integrates,  out[2] += particles in the disc

@@ -16,7 +16,8 @@
 #define PGT_WRAP_MAX_ITERS 4096  // a position further than this many box lengths outside is a data error
 
 // error bits raised by kernels (checked by the host after each stage)
-enum { PGT_EFLAG_Z_NONZERO = 1, PGT_EFLAG_WRAP_RUNAWAY = 2, PGT_EFLAG_BOND_OVERFLOW = 4 };
+enum { PGT_EFLAG_Z_NONZERO = 1, PGT_EFLAG_WRAP_RUNAWAY = 2, PGT_EFLAG_BOND_OVERFLOW = 4, PGT_EFLAG_QAG_FAILED = 8,
+       PGT_EFLAG_QAG_CAPACITY = 16 };
 
 struct PgtBox {
     double lo[3], hi[3], L[3];
@@ -82,6 +83,8 @@ struct PgtIKArgs {
     double* out_kinetic;         // (g1-g0) x 4
     double* out_density;         // (g1-g0)
     unsigned obs_mask;
+    double qag_epsabs, qag_epsrel;   // adaptive bond quadrature (GSL QAG): tolerances and interval limit
+    int qag_limit;
 };
 
 struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 16 (2-D)
@@ -112,6 +115,8 @@ void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_h
                               PgtLaunchCounter* lc);
 // variant 0: automatic; 2: two-phase kernel; 4: tile kernel, 5: walk kernel (Cartesian grids + virial only, else two-phase)
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
+// virial field with the adaptive (QAG, 15-point Gauss-Kronrod) bond quadrature; failures are OR-ed into *eflags
+cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
                        double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
 int pgt_thermo_blocks(int n);

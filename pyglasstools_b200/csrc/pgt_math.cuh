@@ -20,6 +20,12 @@
 #define PGT_HD inline
 #endif
 
+#if defined(__CUDA_ARCH__)
+#define PGT_UNROLL _Pragma("unroll")
+#else
+#define PGT_UNROLL
+#endif
+
 #ifndef M_PI
 #define M_PI 3.14159265358979323846
 #endif
@@ -201,3 +207,131 @@ PGT_HD double pgt_cg_shape(double t)
     if (KERNEL == PGT_CG_RECT) return 1.0;
     return exp(-1.0 / (1.0 - t));
 }
+
+// --------------------------------------------------------------------------------------------
+// Adaptive bond quadrature: the reference's AdaptiveCGFunc (CoarseGrainFunction.h:94-134) calls GSLQuadrature
+// (Quadrature.h:39-51) = gsl_integration_qag(f, 0, 1, epsabs, epsrel, limit, key 1, ...): global adaptive bisection
+// with the 15-point Gauss-Kronrod pair, worst interval first.  The interval store here has a fixed capacity per thread
+// (PGT_QAG_CAP); a bond that needs more (or any of GSL's failure exits, which abort the reference through GSL's
+// default error handler) raises a status instead of a value nobody checked.
+#define PGT_QAG_CAP 40
+enum { PGT_QAG_OK = 0, PGT_QAG_ROUNDOFF0 = 1, PGT_QAG_LIMIT = 2, PGT_QAG_ROUNDOFF = 3, PGT_QAG_SINGULAR = 4, PGT_QAG_FAILED = 5,
+       PGT_QAG_CAPACITY = 6 };
+
+struct PgtGK15 { double r, err, rabs, rasc; };
+
+// one Gauss-Kronrod (7, 15) evaluation on [a, b], sums in GSL's order (qk.c): Gauss nodes first, then the rest
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
+template <class F>
+PGT_HD PgtGK15 pgt_gk15(F f, double a, double b)
+{
+    const double xgk[8] = { 0.991455371120812639206854697526329, 0.949107912342758524526189684047851,
+                            0.864864423359769072789712788640926, 0.741531185599394439863864773280788,
+                            0.586087235467691130294144838258730, 0.405845151377397166906606412076961,
+                            0.207784955007898467600689403773245, 0.0 };
+    const double wg[4] = { 0.129484966168869693270611432679082, 0.279705391489276667901467771423780,
+                           0.381830050505118944950369775488975, 0.417959183673469387755102040816327 };
+    const double wgk[8] = { 0.022935322010529224963732008058970, 0.063092092629978553290700663189204,
+                            0.104790010322250183839876322541518, 0.140653259715525918745189590510238,
+                            0.169004726639267902826583426598550, 0.190350578064785409913256402421014,
+                            0.204432940075298892414161999234649, 0.209482141084727828012999174891714 };
+    const double c = 0.5 * (a + b), h = 0.5 * (b - a);
+    double lo[7], hi[7];
+    const double fc = f(c);
+    double gauss = fc * wg[3], kron = fc * wgk[7], sabs = fabs(kron);
+PGT_UNROLL
+    for (int j = 0; j < 3; ++j) {
+        const int m = 2 * j + 1;
+        const double d = h * xgk[m];
+        lo[m] = f(c - d); hi[m] = f(c + d);
+        const double fs = lo[m] + hi[m];
+        gauss += wg[j] * fs;
+        kron += wgk[m] * fs;
+        sabs += wgk[m] * (fabs(lo[m]) + fabs(hi[m]));
+    }
+PGT_UNROLL
+    for (int j = 0; j < 4; ++j) {
+        const int m = 2 * j;
+        const double d = h * xgk[m];
+        lo[m] = f(c - d); hi[m] = f(c + d);
+        kron += wgk[m] * (lo[m] + hi[m]);
+        sabs += wgk[m] * (fabs(lo[m]) + fabs(hi[m]));
+    }
+    const double mean = kron * 0.5;
+    double sasc = wgk[7] * fabs(fc - mean);
+PGT_UNROLL
+    for (int m = 0; m < 7; ++m) sasc += wgk[m] * (fabs(lo[m] - mean) + fabs(hi[m] - mean));
+    PgtGK15 o;
+    double err = fabs((kron - gauss) * h);
+    o.r = kron * h; o.rabs = sabs * fabs(h); o.rasc = sasc * fabs(h);
+    if (o.rasc != 0 && err != 0) {                       // rescale_error (err.c)
+        const double scale = pow(200 * err / o.rasc, 1.5);
+        err = scale < 1 ? o.rasc * scale : o.rasc;
+    }
+    if (o.rabs > 2.2250738585072014e-308 / (50 * 2.2204460492503131e-16)) {
+        const double floor_err = 50 * 2.2204460492503131e-16 * o.rabs;
+        if (floor_err > err) err = floor_err;
+    }
+    o.err = err;
+    return o;
+}
+
+#if defined(__CUDACC__)
+#pragma nv_exec_check_disable
+#endif
+template <class F>
+PGT_HD double pgt_qag15(F f, double a, double b, double epsabs, double epsrel, int limit, int* status)
+{
+    const double EPS = 2.2204460492503131e-16, TINY = 2.2250738585072014e-308;
+    double ia[PGT_QAG_CAP], ib[PGT_QAG_CAP], ir[PGT_QAG_CAP], ie[PGT_QAG_CAP];
+    const PgtGK15 first = pgt_gk15(f, a, b);
+    double tol = fmax(epsabs, epsrel * fabs(first.r));
+    *status = PGT_QAG_OK;
+    if (first.err <= 50 * EPS * first.rabs && first.err > tol) { *status = PGT_QAG_ROUNDOFF0; return first.r; }
+    if ((first.err <= tol && first.err != first.rasc) || first.err == 0.0) return first.r;
+    if (limit == 1) { *status = PGT_QAG_LIMIT; return first.r; }
+    ia[0] = a; ib[0] = b; ir[0] = first.r; ie[0] = first.err;
+    int n = 1, iter = 1, ro1 = 0, ro2 = 0, bad = 0;
+    double area = first.r, errsum = first.err;
+    do {
+        if (n == PGT_QAG_CAP) { *status = PGT_QAG_CAPACITY; break; }
+        int w = 0;                                       // worst interval, first of equals
+        for (int k = 1; k < n; ++k) if (ie[k] > ie[w]) w = k;
+        const double wa = ia[w], wb = ib[w], wr = ir[w], we = ie[w], mid = 0.5 * (wa + wb);
+        const PgtGK15 L = pgt_gk15(f, wa, mid), R = pgt_gk15(f, mid, wb);
+        const double area12 = L.r + R.r, err12 = L.err + R.err;
+        errsum += (err12 - we);
+        area += area12 - wr;
+        if (L.rasc != L.err && R.rasc != R.err) {
+            if (fabs(wr - area12) <= 1.0e-5 * fabs(area12) && err12 >= 0.99 * we) ++ro1;
+            if (iter >= 10 && err12 > we) ++ro2;
+        }
+        tol = fmax(epsabs, epsrel * fabs(area));
+        if (errsum > tol) {
+            if (ro1 >= 6 || ro2 >= 20) bad = 2;
+            const double small = (1 + 100 * EPS) * (fabs(mid) + 1000 * TINY);
+            if (fabs(wa) <= small && fabs(wb) <= small) bad = 3;
+        }
+        if (R.err > L.err) {                             // the worse half keeps the slot, the other is appended
+            ia[w] = mid; ir[w] = R.r; ie[w] = R.err;
+            ia[n] = wa; ib[n] = mid; ir[n] = L.r; ie[n] = L.err;
+        } else {
+            ib[w] = mid; ir[w] = L.r; ie[w] = L.err;
+            ia[n] = mid; ib[n] = wb; ir[n] = R.r; ie[n] = R.err;
+        }
+        ++n;
+        ++iter;
+    } while (iter < limit && !bad && errsum > tol);
+    double sum = 0.0;
+    for (int k = 0; k < n; ++k) sum += ir[k];
+    if (*status == PGT_QAG_CAPACITY) return sum;
+    if (errsum <= tol) *status = PGT_QAG_OK;
+    else if (bad == 2) *status = PGT_QAG_ROUNDOFF;
+    else if (bad == 3) *status = PGT_QAG_SINGULAR;
+    else if (iter == limit) *status = PGT_QAG_LIMIT;
+    else *status = PGT_QAG_FAILED;
+    return sum;
+}
+

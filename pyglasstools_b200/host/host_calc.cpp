@@ -189,7 +189,10 @@ void IrvingKirkwood::run(long long npoints)
     py::gil_scoped_release nogil;
     DeviceSession& S = DeviceSession::get();
     pgt_ctx* ctx = S.ctx();
-    S.check(pgt_cg_set(ctx, m_cg->kernel, m_cg->cg_rcut, m_cg->quad_mode, m_cg->order), "pgt_cg_set");
+    if (m_cg->quad_mode == PGT_QUAD_ADAPTIVE)
+        S.check(pgt_cg_set_adaptive(ctx, m_cg->kernel, m_cg->cg_rcut, m_cg->abserr, m_cg->relerr, m_cg->maxiter), "pgt_cg_set_adaptive");
+    else
+        S.check(pgt_cg_set(ctx, m_cg->kernel, m_cg->cg_rcut, m_cg->quad_mode, m_cg->order), "pgt_cg_set");
     prepare_device((mask & PGT_OBS_VIRIAL) != 0);
     S.check(pgt_ik_compute(ctx, mask), "pgt_ik_compute");
     for (auto& kv : m_obs) {

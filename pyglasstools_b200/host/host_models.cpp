@@ -3,6 +3,8 @@
 // pgt_cg_bond), i.e. the same source (pgt_math.cuh) the device kernels are compiled from.
 #include <cmath>
 #include <cstdio>
+#include <stdexcept>
+#include <string>
 
 #include "host_common.h"
 
@@ -57,8 +59,13 @@ double CoarseGrainFunction::getObjFunc(double s, const Vec3& x, const Vec3& ri, 
 double CoarseGrainFunction::getBondFunc(const Vec3& x, const Vec3& ri, const Vec3& rij) const
 {
     if (kernel < 0) return 0.0;
-    if (quad_mode != PGT_QUAD_FIXEDPOINT)
-        throw std::domain_error("[ERROR] adaptive (GSL QAG) bond quadrature is not implemented in pyglasstools_b200");
+    if (quad_mode != PGT_QUAD_FIXEDPOINT) {
+        int status = 0;
+        const double v = pgt_cg_bond_adaptive(kernel, cg_rcut, abserr, relerr, maxiter, x.data(), ri.data(), rij.data(), &status);
+        // GSL's default error handler aborts the reference on any of these exits (Quadrature.h:46-48)
+        if (status) throw std::runtime_error("[ERROR] gsl_integration_qag: tolerance not reached (exit code " + std::to_string(status) + ")");
+        return v * frozen_norm_ratio(*this);
+    }
     return pgt_cg_bond(kernel, cg_rcut, order, x.data(), ri.data(), rij.data()) * frozen_norm_ratio(*this);
 }
 

@@ -410,3 +410,41 @@ def test_walk_gather_on_cartesian_grids(gpu_ctx, orc, kernel, order, R, nmax, mo
     want = S.ik(P, cg, grid)["virial"]
     got = fields[5].reshape(nmax, nmax, 4)[np.ix_(ii, ii)].reshape(-1, 4)
     assert_close(got, want, scale=np.abs(want).max(axis=1, keepdims=True))
+
+
+@pytest.mark.parametrize("kernel", ["octic", "mollifier"])
+def test_adaptive_bond_quadrature_field(gpu_ctx, orc, kernel):
+    """cgfunc.<kernel>(mode="adaptive"): the device QAG / GK15 field against the oracle's restatement of
+    gsl_integration_qag (same bisection rule, so far inside the tolerance the user asked for), against the fixed
+    1024-point rule within that tolerance, and the failure exit the reference turns into an abort."""
+    fr = synth.synth_frame(24, 9)
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    rng = np.random.default_rng(5)
+    L = float(box[0])
+    pts = np.zeros((300, 3)); pts[:, :2] = rng.uniform(-L / 2, L / 2, (300, 2))
+    gpu_ctx.set_grid_points(pts)
+    gpu_ctx.set_cg_adaptive(kernel, 2.0, relerr=1e-9, abserr=1e-11, maxiter=100)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_DENSITY)
+    got = gpu_ctx.ik_download()
+    rho = gpu_ctx.ik_download(_capi.FIELD_DENSITY)
+    want = S.ik(P, orc.cgfunc_adaptive(kernel, 2.0, 1e-9, 1e-11, 100), pts, obs_mask=1 | 4)
+    scale = np.abs(want["virial"]).max(axis=1, keepdims=True)
+    assert_close(got, want["virial"], scale=scale)
+    assert_close(rho, want["density"], scale=np.abs(want["density"]).max())
+    fixed = S.ik(P, orc.cgfunc(kernel, 2.0, 1024), pts)["virial"]
+    assert np.all(np.abs(got - fixed) <= 1e-6 * scale + 1e-8)
+    # Cartesian grids take the same kernel
+    axis = synth.linspace_axis(L, 20)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    grid = np.zeros((400, 3)); grid[:, 0] = np.repeat(axis, 20); grid[:, 1] = np.tile(axis, 20)
+    wantg = S.ik(P, orc.cgfunc_adaptive(kernel, 2.0, 1e-9, 1e-11, 100), grid)["virial"]
+    assert_close(gpu_ctx.ik_download(), wantg, scale=np.abs(wantg).max(axis=1, keepdims=True))
+    # two intervals cannot reach 1e-13: GSL_EMAXITER -> the reference aborts, we return an error
+    gpu_ctx.set_cg_adaptive(kernel, 2.0, relerr=1e-13, abserr=1e-300, maxiter=2)
+    with pytest.raises(_capi.PgtError):
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    gpu_ctx.set_cg("octic", 2.0, 5)

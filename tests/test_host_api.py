@@ -174,9 +174,16 @@ def test_cg_getters_match_reference_headers(kernel):
     xs, ws = np.polynomial.legendre.leggauss(5)
     quad = sum(0.5 * w * f.get_objfunc(0.5 + 0.5 * t, x, ri, rij) for t, w in zip(xs, ws))
     assert f.get_bondfunc(x, ri, rij) == pytest.approx(quad, rel=1e-14)
+    # adaptive mode = GSL QAG with the 15-point Gauss-Kronrod pair (Quadrature.h:39-51): agrees with a high-order
+    # fixed rule to the requested tolerance (the rect kernel is discontinuous: QAG's own error estimate bounds it)
     a = getattr(cgfunc, kernel)(rcut=2.0, mode="adaptive", relerr=1e-8, abserr=1e-10, maxiter=100)
-    with pytest.raises(ValueError):
-        a.get_bondfunc(x, ri, rij)                                   # constructible, but QAG is not implemented
+    xs, ws = np.polynomial.legendre.leggauss(400)
+    fine = sum(0.5 * w * f.get_objfunc(0.5 + 0.5 * t, x, ri, rij) for t, w in zip(xs, ws))
+    assert a.get_bondfunc(x, ri, rij) == pytest.approx(fine, rel=1e-3 if kernel == "rect" else 1e-7, abs=1e-10)
+    tight = getattr(cgfunc, kernel)(rcut=2.0, mode="adaptive", relerr=1e-13, abserr=1e-300, maxiter=2)
+    if kernel != "rect":
+        with pytest.raises(RuntimeError):
+            tight.get_bondfunc([0.0, 0.0, 0.0], [1.5, 0.0, 0.0], [1.0, 0.2, 0.0])     # GSL_EMAXITER: the reference aborts here
 
 
 def test_mollifier_norm_is_frozen_at_construction():

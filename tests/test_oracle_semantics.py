@@ -192,3 +192,52 @@ def test_thermo_divides_everything_by_volume(orc):
     assert t["npairs"] == 1
     assert t["energy"] == tab["energy"][0] * (1 / 80.0)
     assert t["virial"][0] == tab["fdivr"][0] * 1.0 * 1.0 * (1 / 80.0)
+
+
+def test_qag_restatement_known_answers(orc):
+    """GSL QAG (key 1 = 15-point Gauss-Kronrod), restated in the oracle because GSL is not vendored: the Kronrod rule is
+    exact to degree 22 and its embedded Gauss rule is numpy's 7-point rule; closed-form integrals are met within the
+    requested tolerance and the reported error bounds the true one; the failure exits are GSL's."""
+    import math
+    xgk, wg, wgk = orc.gk15_tables()
+    xs = np.concatenate([-xgk[:7], [0.0], xgk[:7][::-1]])
+    ws = np.concatenate([wgk[:7], [wgk[7]], wgk[:7][::-1]])
+    for d in range(0, 23, 2):
+        assert abs((ws * xs ** d).sum() - 2.0 / (d + 1)) < 5e-16
+    assert abs((ws * xs ** 24).sum() - 2.0 / 25) > 1e-10
+    gx, gw = np.polynomial.legendre.leggauss(7)
+    assert np.allclose(np.sort(np.abs(gx))[::-1][::2], xgk[1::2], rtol=0, atol=1e-15)
+    assert np.allclose(np.sort(gw)[::2], wg, rtol=0, atol=1e-15)
+    cases = [(0, 0.0, 1.0, math.e - 1), (1, -1.0, 1.0, 0.4 * math.atan(5.0)), (2, -1.0, 2.0, 2.0 / 3 * (1 + 2 ** 1.5)),
+             (3, 0.0, 1.0, 0.3), (4, 0.0, 1.0, math.sin(40.0) / 40)]
+    for which, a, b, exact in cases:
+        v, status, abserr = orc.qag_test(which, a, b, 1e-10, 1e-10, 200)
+        assert status == 0 and abs(v - exact) <= max(abserr, 1e-15) <= 1e-9
+    v, status, _ = orc.qag_test(2, -1.0, 2.0, 1e-14, 1e-14, 3)
+    assert status == 2                                               # GSL_EMAXITER
+    v, status, _ = orc.qag_test(0, 0.0, 1.0, 1e-10, 1e-10, 1)
+    assert status == 0 and abs(v - (math.e - 1)) < 1e-14           # smooth: the first GK15 pair already converges
+
+
+def test_adaptive_bond_function_oracle_vs_library_host_and_fixed_rule(orc):
+    """AdaptiveCGFunc::getBondFunc: the oracle's QAG and the library's host-side QAG (pgt_cg_bond_adaptive) are two
+    separate restatements of the same published algorithm and agree to rounding; both agree with a 1024-point fixed rule
+    within the tolerance (1024 nodes: the integrand has a kink where the bond leaves the disc)."""
+    import ctypes as C
+    from pyglasstools_b200 import _capi
+    L = orc.lib()
+    L.orc_bond.restype = C.c_double
+    rng = np.random.default_rng(11)
+    for kernel in ("octic", "mollifier"):
+        cga = orc.cgfunc_adaptive(kernel, 2.0, 1e-9, 1e-11, 100)
+        cgf = orc.cgfunc(kernel, 2.0, 1024)
+        for _ in range(40):
+            x = np.array([*rng.uniform(-1, 1, 2), 0.0])
+            ri = np.array([*rng.uniform(-2, 2, 2), 0.0])
+            rij = np.array([*rng.uniform(-1.5, 1.5, 2), 0.0])
+            p = lambda v: v.ctypes.data_as(C.c_void_p)
+            want = L.orc_bond(C.byref(cga), p(x), p(ri), p(rij))
+            got, status = _capi.cg_bond_adaptive(kernel, 2.0, 1e-9, 1e-11, 100, x, ri, rij)
+            assert status == 0 and got == pytest.approx(want, rel=1e-13, abs=1e-16)
+            fixed = L.orc_bond(C.byref(cgf), p(x), p(ri), p(rij))
+            assert got == pytest.approx(fixed, rel=1e-6, abs=1e-9)
