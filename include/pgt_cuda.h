@@ -41,9 +41,10 @@ enum { PGT_CG_OCTIC = 0, PGT_CG_RECT = 1, PGT_CG_MOLLIFIER = 2 };
 enum { PGT_QUAD_FIXEDPOINT = 0, PGT_QUAD_ADAPTIVE = 1 };
 /* observable masks */
 enum { PGT_OBS_VIRIAL = 1u, PGT_OBS_KINETIC = 2u, PGT_OBS_DENSITY = 4u,      /* IK fields */
-       PGT_OBS_ENERGY = 8u, PGT_OBS_BORN = 16u };                           /* thermo only */
+       PGT_OBS_ENERGY = 8u, PGT_OBS_BORN = 16u,                             /* thermo only */
+       PGT_OBS_ELASTIC = 32u };                                             /* IK field (needs displacements) */
 /* observable ids for downloads */
-enum { PGT_FIELD_VIRIAL = 0, PGT_FIELD_KINETIC = 1, PGT_FIELD_DENSITY = 2 };
+enum { PGT_FIELD_VIRIAL = 0, PGT_FIELD_KINETIC = 1, PGT_FIELD_DENSITY = 2, PGT_FIELD_ELASTIC = 3 };
 /* stage ids for pgt_stage_time_ms */
 enum { PGT_STAGE_UPLOAD = 0, PGT_STAGE_CELLS = 1, PGT_STAGE_BONDS = 2, PGT_STAGE_IK = 3, PGT_STAGE_THERMO = 4,
        PGT_STAGE_DOWNLOAD = 5, PGT_STAGE_COUNT = 6 };
@@ -121,6 +122,13 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
  * then Dim^4 Born tensor (col-major flat); all already multiplied by 1/vol.  Entries whose
  * observable is not in obs_mask are 0.  out must hold 2*Dim^2 + 1 + Dim^4 doubles.              */
 int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out);
+/* Replaces: ParticleSystem::setDisplacement (ParticleSystem.cc:60-67): N x 3 doubles, one row per particle of the frame
+ * last uploaded, in the frame's own order.  A new frame starts with zero displacements (ParticleSystem.cc:28).   */
+int pgt_frame_set_displacement(pgt_ctx* ctx, const double* disp_xyz, int64_t N);
+/* Replaces: GlobalElasticVirialStress (ListofCommonObservables.h:86-123 through ThermoCalculator::compute): the
+ * Dim^2 sums of F1 (x) (u+r) - F (x) r over pairs id_i < id_j within max_rcut, times 1/vol.  The field version is
+ * pgt_ik_compute with PGT_OBS_ELASTIC, read back as PGT_FIELD_ELASTIC.                                            */
+int pgt_thermo_elastic(pgt_ctx* ctx, double* out /* Dim^2 */);
 
 /* ---- parity exports / instrumentation ------------------------------------------------------ */
 /* Ordered force-carrying pairs (orig_i, orig_j) and r_ij = r_i - r_j(image) as the reference's

@@ -307,6 +307,36 @@ class System:
         return dict(virial=vir, kinetic=kin, born=bt, energy=en[0], npairs=int(npairs[0]))
 
 
+    def set_displacement(self, disp):
+        """ParticleSystem::setDisplacement: N x 3 rows in ORIGINAL particle order (None clears)."""
+        L = lib()
+        L.orc_system_set_displacement.argtypes = [C.c_void_p, C.c_void_p]
+        L.orc_system_set_displacement.restype = None
+        d = None if disp is None else np.ascontiguousarray(disp, np.float64)
+        L.orc_system_set_displacement(self.h, None if d is None else d.ctypes.data)
+
+    def thermo_elastic(self, P, max_rcut=None):
+        """GlobalElasticVirialStress (ListofCommonObservables.h:86-123 in ThermoCalculator::compute), times 1/vol."""
+        L = lib()
+        L.orc_thermo_elastic.argtypes = [C.c_void_p, C.POINTER(OrcPot), C.c_double, C.c_void_p]
+        L.orc_thermo_elastic.restype = None
+        out = np.zeros(self.dim * self.dim)
+        mr = self.max_rcut(P) if max_rcut is None else max_rcut
+        L.orc_thermo_elastic(self.h, C.byref(P), mr, out.ctypes.data)
+        return out
+
+    def ik_elastic(self, P, cg, grid, max_rcut=None):
+        """ElasticVirialStressField through IrvingKirkwood::compute."""
+        L = lib()
+        L.orc_ik_elastic.argtypes = [C.c_void_p, C.POINTER(OrcPot), C.POINTER(OrcCG), C.c_double, C.c_int64, C.c_void_p, C.c_void_p]
+        L.orc_ik_elastic.restype = None
+        grid = np.ascontiguousarray(grid, np.float64)
+        out = np.zeros((len(grid), self.dim * self.dim))
+        mr = self.max_rcut(P) if max_rcut is None else max_rcut
+        L.orc_ik_elastic(self.h, C.byref(P), C.byref(cg), mr, len(grid), grid.ctypes.data, out.ctypes.data)
+        return out
+
+
 def cartesian_grid(L, dx):
     """ikcalculator grid (irvingkirkwood/__init__.py:45-53): i-major, both ends included."""
     nmax = int(L / dx)

@@ -483,6 +483,7 @@ struct OrcSystem {
     int periodic[3];
     int64_t n;                       // live particles
     std::vector<double> pos, vel, diam, mass;   // pos/vel: n*3
+    std::vector<double> disp;                  // n*3, zero until set (ParticleSystem.cc:28, setDisplacement :60-67)
     std::vector<int64_t> id;         // original index of each live particle
     // uniform search grid over x,y (z is a single slab)
     int ncx, ncy; double cw[2];
@@ -777,6 +778,74 @@ ORC_API void orc_thermo_compute(const OrcSystem* S, const OrcPot* P, double max_
     if (born) for (int q = 0; q < Dim * Dim * Dim * Dim; ++q) born[q] = bt[q] * invvol;
     if (energy) energy[0] = en * invvol;
     if (npairs) npairs[0] = np;
+}
+
+// ------------------------------------------------------------ ElasticVirialStress (ListofCommonObservables.h:86-123)
+// ParticleSystem::setDisplacement (ParticleSystem.cc:60-67): one row per ORIGINAL particle.
+ORC_API void orc_system_set_displacement(OrcSystem* S, const double* disp)
+{
+    S->disp.assign((size_t)3 * S->n, 0.0);
+    if (!disp) return;
+    for (int64_t i = 0; i < S->n; ++i)
+        for (int d = 0; d < 3; ++d) S->disp[3 * i + d] = disp[3 * S->id[i] + d];
+}
+
+// ElasticVirialStress::compute: val(a,b) += F1[a] (uij+rij)[b] - F[a] rij[b],  uij = disp_j - disp_i,
+// F = fdivr(rij) rij, F1 = fdivr(uij + rij) (uij + rij)
+static inline void orc_elastic_pair(const OrcSystem* S, const OrcPot* P, int64_t i, int64_t j, const double* rij, int Dim, double* tmp)
+{
+    const double* ui = S->disp.empty() ? nullptr : &S->disp[3 * i];
+    const double* uj = S->disp.empty() ? nullptr : &S->disp[3 * j];
+    double uij[3] = { 0, 0, 0 };
+    if (ui) for (int d = 0; d < 3; ++d) uij[d] = uj[d] - ui[d];
+    const double w[3] = { uij[0] + rij[0], uij[1] + rij[1], uij[2] + rij[2] };
+    const double di = S->diam[i], dj = S->diam[j];
+    const double forceval = orc_model_eval(*P, orc_dot3(rij, rij), di, dj, 1);
+    const double forceval1 = orc_model_eval(*P, orc_dot3(w, w), di, dj, 1);
+    const double F[3] = { forceval * rij[0], forceval * rij[1], forceval * rij[2] };
+    const double F1[3] = { forceval1 * w[0], forceval1 * w[1], forceval1 * w[2] };
+    for (int b = 0; b < Dim; ++b) for (int a = 0; a < Dim; ++a) tmp[a + Dim * b] += F1[a] * (uij[b] + rij[b]) - F[a] * rij[b];
+}
+
+// GlobalElasticVirialStress: ThermoCalculator::compute (ThermoCalculator.h:68-90), rij = +dx
+ORC_API void orc_thermo_elastic(const OrcSystem* S, const OrcPot* P, double max_rcut, double* out)
+{
+    const int Dim = S->dim;
+    double val[9] = { 0 };
+    for (int64_t i = 0; i < S->n; ++i)
+        orc_search(*S, &S->pos[3 * i], max_rcut, [&](int64_t j, const double* dx) {
+            if (!(S->id[i] < S->id[j])) return;
+            const double rij[3] = { dx[0], dx[1], dx[2] };
+            orc_elastic_pair(S, P, i, j, rij, Dim, val);
+        });
+    const double invvol = 1 / S->vol;
+    for (int q = 0; q < Dim * Dim; ++q) out[q] = val[q] * invvol;
+}
+
+// ElasticVirialStressField: IrvingKirkwood::compute (IrvingKirkwood.h:74-110) hands the functor rij = -dx (:100), so
+// the displaced separation it evaluates is  (disp_j - disp_i) + (r_i - r_j)  -- reproduced as written.
+ORC_API void orc_ik_elastic(const OrcSystem* S, const OrcPot* P, const OrcCG* cg, double max_rcut, int64_t G, const double* grid,
+                            double* out)
+{
+    const int Dim = S->dim;
+    const OrcGL gl = orc_make_gl(cg->adaptive ? 1 : cg->order);
+#pragma omp parallel for schedule(dynamic, 64)
+    for (int64_t g = 0; g < G; ++g) {
+        const double* x = grid + 3 * g;
+        double val[9] = { 0 };
+        orc_search(*S, x, cg->rcut, [&](int64_t i, const double* dr) {
+            const double ri[3] = { x[0] - dr[0], x[1] - dr[1], x[2] - dr[2] };
+            orc_search(*S, &S->pos[3 * i], max_rcut, [&](int64_t j, const double* dxj) {
+                if (S->id[i] == S->id[j]) return;
+                const double rij[3] = { -dxj[0], -dxj[1], -dxj[2] };
+                const double bondval = orc_bond_any(cg, gl, x, ri, rij, nullptr);
+                double tmp[9] = { 0 };                          // compute_cg: zeroed temporary, then 0.5 bondval tmp
+                orc_elastic_pair(S, P, i, j, rij, Dim, tmp);
+                for (int q = 0; q < Dim * Dim; ++q) val[q] += 0.5 * bondval * tmp[q];
+            });
+        });
+        for (int q = 0; q < Dim * Dim; ++q) out[g * Dim * Dim + q] = val[q];
+    }
 }
 
 ORC_API int orc_num_threads(void)

@@ -14,13 +14,13 @@ LIB_PATH = os.path.join(_HERE, "libpgt_cuda.so")
 POT_IDS = {"lj": 0, "forceshifted-lj": 1, "poly12": 2, "poly18": 3, "poly10": 4, "poly106": 5, "polyyukawa": 6,
            "polylj": 7}
 CG_IDS = {"octic": 0, "rect": 1, "mollifier": 2}
-OBS_VIRIAL, OBS_KINETIC, OBS_DENSITY, OBS_ENERGY, OBS_BORN = 1, 2, 4, 8, 16
-FIELD_VIRIAL, FIELD_KINETIC, FIELD_DENSITY = 0, 1, 2
+OBS_VIRIAL, OBS_KINETIC, OBS_DENSITY, OBS_ENERGY, OBS_BORN, OBS_ELASTIC = 1, 2, 4, 8, 16, 32
+FIELD_VIRIAL, FIELD_KINETIC, FIELD_DENSITY, FIELD_ELASTIC = 0, 1, 2, 3
 STAGES = {"upload": 0, "cells": 1, "bonds": 2, "ik": 3, "thermo": 4, "download": 5}
 
 EXPORTED = [
     "pgt_ctx_create", "pgt_ctx_destroy", "pgt_last_error", "pgt_device_count", "pgt_synchronize", "pgt_stream",
-    "pgt_potential_set", "pgt_cg_set", "pgt_cg_set_adaptive", "pgt_cg_bond_adaptive", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
+    "pgt_frame_set_displacement", "pgt_thermo_elastic", "pgt_potential_set", "pgt_cg_set", "pgt_cg_set_adaptive", "pgt_cg_bond_adaptive", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
     "pgt_frame_set_device", "pgt_build_cells", "pgt_build_bonds", "pgt_frame_counts", "pgt_grid_set_cartesian",
     "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_download_async", "pgt_ik_download_wait", "pgt_ik_device_ptr",
     "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
@@ -93,6 +93,8 @@ def lib():
         L.pgt_ik_download.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.pgt_ik_device_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pgt_thermo_compute.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
+        L.pgt_thermo_elastic.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
+        L.pgt_frame_set_displacement.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int64]
         L.pgt_export_bonds.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p,
                                        C.c_void_p]
         L.pgt_export_neighbors.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p]
@@ -242,6 +244,16 @@ class Context:
         out = np.zeros(25, np.float64)
         self._ck(lib().pgt_thermo_compute(self._h, int(obs_mask), _dp(out)))
         return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy())
+
+    def set_displacement(self, disp):
+        """ParticleSystem::setDisplacement: N x 3 rows in the uploaded frame's particle order."""
+        d = np.ascontiguousarray(disp, np.float64).reshape(-1, 3)
+        self._ck(lib().pgt_frame_set_displacement(self._h, _dp(d), C.c_int64(len(d))))
+
+    def thermo_elastic(self):
+        out = np.zeros(4, np.float64)
+        self._ck(lib().pgt_thermo_elastic(self._h, _dp(out)))
+        return out
 
     # exports ----------------------------------------------------------------
     def export_bonds(self):

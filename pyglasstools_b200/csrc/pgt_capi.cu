@@ -149,7 +149,9 @@ struct pgt_ctx {
     DevBuf gxs, gys, gpts;
 
     // outputs
-    DevBuf out_virial, out_kinetic, out_density;
+    DevBuf out_virial, out_kinetic, out_density, out_elastic;
+    DevBuf disp;                 // N x 3 displacements, original particle order
+    bool have_disp = false;
     unsigned last_ik_mask = 0;
     DevBuf thermo_partials, thermo_out;
     double* h_small = nullptr;   // mapped page-locked scratch for small read-backs (written by k_publish)
@@ -322,7 +324,8 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
                        &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->nb_list, &ctx->gxs, &ctx->gys, &ctx->gpts,
-                       &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->thermo_partials, &ctx->thermo_out,
+                       &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->out_elastic, &ctx->disp, &ctx->thermo_partials,
+                       &ctx->thermo_out,
                        &ctx->comm_scratch };
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
@@ -499,6 +502,7 @@ int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void
     ctx->src_diam = ctx->raw_diam.p;
     ctx->src_mass = nullptr;
     ctx->src_vel = nullptr;
+    ctx->have_disp = false;
     if (mass) {
         ENSURE(ctx->raw_mass, (size_t)N * es);
         CK(cudaMemcpyAsync(ctx->raw_mass.p, mass, (size_t)N * es, cudaMemcpyHostToDevice, ctx->stream));
@@ -523,6 +527,7 @@ int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, co
     ctx->src_diam = d_diam;
     ctx->src_mass = d_mass;
     ctx->src_vel = d_vel;
+    ctx->have_disp = false;
     return PGT_OK;
 }
 
@@ -720,6 +725,7 @@ int pgt_grid_set_shard(pgt_ctx* ctx, int64_t g0, int64_t g1)
 
 // ---------------------------------------------------------------------------------- compute
 static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask);
+static int ensure_disp(pgt_ctx* ctx);
 #define ik_args ik_args_impl
 int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
 {
@@ -728,7 +734,8 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if ((obs_mask & PGT_OBS_VIRIAL) && !ctx->bonds_built) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: bonds not built");
     if (!ctx->have_cg) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no coarse-graining function");
     if (ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no grid");
-    if (!(obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_KINETIC | PGT_OBS_DENSITY))) return fail(ctx, PGT_ERR_ARG, "pgt_ik_compute: empty observable mask");
+    if (!(obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_KINETIC | PGT_OBS_DENSITY | PGT_OBS_ELASTIC))) return fail(ctx, PGT_ERR_ARG, "pgt_ik_compute: empty observable mask");
+    if ((obs_mask & PGT_OBS_ELASTIC) && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no pair potential");
     if (ctx->cg.rcut >= ctx->box.L[0] || ctx->cg.rcut >= ctx->box.L[1])
         return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
     CK(cudaSetDevice(ctx->device));
@@ -737,6 +744,11 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if (obs_mask & PGT_OBS_VIRIAL) ENSURE(ctx->out_virial, sizeof(double) * 4 * n);
     if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 4 * n);
     if (obs_mask & PGT_OBS_DENSITY) ENSURE(ctx->out_density, sizeof(double) * n);
+    if (obs_mask & PGT_OBS_ELASTIC) {
+        ENSURE(ctx->out_elastic, sizeof(double) * 4 * n);
+        const int rc = ensure_disp(ctx);
+        if (rc != PGT_OK) return rc;
+    }
 
     if (ctx->dl_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_dl_done, 0));   // the field buffers are still being read back
     stage_begin(ctx, PGT_STAGE_IK);
@@ -745,9 +757,18 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
         ctx->hb_cscale = 1.0 / ctx->cg.rcutsq;
         pgt_launch_rescale_bonds(ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->n_hb, ctx->hb_cscale, ctx->stream, &ctx->launches);
     }
+    const unsigned mask_all = obs_mask;
+    obs_mask &= ~PGT_OBS_ELASTIC;
     PgtIKArgs a = ik_args(ctx, obs_mask);
     bool check_qag = false;
-    if (ctx->quad_mode == PGT_QUAD_ADAPTIVE && (obs_mask & PGT_OBS_VIRIAL)) {
+    if (gl > 0 && (mask_all & PGT_OBS_ELASTIC)) {
+        const bool adaptive = ctx->quad_mode == PGT_QUAD_ADAPTIVE;
+        if (adaptive) { CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream)); check_qag = true; }
+        CK(pgt_launch_ik_elastic(ctx->pot, a, ctx->disp.as<double>(), ctx->max_rcut, adaptive ? 1 : 0, ctx->out_elastic.as<double>(),
+                                 ctx->eflags.as<int>(), ctx->stream, &ctx->launches));
+    }
+    if (obs_mask == 0) {
+    } else if (ctx->quad_mode == PGT_QUAD_ADAPTIVE && (obs_mask & PGT_OBS_VIRIAL)) {
         // local observables only need Delta(): the regular kernel; the virial field: the QAG kernel
         if (gl > 0 && (obs_mask & ~PGT_OBS_VIRIAL)) {
             PgtIKArgs al = a;
@@ -755,7 +776,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
             CK(pgt_launch_ik(al, 2, ctx->stream, &ctx->launches));
         }
         if (gl > 0) {
-            CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
+            if (!check_qag) CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
             CK(pgt_launch_ik_adaptive(a, ctx->eflags.as<int>(), ctx->stream, &ctx->launches));
             check_qag = true;
         }
@@ -771,7 +792,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
             return fail(ctx, PGT_ERR_DATA, "adaptive bond quadrature did not reach the tolerance within maxiter = %d intervals "
                         "(GSL's error handler aborts the reference here)", ctx->qag_limit);
     }
-    ctx->last_ik_mask = obs_mask;
+    ctx->last_ik_mask = mask_all;
     return PGT_OK;
 }
 
@@ -888,6 +909,7 @@ static int field_info(pgt_ctx* ctx, int field_id, DevBuf** buf, int* ncomp)
     case PGT_FIELD_VIRIAL: *buf = &ctx->out_virial; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_VIRIAL) ? 0 : -1;
     case PGT_FIELD_KINETIC: *buf = &ctx->out_kinetic; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_KINETIC) ? 0 : -1;
     case PGT_FIELD_DENSITY: *buf = &ctx->out_density; *ncomp = 1; return (ctx->last_ik_mask & PGT_OBS_DENSITY) ? 0 : -1;
+    case PGT_FIELD_ELASTIC: *buf = &ctx->out_elastic; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_ELASTIC) ? 0 : -1;
     }
     return -2;
 }
@@ -965,6 +987,52 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
     const double* h = ctx->h_small;
     // device order: virial 4 | kinetic 4 | energy | born 16  ->  API order (same, documented in the header)
     for (int k = 0; k < 25; ++k) out[k] = h[k];
+    return PGT_OK;
+}
+
+static int ensure_disp(pgt_ctx* ctx)
+{
+    const size_t bytes = sizeof(double) * 3 * (size_t)std::max<long long>(ctx->N, 1);
+    if (!ctx->have_disp) {                                   // ParticleSystem.cc:28: displacement = 0 until set
+        ENSURE(ctx->disp, bytes);
+        CK(cudaMemsetAsync(ctx->disp.p, 0, bytes, ctx->stream));
+        ctx->have_disp = true;
+    }
+    return PGT_OK;
+}
+
+int pgt_frame_set_displacement(pgt_ctx* ctx, const double* disp_xyz, int64_t N)
+{
+    if (!ctx || (!disp_xyz && N > 0)) return fail(ctx, PGT_ERR_ARG, "pgt_frame_set_displacement: null argument");
+    if (N != ctx->N) return fail(ctx, PGT_ERR_ARG, "displacement has %lld rows, the frame has %lld particles", (long long)N, (long long)ctx->N);
+    CK(cudaSetDevice(ctx->device));
+    const size_t bytes = sizeof(double) * 3 * (size_t)std::max<long long>(N, 1);
+    ENSURE(ctx->disp, bytes);
+    if (N > 0) CK(cudaMemcpyAsync(ctx->disp.p, disp_xyz, sizeof(double) * 3 * (size_t)N, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));                  // the caller's buffer may be pageable and short-lived
+    ctx->have_disp = true;
+    return PGT_OK;
+}
+
+int pgt_thermo_elastic(pgt_ctx* ctx, double* out)
+{
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_elastic: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: cells not built");
+    if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: no pair potential");
+    CK(cudaSetDevice(ctx->device));
+    int rc = ensure_disp(ctx);
+    if (rc != PGT_OK) return rc;
+    const int blocks = pgt_thermo_blocks(ctx->n_live);
+    ENSURE(ctx->thermo_partials, sizeof(double) * 25 * (size_t)blocks);
+    ENSURE(ctx->thermo_out, sizeof(double) * 32);
+    stage_begin(ctx, PGT_STAGE_THERMO);
+    pgt_launch_thermo_elastic(ctx->pot, frame_view(ctx), ctx->box, ctx->cells, ctx->max_rcut, ctx->disp.as<double>(), 1 / ctx->vol,
+                              ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    stage_end(ctx, PGT_STAGE_THERMO);
+    pgt_launch_publish(ctx->thermo_out.p, 8, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int k = 0; k < 4; ++k) out[k] = ctx->h_small[k];
     return PGT_OK;
 }
 

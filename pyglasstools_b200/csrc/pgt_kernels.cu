@@ -1022,6 +1022,156 @@ cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t
 }
 
 // ------------------------------------------------------------------------------------------
+// ElasticVirialStress (ListofCommonObservables.h:86-123): val(a,b) += F1[a] w[b] - F[a] r[b] with r the pair separation the
+// caller hands in, w = (disp_j - disp_i) + r, F = fdivr(|r|) r, F1 = fdivr(|w|) w.  Pairs are ALL neighbours within max_rcut
+// (a pair beyond its own cut-off at r may carry force at w), so these kernels run the neighbour search themselves
+// instead of reading the half-bond list.  Displacements are rows of the ORIGINAL particle order (setDisplacement).
+template <int MODEL>
+__device__ __forceinline__ void elastic_pair(const PgtPot& pot, double rx, double ry, double ux, double uy, double uz, double di,
+                                             double dj, double& sxx, double& syx, double& sxy, double& syy)
+{
+    const double wx = ux + rx, wy = uy + ry;
+    const double f = pgt_pair_eval_t<MODEL>(pot, rx * rx + ry * ry, di, dj, PGT_WANT_FDIVR);
+    const double f1 = pgt_pair_eval_t<MODEL>(pot, wx * wx + wy * wy + uz * uz, di, dj, PGT_WANT_FDIVR);
+    const double Fx = f * rx, Fy = f * ry, Gx = f1 * wx, Gy = f1 * wy;
+    sxx = Gx * wx - Fx * rx;        // index a + 2 b
+    syx = Gy * wx - Fy * rx;
+    sxy = Gx * wy - Fx * ry;
+    syy = Gy * wy - Fy * ry;
+}
+
+// GlobalElasticVirialStress: pairs id_i < id_j, r = +dx (ThermoCalculator.h:81-84); per-block partials of 4 sums
+template <int MODEL>
+__global__ void __launch_bounds__(THERMO_THREADS) k_thermo_elastic(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
+                                                                   const double* __restrict__ disp, double* __restrict__ partials)
+{
+    __shared__ double red[THERMO_THREADS / 32][4];
+    double acc[4] = { 0.0, 0.0, 0.0, 0.0 };
+    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < fr.n; p += gridDim.x * blockDim.x) {
+        const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+        const int oi = fr.sorig[p];
+        const double uix = disp[3 * (size_t)oi], uiy = disp[3 * (size_t)oi + 1], uiz = disp[3 * (size_t)oi + 2];
+        for_each_neighbor(fr, box, cells, p, xi, yi, rc2, [&](int q, double dx, double dy, double) {
+            const int oj = __ldg(fr.sorig + q);
+            if (!(oi < oj)) return;
+            double sxx, syx, sxy, syy;
+            elastic_pair<MODEL>(pot, dx, dy, disp[3 * (size_t)oj] - uix, disp[3 * (size_t)oj + 1] - uiy, disp[3 * (size_t)oj + 2] - uiz,
+                                di, __ldg(fr.sd + q), sxx, syx, sxy, syy);
+            acc[0] += sxx; acc[1] += syx; acc[2] += sxy; acc[3] += syy;
+        });
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const double s = warp_sum(acc[k]);
+        if (lane == 0) red[w][k] = s;
+    }
+    __syncthreads();
+    if (threadIdx.x < 4) {
+        double s = 0.0;
+        for (int ww = 0; ww < THERMO_THREADS / 32; ++ww) s += red[ww][threadIdx.x];
+        partials[(size_t)blockIdx.x * 4 + threadIdx.x] = s;
+    }
+}
+
+__global__ void __launch_bounds__(128) k_sum_partials4(const double* __restrict__ partials, int nblocks, double scale, double* __restrict__ out)
+{
+    const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    double s = 0.0;
+    for (int b = lane; b < nblocks; b += 32) s += partials[(size_t)b * 4 + k];
+    s = warp_sum(s);
+    if (lane == 0) out[k] = s * scale;                    // val * (1/vol)
+}
+
+void pgt_launch_thermo_elastic(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, const double* disp,
+                               double inv_vol, double* partials, int blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    const double rc2 = max_rcut * max_rcut;
+    PGT_DISPATCH_MODEL(pot.model, (k_thermo_elastic<M><<<blocks, THERMO_THREADS, 0, st>>>(pot, fr, box, cells, rc2, disp, partials)));
+    k_sum_partials4<<<1, 128, 0, st>>>(partials, blocks, inv_vol, out_dev);
+    lc->n += 2;
+}
+
+// ElasticVirialStressField: the reference's loop (IrvingKirkwood.h:80-107), one thread per grid point.  The functor
+// receives r = -dx there (:100), so w = (disp_j - disp_i) - dx: reproduced as written.  Fixed-point or adaptive rule.
+template <int MODEL>
+__global__ void __launch_bounds__(128) k_ik_elastic(const PgtPot pot, const PgtIKArgs A, const double* __restrict__ disp, double rc2,
+                                                    int adaptive, double* __restrict__ out, int* __restrict__ eflags)
+{
+    const long long g = A.grid.g0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= A.grid.g1) return;
+    double gx, gy;
+    if (A.grid.mode == 0) { gx = A.grid.xs[g / A.grid.ny]; gy = A.grid.ys[g % A.grid.ny]; }
+    else { gx = A.grid.pts[3 * g]; gy = A.grid.pts[3 * g + 1]; }
+    const PgtFrameView& fr = A.fr;
+    const PgtCG cg = A.cg;
+    const double R = cg.rcut, R2 = cg.rcutsq;
+    const int ncx = A.cells.ncx, ncy = A.cells.ncy;
+    const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
+    const int ux0 = max(__double2int_rd((gx - R - padx - A.box.lo[0]) * A.cells.inv_cwx), -ncx);
+    const int ux1 = min(__double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx), 2 * ncx - 1);
+    const int uy0 = max(__double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy), -ncy);
+    const int uy1 = min(__double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy), 2 * ncy - 1);
+    Seg seg[3];
+    const int nseg = split_segments(ux0, ux1, ncx, seg);
+    double vxx = 0.0, vyx = 0.0, vxy = 0.0, vyy = 0.0;
+    int bad = 0;
+    for (int uy = uy0; uy <= uy1; ++uy) {
+        int ky = 0, row = uy;
+        if (uy < 0) { ky = +1; row += ncy; } else if (uy >= ncy) { ky = -1; row -= ncy; }
+        const double cpy = gy + ky * A.box.L[1];
+        for (int s = 0; s < nseg; ++s) {
+            const double cpx = gx + seg[s].k * A.box.L[0];
+            const int qb = fr.cell_start[row * ncx + seg[s].c0], qe = fr.cell_start[row * ncx + seg[s].c1 + 1];
+            for (int p = qb; p < qe; ++p) {
+                const double ax = fr.sx[p] - cpx, ay = fr.sy[p] - cpy;
+                if (ax * ax + ay * ay > R2) continue;
+                const double di = fr.sd[p];
+                const int oi = fr.sorig[p];
+                const double uix = disp[3 * (size_t)oi], uiy = disp[3 * (size_t)oi + 1], uiz = disp[3 * (size_t)oi + 2];
+                for_each_neighbor(fr, A.box, A.cells, p, fr.sx[p], fr.sy[p], rc2, [&](int q, double dx, double dy, double) {
+                    // bond function along r_i -> r_j (the reference reflects both vectors through x: same norms)
+                    double B;
+                    if (adaptive) {
+                        int st = 0;
+                        B = pgt_qag15([&](double t) {
+                            const double px = ax + t * dx, py = ay + t * dy;
+                            return pgt_cg_delta_exact(cg, px * px + py * py);
+                        }, 0.0, 1.0, A.qag_epsabs, A.qag_epsrel, A.qag_limit, &st);
+                        if (st) bad |= (st == PGT_QAG_CAPACITY) ? PGT_EFLAG_QAG_CAPACITY : PGT_EFLAG_QAG_FAILED;
+                    } else {
+                        B = 0.0;
+                        for (int k = 0; k < A.nq; ++k) {
+                            const double t = c_gl_s[k], px = ax + t * dx, py = ay + t * dy;
+                            B += c_gl_w[k] * pgt_cg_delta_exact(cg, px * px + py * py);
+                        }
+                    }
+                    const int oj = __ldg(fr.sorig + q);
+                    double sxx, syx, sxy, syy;
+                    elastic_pair<MODEL>(pot, -dx, -dy, disp[3 * (size_t)oj] - uix, disp[3 * (size_t)oj + 1] - uiy,
+                                        disp[3 * (size_t)oj + 2] - uiz, di, __ldg(fr.sd + q), sxx, syx, sxy, syy);
+                    const double hb = 0.5 * B;                 // val += 0.5 * bondval * tmp
+                    vxx += hb * sxx; vyx += hb * syx; vxy += hb * sxy; vyy += hb * syy;
+                });
+            }
+        }
+    }
+    if (bad) atomicOr(eflags, bad);
+    *reinterpret_cast<double4*>(out + 4 * (g - A.grid.g0)) = make_double4(vxx, vyx, vxy, vyy);
+}
+
+cudaError_t pgt_launch_ik_elastic(const PgtPot& pot, const PgtIKArgs& a, const double* disp, double max_rcut, int adaptive, double* out,
+                                  int* eflags, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    const long long n = a.grid.g1 - a.grid.g0;
+    if (n <= 0) return cudaSuccess;
+    const double rc2 = max_rcut * max_rcut;
+    PGT_DISPATCH_MODEL(pot.model, (k_ik_elastic<M><<<(unsigned)((n + 127) / 128), 128, 0, st>>>(pot, a, disp, rc2, adaptive, out, eflags)));
+    lc->n++;
+    return cudaGetLastError();
+}
+
+// ------------------------------------------------------------------------------------------
 // Work counter for the roofline numerator (not on the hot path): one thread per grid point.
 //   out[0] += U(x): unique force-carrying bonds with >= 1 endpoint in the disc (both tests exact)
 //   out[1] += half-bond items the gather integrates,  out[2] += particles in the disc

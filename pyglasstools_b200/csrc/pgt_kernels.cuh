@@ -120,6 +120,11 @@ cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
                        double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
 int pgt_thermo_blocks(int n);
+// ElasticVirialStress (needs per-particle displacements, rows of the original particle order): global sum and field
+void pgt_launch_thermo_elastic(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, const double* disp,
+                               double inv_vol, double* partials, int blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
+cudaError_t pgt_launch_ik_elastic(const PgtPot& pot, const PgtIKArgs& a, const double* disp, double max_rcut, int adaptive, double* out,
+                                  int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStream_t st, PgtLaunchCounter* lc);
 // copies nwords0 + nwords1 (<= 64) 32-bit words to mapped host memory
 void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc);

@@ -134,20 +134,25 @@ void Calculator::prepare_device(bool need_bonds)
 void ThermoCalculator::compute()
 {
     unsigned mask = 0;
+    bool elastic = false;
     for (auto& kv : m_obs) {
-        if (kv.second->kind == ThermoKind::ElasticVirial)
-            throw std::domain_error("[ERROR] elasticvirialstress is not implemented in pyglasstools_b200");
         if (kv.second->dim != 2) throw std::domain_error("[ERROR] only 2-D observables are implemented on device");
-        mask |= kv.second->mask();
+        if (kv.second->kind == ThermoKind::ElasticVirial) elastic = true;
+        else mask |= kv.second->mask();
     }
     for (auto& kv : m_obs) kv.second->clear();
-    if (mask == 0) return;
-    double out[32] = { 0 };
+    if (mask == 0 && !elastic) return;
+    double out[32] = { 0 }, out_el[4] = { 0 };
     {
         py::gil_scoped_release nogil;
         prepare_device(false);
         DeviceSession& S = DeviceSession::get();
-        S.check(pgt_thermo_compute(S.ctx(), mask, out), "pgt_thermo_compute");
+        if (mask) S.check(pgt_thermo_compute(S.ctx(), mask, out), "pgt_thermo_compute");
+        if (elastic) {
+            // displacements may change between two computes on the same frame (set_displacement): always resend
+            S.check(pgt_frame_set_displacement(S.ctx(), m_sysdata->m_disp.data(), (int64_t)m_sysdata->size()), "pgt_frame_set_displacement");
+            S.check(pgt_thermo_elastic(S.ctx(), out_el), "pgt_thermo_elastic");
+        }
     }
     // device layout: virial 4 | kinetic 4 | energy | born 16, already times 1/vol (ThermoCalculator.h:58-64)
     for (auto& kv : m_obs) {
@@ -157,6 +162,7 @@ void ThermoCalculator::compute()
         case ThermoKind::Kinetic: std::copy(out + 4, out + 8, o.val.begin()); break;
         case ThermoKind::Energy: o.val[0] = out[8]; break;
         case ThermoKind::Born: std::copy(out + 9, out + 25, o.val.begin()); break;
+        case ThermoKind::ElasticVirial: std::copy(out_el, out_el + 4, o.val.begin()); break;
         default: break;
         }
     }
@@ -175,12 +181,11 @@ void IrvingKirkwood::run(long long npoints)
     unsigned mask = 0;
     for (auto& kv : m_obs) {
         FieldObservable& o = *kv.second;
-        if (o.kind == FieldKind::ElasticVirial) throw std::domain_error("[ERROR] elasticvirialstress fields are not implemented in pyglasstools_b200");
         if (o.dim != 2) throw std::domain_error("[ERROR] only 2-D fields are implemented on device");
         if ((long long)o.npoints != npoints)
             throw std::invalid_argument("[ERROR] field '" + o.name + "' was sized for " + std::to_string(o.npoints) + " grid points, compute() got " +
                                         std::to_string(npoints));
-        mask |= (o.kind == FieldKind::Virial) ? PGT_OBS_VIRIAL : PGT_OBS_KINETIC;
+        mask |= (o.kind == FieldKind::Virial) ? PGT_OBS_VIRIAL : (o.kind == FieldKind::Kinetic ? PGT_OBS_KINETIC : PGT_OBS_ELASTIC);
     }
     if (mask == 0 || npoints == 0) return;
     if (m_cg->kernel < 0) throw std::domain_error("[ERROR] the abstract CoarseGrainFunction has no kernel");
@@ -194,10 +199,13 @@ void IrvingKirkwood::run(long long npoints)
     else
         S.check(pgt_cg_set(ctx, m_cg->kernel, m_cg->cg_rcut, m_cg->quad_mode, m_cg->order), "pgt_cg_set");
     prepare_device((mask & PGT_OBS_VIRIAL) != 0);
+    if (mask & PGT_OBS_ELASTIC)
+        S.check(pgt_frame_set_displacement(ctx, m_sysdata->m_disp.data(), (int64_t)m_sysdata->size()), "pgt_frame_set_displacement");
     S.check(pgt_ik_compute(ctx, mask), "pgt_ik_compute");
     for (auto& kv : m_obs) {
         FieldObservable& o = *kv.second;
-        S.check(pgt_ik_download(ctx, o.kind == FieldKind::Virial ? PGT_FIELD_VIRIAL : PGT_FIELD_KINETIC, o.val.data()), "pgt_ik_download");
+        const int field = o.kind == FieldKind::Virial ? PGT_FIELD_VIRIAL : (o.kind == FieldKind::Kinetic ? PGT_FIELD_KINETIC : PGT_FIELD_ELASTIC);
+        S.check(pgt_ik_download(ctx, field, o.val.data()), "pgt_ik_download");
         if (ratio != 1.0)
             for (double& v : o.val) v *= ratio;
     }

@@ -182,3 +182,39 @@ def test_missing_device_paths_raise(workdir, fixture_gsd):
     io.fieldlogger(keyword="x", names=['virialstress_00'], solver=calc)
     with pytest.raises(ValueError):
         calc.run()                                   # QAG cannot reach the tolerance in 2 intervals: GSL aborts the reference
+
+
+def test_elastic_virial_through_the_python_surface(workdir, fixture_gsd, fixture_frames, orc):
+    """data_gsd.set_displacement + thermo.calculator / ik.ikcalculator with elasticvirialstress_* names
+    (thermo/__init__.py:18, irvingkirkwood/__init__.py:13), against the oracle."""
+    import pyglasstools as pglass
+    import pyglasstools.utils as utils
+    import pyglasstools.io as io
+    import pyglasstools.potential as pot
+    import pyglasstools.thermo as thermo
+    import pyglasstools.irvingkirkwood as ik
+    import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+
+    pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)
+    mysystem = utils.read_gsd(filename=fixture_gsd, checkpointfile="restart.log", frame_num=7)
+    n = len(fixture_frames.diameter)
+    rng = np.random.default_rng(2)
+    disp = np.zeros((n, 3)); disp[:, :2] = rng.normal(0.0, 0.05, (n, 2))
+    mysystem.set_displacement(disp.tolist())
+    tcalc = thermo.calculator()
+    io.logfile(filename="elastic.log", names=['elasticvirialstress_00', 'elasticvirialstress_01', 'elasticvirialstress_11'], solver=tcalc)
+    tcalc.run()
+    P = orc.potential("poly12")
+    S = orc.System(fixture_frames.box, fixture_frames.position(7), fixture_frames.diameter)
+    S.set_displacement(disp)
+    want = S.thermo_elastic(P)
+    got = pglass.loggers_list[-1].global_obs['elasticvirialstress'].values()
+    assert np.all(np.abs(np.asarray(got) - want) <= ATOL + RTOL * np.abs(want).max())
+
+    calc = ik.ikcalculator(cgfunc=cgfunc.octic(rcut=2.0, mode="fixedpoint", order=5), dx=2.0)
+    io.fieldlogger(keyword="el", names=['elasticvirialstress_00', 'elasticvirialstress_11'], solver=calc)
+    calc.run()
+    grid, _ = orc.cartesian_grid(float(fixture_frames.box[0]), 2.0)
+    wantf = S.ik_elastic(P, orc.cgfunc("octic", 2.0, 5), grid)
+    gotf = pglass.loggers_list[-1].field_obs['elasticvirialstress'].values()
+    assert np.all(np.abs(np.asarray(gotf).reshape(-1, 4) - wantf) <= ATOL + RTOL * np.abs(wantf).max())
