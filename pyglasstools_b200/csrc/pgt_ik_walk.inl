@@ -5,22 +5,23 @@
 //
 //  stage     The cells within R of the tile form a rectangle of cell rows; the frame is sorted by cell (row-major), so
 //            every row of the rectangle is ONE contiguous run of particles and ONE contiguous run of half-bond records
-//            (two when the tile straddles the periodic seam).  A warp takes a run: positions, record offsets, the
-//            records themselves (b, (c2, f)) and the tile-local index of every bond's far end j go to shared memory
-//            with coalesced loads.  Nothing is read from global memory after this point.
+//            (two when the tile straddles the periodic seam).  A warp takes a run: positions, each particle's record
+//            range, each record's owner and the tile-local index of its far end j (found by counting the row starts
+//            at or below j; bit 15 marks j < i) go to shared memory with coalesced loads.  The records themselves
+//            (b, (c2, f)) are read through L1 by default; STAGE = true copies them to shared memory as well.
 //  phase 1   Each thread tests the particles of ITS cell window exactly as Aboria does (dx = r_p - (x + kL),
-//            dx^2 + dy^2 <= R^2) and records the hits as bits of a private bitmap over tile-local particle indices.
-//  phase 2   "walk": a per-thread state machine over the set bits and, for a particle i in the disc, over its half-bonds
-//            i -> j.  A bond whose far end j is also in the disc (one bitmap probe) is visited twice by the reference,
-//            from i and from j, each time with weight 1/2 and the same line integral: it is kept ONCE (from the end with
-//            the smaller local index) with weight 1; a bond with only i inside keeps weight 1/2.  That is the
-//            reference's sum (IrvingKirkwood.h:80-107) with U(x) quadratures instead of ~1.5 U(x).  Survivors go to a
-//            private list in shared memory ([slot][thread], 2 bytes): a header entry (particle) in front of the first
-//            kept bond of every particle, then one entry per kept bond.
-//  phase 3   Each thread integrates its own list: header -> a = r_i - x, c0 = |a|^2/R^2 (once per particle); bond ->
-//            t(s) = c0 + s (c1 + s c2), Gauss-Legendre sum of the shape, 3 FMAs into register accumulators.
-//            Phases 2 and 3 alternate until the walk is finished (the list holds `list_cap` entries per thread), on
-//            warp-uniform conditions only, so the warps of a CTA drift apart and overlap integer and FP64 work.
+//            dx^2 + dy^2 <= R^2); the hits of a window row are collected in a register mask and OR-ed into a private
+//            bitmap over tile-local particle indices.
+//  phase 2   "walk": one step = the next particle i of my disc (if the current one is exhausted), then four of its
+//            half-bonds i -> j.  A bond whose far end j is also in the disc (one bitmap probe) is visited twice by the
+//            reference, from i and from j, each time with weight 1/2 and the same line integral: it is kept ONCE (from
+//            the end with the smaller local index) with weight 1; a bond with only i inside keeps weight 1/2.  That is
+//            the reference's sum (IrvingKirkwood.h:80-107) with U(x) quadratures instead of ~1.5 U(x).  Survivors go
+//            to a private list in shared memory ([slot][thread], 2 bytes: record + weight bit).
+//  phase 3   Each thread integrates its own list: a = r_i - x, t(s) = c0 + s (c1 + s c2), Gauss-Legendre sum of the
+//            shape, 3 FMAs into register accumulators.  Phases 2 and 3 alternate until the walk is finished (the list
+//            holds `list_cap` entries per thread), on warp-uniform conditions only, so the warps of a CTA drift apart
+//            and overlap integer and FP64 work.
 //
 // Everything discrete (disc membership, bond set, weights) is bit-identical to the reference arithmetic; a grid
 // point's items are visited in an order that depends on nothing but the frame and the point, so the field does not

@@ -2,8 +2,8 @@
 //
 // Stage map (BASELINE.json north_star):
 //   0/1  k_wrap_count, scan, k_scatter_ids, k_cell_sort, k_gather_sorted   (cell list, counting sort)
-//   2/3  k_bonds<MODEL, COUNT|FILL>                                        (pair force + compacted half-bonds)
-//   4/5  k_ik_tile<KERNEL, Q> (Cartesian grids), k_ik_gather2 (point lists, local observables)   (IK field gather)
+//   2/3  k_bonds_find<MODEL> + scan + k_bonds_fill_flat<MODEL>             (pair force + compacted half-bonds)
+//   4/5  k_ik_gather2 (default), k_ik_walk / k_ik_tile (Cartesian grids), k_ik_adaptive, k_ik_elastic   (IK field gather)
 //   6    k_thermo_pairs<MODEL>, k_thermo_final                             (global virial / energy / Born / kinetic)
 // All arithmetic is FP64; no tensor cores (there is no dense contraction on this path).
 #pragma once
