@@ -470,7 +470,10 @@ static cudaError_t launch_ik_tile_t(const PgtIKArgs& a, cudaStream_t st)
         g_ikt_item_cap = (int)std::max<long long>(1536, (budget - 2LL * g_ikt_jl_cap) / 4) & ~3;
     }
     const size_t dyn = (size_t)g_ikt_item_cap * 4 + (size_t)g_ikt_jl_cap * 2;
-    static bool attr_set = false;                           // one flag per template instance
+    static bool attr_set_dev[64] = { false };               // one flag per template instance and device
+    int cur_dev = 0;
+    cudaGetDevice(&cur_dev);
+    bool& attr_set = attr_set_dev[cur_dev & 63];
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(k_ik_tile<KERNEL, Q>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
         if (e != cudaSuccess) return e;

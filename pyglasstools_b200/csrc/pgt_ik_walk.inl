@@ -445,7 +445,10 @@ template <int KERNEL, int Q, bool STAGE>
 static cudaError_t launch_ik_walk_t(const PgtIKArgs& a, const IKWCaps& caps, size_t dyn, cudaStream_t st)
 {
     if (a.grid.g1 <= a.grid.g0) return cudaSuccess;
-    static size_t attr_dyn = 0;                             // one per template instance
+    static size_t attr_dyn_dev[64] = { 0 };                 // one per template instance and device (the attribute is per device)
+    int dev = 0;
+    cudaGetDevice(&dev);
+    size_t& attr_dyn = attr_dyn_dev[dev & 63];
     if (dyn > attr_dyn) {
         cudaError_t e = cudaFuncSetAttribute(k_ik_walk<KERNEL, Q, STAGE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn);
         if (e != cudaSuccess) return e;
