@@ -176,6 +176,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
+    ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="host threads driving the two end-to-end lanes")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -331,8 +332,23 @@ def main():
     barrier()
     w2 = time.time()
     ctx.event_record(2)
-    for s in range(args.steps):
-        step_e2e(s, s % pool)
+    if args.e2e_threads == 2:
+        # one host thread per lane (ctypes releases the GIL inside the C-ABI calls): while one lane's host thread waits
+        # for a stage's counts, the other keeps the device fed
+        import threading
+
+        def lane_worker(lane):
+            for s in range(lane, args.steps, 2):
+                step_e2e(s, s % pool)
+
+        workers = [threading.Thread(target=lane_worker, args=(lane,)) for lane in (0, 1)]
+        for t in workers:
+            t.start()
+        for t in workers:
+            t.join()
+    else:
+        for s in range(args.steps):
+            step_e2e(s, s % pool)
     ctx_b.sync()                                   # both lanes drained: the end event below is later than all work
     ctx.sync()
     ctx.event_record(3)
@@ -394,7 +410,7 @@ def main():
                        "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
             "clocks": sampler.summary([(w0, w1), (w2, w3)]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "api": "C-ABI pgt_frame_upload .. pgt_ik_download_async, pinned host buffers, frames double-buffered over two contexts"},
+                    "ms_per_step": ms_e2e / args.steps, "api": "C-ABI pgt_frame_upload .. pgt_ik_download_async, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % args.e2e_threads},
             "gpu_launches": launches_total,
             "stage_ms": {"cells": float(np.mean(stage_ms["cells"])), "bonds": float(np.mean(stage_ms["bonds"])), "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_gather", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
