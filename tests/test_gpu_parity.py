@@ -486,3 +486,64 @@ def test_elastic_virial_stress_global_and_field(gpu_ctx, orc, model):
     # a new frame forgets the displacements
     setup_ctx(gpu_ctx, orc, P, GPU_NAME[model], pos, diam, box)
     assert np.all(gpu_ctx.thermo_elastic() == 0.0)
+
+
+@pytest.mark.parametrize("n,nsample", [(1024, 300), (2048, 120)])
+def test_full_size_frames_properties_and_sampled_oracle(gpu_ctx, orc, n, nsample):
+    """BASELINE configs[2] / configs[4] sizes (N = 1 048 576 on 1024^2, N = 4 194 304 on 2048^2): the oracle on a random
+    sample of grid points, and the size-independent checks over the whole field: the two gather formulations agree
+    everywhere, the duplicated end rows / columns of the np.linspace grid agree, a 3-way np.array_split sharding
+    reproduces the field bit for bit, half-bonds come in pairs, and the thermo virial equals the sum over the exported
+    bond list."""
+    fr = synth.synth_frame(n, synth.SEEDS["cfg3" if n == 1024 else "cfg5"])
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    nhb = gpu_ctx.counts()["n_halfbonds"]
+    assert nhb % 2 == 0 and nhb > 3 * n * n
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, n)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    fields = {}
+    for variant in (2, 5):
+        gpu_ctx.set_option("ik_variant", variant)
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        fields[variant] = gpu_ctx.ik_download()
+    full = fields[2].reshape(n, n, 4)
+    rowscale = np.abs(fields[2]).max(axis=1, keepdims=True)
+    assert_close(fields[5], fields[2], scale=rowscale)
+    # x = -L/2 and x = +L/2 are the same point of the periodic box (irvingkirkwood/__init__.py:45-53)
+    assert_close(full[0], full[-1], scale=np.abs(full[0]).max(axis=1, keepdims=True))
+    assert_close(full[:, 0], full[:, -1], scale=np.abs(full[:, 0]).max(axis=1, keepdims=True))
+    # sharding: bit for bit, with the automatic kernel choice
+    gpu_ctx.set_option("ik_variant", 0)
+    G = n * n
+    parts, g0 = [], 0
+    for s in [len(c) for c in np.array_split(np.arange(G), 3)]:
+        gpu_ctx.set_shard(g0, g0 + s)
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        parts.append(gpu_ctx.ik_download())
+        g0 += s
+    gpu_ctx.set_shard(0, G)
+    assert np.array_equal(np.vstack(parts), fields[2])
+    # the oracle on a random sample of grid points (incl. the seam rows)
+    rng = np.random.default_rng(n)
+    ii = np.concatenate([rng.integers(0, n, nsample), [0, n - 1, 0, n - 1]])
+    jj = np.concatenate([rng.integers(0, n, nsample), [0, n - 1, n - 1, 0]])
+    grid = np.zeros((len(ii), 3)); grid[:, 0] = axis[ii]; grid[:, 1] = axis[jj]
+    want = S.ik(P, orc.cgfunc("octic", 2.0, 5), grid)["virial"]
+    assert_close(full[ii, jj], want, scale=np.abs(want).max(axis=1, keepdims=True))
+    # thermo: device pair sums vs the oracle's serial loop, and vs the bond list (each unordered pair appears twice)
+    t = gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY)
+    if n == 1024:
+        w = S.thermo(P, born=False)
+        assert_close(t["virial"], w["virial"], scale=np.abs(w["virial"]).max())
+        assert_close(t["energy"], w["energy"])
+    bi, bj, brij, bf = gpu_ctx.export_bonds()
+    vol = float(box[0]) * float(box[1])
+    vxx = 0.5 * np.sum(bf * brij[:, 0] * brij[:, 0]) / vol
+    vyy = 0.5 * np.sum(bf * brij[:, 1] * brij[:, 1]) / vol
+    assert abs(vxx - t["virial"][0]) <= 1e-9 * abs(vxx) and abs(vyy - t["virial"][3]) <= 1e-9 * abs(vyy)
+    assert np.array_equal(np.sort(bi.astype(np.int64) * (n * n) + bj), np.sort(bj.astype(np.int64) * (n * n) + bi))
