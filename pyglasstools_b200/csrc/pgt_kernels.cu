@@ -626,7 +626,21 @@ template <int KERNEL, int Q>
 __device__ __forceinline__ double bond_quadrature(double c0, double c1, double c2, int nq)
 {
     double B = 0.0;
-    if (Q > 0) {
+    if (Q > 0 && KERNEL == PGT_CG_OCTIC) {
+        // octic: g = 1 - t^2 is positive exactly when t < 1, so the cut-off is a clamp of g at zero, done on the sign
+        // word (a cleared high word leaves at most a denormal, whose square is zero); two partial sums
+        double B1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < Q; ++k) {
+            const double s = c_gl_s[k];
+            const double t = fma(fma(c2, s, c1), s, c0);
+            const double g = fma(-t, t, 1.0);
+            const int hi = __double2hiint(g);
+            const double gc = __hiloint2double(hi & ~(hi >> 31), __double2loint(g));
+            if (k & 1) B1 = fma(c_gl_w[k] * gc, gc, B1); else B = fma(c_gl_w[k] * gc, gc, B);
+        }
+        B += B1;
+    } else if (Q > 0) {
 #pragma unroll
         for (int k = 0; k < Q; ++k) {
             const double s = c_gl_s[k];
