@@ -163,7 +163,7 @@ int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
 /* Page-locked host memory for the caller's frame / field buffers (cudaHostAlloc / cudaFreeHost). */
 int pgt_host_alloc(void** ptr, uint64_t bytes);
 int pgt_host_free(void* ptr);
-/* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 4 tile gather);
+/* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 4 tile gather, 5 / 6 walk gather with records via L1 / staged);
  * "bond_single_search" (1 default: one neighbour search per frame, 0: separate count and fill searches). */
 int pgt_set_option(pgt_ctx* ctx, const char* name, double value);
 

@@ -164,7 +164,7 @@ struct pgt_ctx {
     cudaEvent_t user_ev[16]{};
 
     // tuning
-    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather; 5: walk gather
+    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather; 5 / 6: walk gather (records via L1 / staged)
     int quad_mode = PGT_QUAD_FIXEDPOINT;     // PGT_QUAD_ADAPTIVE: QAG / GK15 bond quadrature
     double qag_epsabs = 0.0, qag_epsrel = 0.0;
     int qag_limit = 0;
@@ -309,7 +309,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     if (const char* env = getenv("PGT_BOND_FILL_FLAT")) ctx->bond_fill_flat = atoi(env) != 0;
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
-        if (l == 0 || l == 2 || l == 4 || l == 5) ctx->ik_variant = l;
+        if (l == 0 || l == 2 || l == 4 || l == 5 || l == 6) ctx->ik_variant = l;
     }
     *out = ctx;
     return PGT_OK;
@@ -886,7 +886,7 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
     if (!ctx || !name) return PGT_ERR_ARG;
     if (!strcmp(name, "ik_variant")) {
         const int l = (int)value;
-        if (l != 0 && l != 2 && l != 4 && l != 5) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase), 4 (tile) or 5 (walk)");
+        if (l != 0 && l != 2 && l != 4 && l != 5 && l != 6) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase), 4 (tile), 5 or 6 (walk)");
         ctx->ik_variant = l;
         return PGT_OK;
     }

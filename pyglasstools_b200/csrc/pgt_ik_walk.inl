@@ -390,7 +390,7 @@ static bool ik_walk_applicable(const PgtIKArgs& a)
 
 // Shared-memory budget of one CTA from frame-wide statistics only (never from the shard), so that every shard of a
 // grid runs the same code on the same tiles.  Returns false when the rectangle cannot fit one SM.
-static bool ikw_pick_caps(const PgtIKArgs& a, IKWCaps* caps, size_t* dyn_bytes, bool* stage_out)
+static bool ikw_pick_caps(const PgtIKArgs& a, bool stage, IKWCaps* caps, size_t* dyn_bytes)
 {
     static int smem_sm = 0, smem_cta = 0;
     if (smem_sm == 0) {
@@ -399,15 +399,13 @@ static bool ikw_pick_caps(const PgtIKArgs& a, IKWCaps* caps, size_t* dyn_bytes, 
         cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
         cudaDeviceGetAttribute(&smem_cta, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     }
-    static int want_ctas = -1, margin_pct = 15, want_stage = 0, want_list = 0;
+    static int want_ctas = -1, margin_pct = 15, want_list = 0;
     if (want_ctas < 0) {
         const char* e = getenv("PGT_IKW_CTAS");
         want_ctas = e ? atoi(e) : 0;
         if ((e = getenv("PGT_IKW_MARGIN"))) margin_pct = atoi(e);
-        if ((e = getenv("PGT_IKW_STAGE"))) want_stage = atoi(e);
         if ((e = getenv("PGT_IKW_LIST"))) want_list = atoi(e);
     }
-    const bool stage = want_stage != 0;
     const double R = a.cg.rcut, cwx = 1.0 / a.cells.inv_cwx, cwy = 1.0 / a.cells.inv_cwy;
     const double area = (a.grid.tspan_x + 2.0 * R + 2.0 * cwx) * (a.grid.tspan_y + 2.0 * R + 2.0 * cwy);
     const double rho = (double)a.fr.n / (a.box.L[0] * a.box.L[1]);
@@ -437,7 +435,6 @@ static bool ikw_pick_caps(const PgtIKArgs& a, IKWCaps* caps, size_t* dyn_bytes, 
     caps->nrec_cap = (int)nrec;
     caps->list_cap = list_cap;
     *dyn_bytes = (size_t)(base + (long long)list_cap * 2 * IKW_THREADS + 15) & ~(size_t)15;
-    *stage_out = stage;
     return true;
 }
 

@@ -961,11 +961,11 @@ cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtL
     // measured on B200 (cfg5, 2048^2): two-phase 1.85 ms, tile 3.5 ms (its integer bookkeeping -- staging, bitmap walks --
     // outweighs the 1.5x fewer quadratures) -> automatic = two-phase; the tile kernel stays selectable (variant 4)
     if (variant == 4 && ik_tile_applicable(a)) return launch_ik_tile(a, st);   // Cartesian grids, virial field only
-    if (variant == 5 && ik_walk_applicable(a)) {
+    if ((variant == 5 || variant == 6) && ik_walk_applicable(a)) {            // 5: records through L1, 6: staged in shared memory
         IKWCaps caps;
         size_t dyn = 0;
-        bool stage = true;
-        if (ikw_pick_caps(a, &caps, &dyn, &stage)) return launch_ik_walk(a, caps, dyn, stage, st);
+        const bool stage = variant == 6;
+        if (ikw_pick_caps(a, stage, &caps, &dyn)) return launch_ik_walk(a, caps, dyn, stage, st);
     }
     return launch_ik2(a, st);                                                  // two-phase kernel (any point list, local fields)
 }

@@ -113,7 +113,8 @@ void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, 
 // rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)
 void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_hb, double cscale, cudaStream_t st,
                               PgtLaunchCounter* lc);
-// variant 0: automatic; 2: two-phase kernel; 4: tile kernel, 5: walk kernel (Cartesian grids + virial only, else two-phase)
+// variant 0: automatic; 2: two-phase kernel; 4: tile kernel, 5 / 6: walk kernel with records through L1 / staged in shared
+// memory (4-6: Cartesian grids + virial only, else two-phase)
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 // virial field with the adaptive (QAG, 15-point Gauss-Kronrod) bond quadrature; failures are OR-ed into *eflags
 cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);

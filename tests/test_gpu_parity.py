@@ -273,7 +273,7 @@ def test_empty_and_tiny_inputs(gpu_ctx, orc):
     assert np.all(gpu_ctx.ik_download() == 0)
 
 
-@pytest.mark.parametrize("variant", [2, 4, 5])
+@pytest.mark.parametrize("variant", [2, 4, 5, 6])
 def test_sharding_is_bitwise_independent(gpu_ctx, orc, fixture_frames, variant):
     """np.array_split shards (irvingkirkwood/__init__.py:53-60) reproduce the unsharded field bit for bit,
     with either gather kernel."""
@@ -324,7 +324,7 @@ def test_bond_list_single_search_equals_two_search(gpu_ctx, orc, fixture_frames)
         assert len(got[0][0]) > (20000 if model == "poly106" else 5000)
 
 
-@pytest.mark.parametrize("variant", [0, 2, 4, 5])
+@pytest.mark.parametrize("variant", [0, 2, 4, 5, 6])
 def test_gather_kernel_variants(orc, fixture_frames, variant, monkeypatch):
     """Every gather formulation (two-phase point lists, shared-memory tiles, per-thread walk) against the oracle."""
     monkeypatch.setenv("PGT_IK_VARIANT", str(variant))
@@ -398,13 +398,14 @@ def test_walk_gather_on_cartesian_grids(gpu_ctx, orc, kernel, order, R, nmax, mo
     axis = synth.linspace_axis(L, nmax)
     gpu_ctx.set_grid_cartesian(axis, axis)
     fields = {}
-    for variant in (2, 5):
+    for variant in (2, 5, 6):
         gpu_ctx.set_option("ik_variant", variant)
         gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
         fields[variant] = gpu_ctx.ik_download()
     gpu_ctx.set_option("ik_variant", 0)
     scale = np.abs(fields[2]).max(axis=1, keepdims=True)
     assert_close(fields[5], fields[2], scale=scale)
+    assert np.array_equal(fields[6], fields[5])               # staged records: same arithmetic, same order
     ii = np.unique(np.concatenate([np.arange(0, nmax, 7), [nmax - 1]]))
     grid = np.zeros((len(ii) ** 2, 3)); grid[:, 0] = np.repeat(axis[ii], len(ii)); grid[:, 1] = np.tile(axis[ii], len(ii))
     want = S.ik(P, cg, grid)["virial"]
