@@ -176,6 +176,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
+    ap.add_argument("--e2e-field", default="full", choices=("full", "sym"),
+                    help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy)")
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="host threads driving the two end-to-end lanes")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
@@ -251,7 +253,8 @@ def main():
         pin_diam[k].array[...] = f["diameter"]
         dev_pos.append(torch.from_numpy(f["position"]).cuda())
         dev_diam.append(torch.from_numpy(f["diameter"]).cuda())
-    pin_out = _capi.PinnedArray((g_local, 4), np.float64)
+    ncomp_out = 3 if args.e2e_field == "sym" else 4
+    pin_out = _capi.PinnedArray((g_local, ncomp_out), np.float64)
     box = frames[0]["box"]
     torch.cuda.synchronize()
 
@@ -270,7 +273,7 @@ def main():
     ctx_b.set_grid_cartesian(axis, axis)
     if args.shard == "grid" and world > 1:
         ctx_b.set_shard(*shards[rank])
-    pin_out_b = _capi.PinnedArray((g_local, 4), np.float64)
+    pin_out_b = _capi.PinnedArray((g_local, ncomp_out), np.float64)
     lanes = [(ctx, pin_out), (ctx_b, pin_out_b)]
 
     def step_e2e(s, k):
@@ -280,7 +283,10 @@ def main():
         c.build_bonds()
         c.ik_compute(_capi.OBS_VIRIAL)
         c.ik_download_wait()                       # this lane's previous field has landed in `out` (consumed here)
-        c.ik_download_async(_capi.FIELD_VIRIAL, out.array)
+        if args.e2e_field == "sym":
+            c.ik_download_sym_async(_capi.FIELD_VIRIAL, out.array)
+        else:
+            c.ik_download_async(_capi.FIELD_VIRIAL, out.array)
 
     # ---- algorithmic work of the gather per frame (outside the timed regions)
     flops_per_frame, items_per_frame, hb_per_frame = [], [], []
@@ -394,7 +400,7 @@ def main():
     except Exception:
         pass
     h2d = N * 3 * 4 + N * 4
-    d2h = g_local * 4 * 8
+    d2h = g_local * ncomp_out * 8
 
     if rank == 0:
         out = {
@@ -410,7 +416,7 @@ def main():
                        "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
             "clocks": sampler.summary([(w0, w1), (w2, w3)]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "api": "C-ABI pgt_frame_upload .. pgt_ik_download_async, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % args.e2e_threads},
+                    "ms_per_step": ms_e2e / args.steps, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_threads)},
             "gpu_launches": launches_total,
             "stage_ms": {"cells": float(np.mean(stage_ms["cells"])), "bonds": float(np.mean(stage_ms["bonds"])), "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_gather", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",

@@ -113,6 +113,9 @@ int pgt_ik_download(pgt_ctx* ctx, int field_id, double* out);
  * pgt_synchronize(ctx).  With two contexts used alternately, frame k+1's upload and compute overlap frame k's
  * read-back (PCIe is full duplex) -- the trajectory loop of pyglasstools.analyze, double-buffered.              */
 int pgt_ik_download_async(pgt_ctx* ctx, int field_id, double* out);
+/* Same for a 2x2 tensor field, 3 doubles per grid point (xx, xy, yy): the stress tensors are symmetric by construction
+ * (VirialStress::compute, ListofCommonObservables.h:49-70: F (x) r with F parallel to r), the copy is 25 % smaller. */
+int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out);
 /* Waits for the read-backs enqueued by pgt_ik_download_async only (not for kernels of later frames).        */
 int pgt_ik_download_wait(pgt_ctx* ctx);
 /* Device pointer of a field of the local shard (for NCCL / zero-copy consumers).               */

@@ -20,7 +20,7 @@ STAGES = {"upload": 0, "cells": 1, "bonds": 2, "ik": 3, "thermo": 4, "download":
 
 EXPORTED = [
     "pgt_ctx_create", "pgt_ctx_destroy", "pgt_last_error", "pgt_device_count", "pgt_synchronize", "pgt_stream",
-    "pgt_frame_set_displacement", "pgt_thermo_elastic", "pgt_potential_set", "pgt_cg_set", "pgt_cg_set_adaptive", "pgt_cg_bond_adaptive", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
+    "pgt_ik_download_sym_async", "pgt_frame_set_displacement", "pgt_thermo_elastic", "pgt_potential_set", "pgt_cg_set", "pgt_cg_set_adaptive", "pgt_cg_bond_adaptive", "pgt_set_max_rcut", "pgt_set_cell_size", "pgt_frame_upload",
     "pgt_frame_set_device", "pgt_build_cells", "pgt_build_bonds", "pgt_frame_counts", "pgt_grid_set_cartesian",
     "pgt_grid_set_points", "pgt_grid_set_shard", "pgt_ik_compute", "pgt_ik_download", "pgt_ik_download_async", "pgt_ik_download_wait", "pgt_ik_device_ptr",
     "pgt_thermo_compute", "pgt_export_bonds", "pgt_export_neighbors", "pgt_export_wrapped", "pgt_stage_time_ms",
@@ -230,6 +230,11 @@ class Context:
     def ik_download_async(self, field, out):
         """Enqueues the read-back into the page-locked array `out`; valid after sync()."""
         self._ck(lib().pgt_ik_download_async(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    def ik_download_sym_async(self, field, out):
+        """Same for a 2x2 tensor field as (n, 3) rows (xx, xy, yy) -- the tensors are symmetric, the copy 25 % smaller."""
+        self._ck(lib().pgt_ik_download_sym_async(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
         return out
 
     def ik_download_wait(self):

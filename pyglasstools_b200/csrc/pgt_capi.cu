@@ -150,6 +150,7 @@ struct pgt_ctx {
 
     // outputs
     DevBuf out_virial, out_kinetic, out_density, out_elastic;
+    DevBuf pack;                 // packed symmetric field for pgt_ik_download_sym_async
     DevBuf disp;                 // N x 3 displacements, original particle order
     bool have_disp = false;
     unsigned last_ik_mask = 0;
@@ -324,7 +325,7 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
                        &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->nb_list, &ctx->gxs, &ctx->gys, &ctx->gpts,
-                       &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->out_elastic, &ctx->disp, &ctx->thermo_partials,
+                       &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->out_elastic, &ctx->disp, &ctx->pack, &ctx->thermo_partials,
                        &ctx->thermo_out,
                        &ctx->comm_scratch };
     for (DevBuf* b : bufs)
@@ -940,6 +941,28 @@ static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
     CK(cudaEventRecord(ctx->ev_field_ready, ctx->stream));
     CK(cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_field_ready, 0));
     if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
+    CK(cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
+    ctx->dl_pending = true;
+    return PGT_OK;
+}
+
+int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out)
+{
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_ik_download_sym_async: null argument");
+    DevBuf* b;
+    int nc;
+    int rc = field_info(ctx, field_id, &b, &nc);
+    if (rc == -2) return fail(ctx, PGT_ERR_ARG, "unknown field %d", field_id);
+    if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
+    if (nc != 4) return fail(ctx, PGT_ERR_ARG, "field %d is not a 2x2 tensor field", field_id);
+    CK(cudaSetDevice(ctx->device));
+    const long long gl = ctx->g1 - ctx->g0;
+    if (ctx->dl_pending) CK(cudaStreamSynchronize(ctx->dl_stream));      // the pack buffer is still being read back
+    ENSURE(ctx->pack, sizeof(double) * 3 * (size_t)std::max<long long>(gl, 1));
+    CK(cudaEventRecord(ctx->ev_field_ready, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_field_ready, 0));
+    pgt_launch_pack_sym(static_cast<const double*>(b->p), ctx->pack.as<double>(), gl, ctx->dl_stream, &ctx->launches);
+    if (gl > 0) CK(cudaMemcpyAsync(out, ctx->pack.p, sizeof(double) * 3 * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
     CK(cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
     ctx->dl_pending = true;
     return PGT_OK;

@@ -1264,6 +1264,26 @@ void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStrea
 }
 
 // ------------------------------------------------------------------------------------------
+// Symmetric read-back: the 2x2 tensors of the stress fields are symmetric by construction (xy is stored twice), so the
+// host needs 3 of the 4 doubles per grid point: packs (xx, xy, yy) for a 25 % smaller device-to-host copy.
+__global__ void __launch_bounds__(256) k_pack_sym(const double4* __restrict__ in, double* __restrict__ out, long long n)
+{
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double4 v = in[i];
+    out[3 * i] = v.x;
+    out[3 * i + 1] = v.y;
+    out[3 * i + 2] = v.w;
+}
+
+void pgt_launch_pack_sym(const double* in4, double* out3, long long n, cudaStream_t st, PgtLaunchCounter* lc)
+{
+    if (n <= 0) return;
+    k_pack_sym<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(reinterpret_cast<const double4*>(in4), out3, n);
+    lc->n++;
+}
+
+// ------------------------------------------------------------------------------------------
 // Small results (counts, flags, the 25 thermo sums) reach the host through MAPPED page-locked memory written by
 // this kernel, not through a device-to-host memcpy: a memcpy would queue in the copy engine behind a field
 // read-back of another frame (134 MB at cfg5) and stall the stage that waits for it.

@@ -129,4 +129,6 @@ cudaError_t pgt_launch_ik_elastic(const PgtPot& pot, const PgtIKArgs& a, const d
 void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStream_t st, PgtLaunchCounter* lc);
 // copies nwords0 + nwords1 (<= 64) 32-bit words to mapped host memory
 void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc);
+// (xx, xy, yx, yy) per point -> (xx, xy, yy) per point
+void pgt_launch_pack_sym(const double* in4, double* out3, long long n, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_fp64_probe(double* out, int iters, int blocks, int threads, cudaStream_t st, PgtLaunchCounter* lc);

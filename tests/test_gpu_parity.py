@@ -548,3 +548,22 @@ def test_full_size_frames_properties_and_sampled_oracle(gpu_ctx, orc, n, nsample
     vyy = 0.5 * np.sum(bf * brij[:, 1] * brij[:, 1]) / vol
     assert abs(vxx - t["virial"][0]) <= 1e-9 * abs(vxx) and abs(vyy - t["virial"][3]) <= 1e-9 * abs(vyy)
     assert np.array_equal(np.sort(bi.astype(np.int64) * (n * n) + bj), np.sort(bj.astype(np.int64) * (n * n) + bi))
+
+
+def test_symmetric_packed_readback(gpu_ctx, orc, fixture_frames):
+    """pgt_ik_download_sym_async: (xx, xy, yy) per grid point equals columns 0, 1, 3 of the full read-back, and the
+    dropped column 2 (yx) is bit-identical to column 1 in the full field."""
+    P = orc.potential("poly12")
+    pos, diam, box = fixture_frames.position(12), fixture_frames.diameter, fixture_frames.box
+    setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    axis = synth.linspace_axis(float(box[0]), 50)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    full = gpu_ctx.ik_download()
+    out = _capi.PinnedArray((2500, 3), np.float64)
+    gpu_ctx.ik_download_sym_async(_capi.FIELD_VIRIAL, out.array)
+    gpu_ctx.ik_download_wait()
+    assert np.array_equal(out.array, full[:, [0, 1, 3]])
+    assert np.array_equal(full[:, 1], full[:, 2])
