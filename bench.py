@@ -128,6 +128,38 @@ def make_frames(wl, rank, nframes):
     return frames
 
 
+def _parse_cpulist(txt):
+    cpus = set()
+    for part in txt.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def bind_to_gpu_numa_node(local_rank):
+    """One process per GPU: keep this rank's host threads, and therefore the pinned staging buffers they first touch,
+    on the NUMA node the GPU hangs off (sysfs numa_node of its PCI function).  Returns a description for the log."""
+    if os.environ.get("PGT_BENCH_NUMA", "1") == "0":
+        return "off"
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local_rank)
+        bdf = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % bdf).read())
+        if node < 0:
+            return "gpu %s: no NUMA node reported" % bdf
+        cpus = _parse_cpulist(open("/sys/devices/system/node/node%d/cpulist" % node).read())
+        mine = cpus & os.sched_getaffinity(0)
+        if not mine:
+            return "gpu %s on node %d: none of its cpus in this process's affinity" % (bdf, node)
+        os.sched_setaffinity(0, mine)
+        return "gpu %s -> node %d, %d cpus" % (bdf, node, len(mine))
+    except Exception as e:                      # sysfs layout differs or the call is not permitted: run unbound
+        return "unbound (%s)" % e
+
+
 def run_reference(args, wl, rank, world):
     """The reference's algorithm on the host cores: the oracle (the reference itself cannot be built
     here -- no Boost / GSL / MPI), all threads, a bounded sample of the grid per step."""
@@ -135,6 +167,8 @@ def run_reference(args, wl, rank, world):
         return
     from oracle import orc
     from pyglasstools_b200 import synth
+    # torchrun exports OMP_NUM_THREADS=1 when it starts more than one rank; this arm is rank 0 alone on the whole host
+    orc.set_num_threads(len(os.sched_getaffinity(0)))
     fr = synth.synth_frame(wl["n"], synth.SEEDS[wl["seed"]])
     name, rc, prm = pot_params(wl["pot"])
     P = orc.potential(name)
@@ -198,6 +232,9 @@ def main():
     from pyglasstools_b200 import _capi, sharding, synth
 
     torch.cuda.set_device(local_rank)
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 else "single rank: unbound"
+    if os.environ.get("PGT_BENCH_VERBOSE"):
+        print("rank %d: %s, affinity %d cpus" % (rank, numa, len(os.sched_getaffinity(0))), file=sys.stderr, flush=True)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
@@ -416,7 +453,7 @@ def main():
                        "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
             "clocks": sampler.summary([(w0, w1), (w2, w3)]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_threads)},
+                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_threads)},
             "gpu_launches": launches_total,
             "stage_ms": {"cells": float(np.mean(stage_ms["cells"])), "bonds": float(np.mean(stage_ms["bonds"])), "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_gather", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
