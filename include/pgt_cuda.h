@@ -26,7 +26,7 @@ typedef enum {
     PGT_OK = 0,
     PGT_ERR_CUDA = -1,        /* a CUDA runtime call or kernel failed */
     PGT_ERR_ARG = -2,         /* invalid argument / call order */
-    PGT_ERR_UNSUPPORTED = -3, /* valid in the reference, not implemented on device (3-D, adaptive quadrature, ...) */
+    PGT_ERR_UNSUPPORTED = -3, /* valid in the reference, not implemented on device (3-D, ...) */
     PGT_ERR_STATE = -4,       /* a required earlier stage has not run */
     PGT_ERR_DATA = -5,        /* the frame violates a documented precondition (box too small, z != 0 in 2-D, ...) */
     PGT_ERR_NCCL = -6
@@ -37,7 +37,7 @@ enum { PGT_POT_LJ = 0, PGT_POT_FORCESHIFTED_LJ = 1, PGT_POT_POLY12 = 2, PGT_POT_
        PGT_POT_POLY106 = 5, PGT_POT_POLYYUKAWA = 6, PGT_POT_POLYLJ = 7 };
 /* coarse-graining kernels: irvingkirkwood/cgfunc/module-cgfunc.cpp:12-19 */
 enum { PGT_CG_OCTIC = 0, PGT_CG_RECT = 1, PGT_CG_MOLLIFIER = 2 };
-/* quadrature modes: FixedPointCGFunc (CoarseGrainFunction.h:56-92); adaptive (:94-134) is PGT_ERR_UNSUPPORTED */
+/* quadrature modes: FixedPointCGFunc (CoarseGrainFunction.h:56-92); AdaptiveCGFunc (:94-134) via pgt_cg_set_adaptive */
 enum { PGT_QUAD_FIXEDPOINT = 0, PGT_QUAD_ADAPTIVE = 1 };
 /* observable masks */
 enum { PGT_OBS_VIRIAL = 1u, PGT_OBS_KINETIC = 2u, PGT_OBS_DENSITY = 4u,      /* IK fields */
