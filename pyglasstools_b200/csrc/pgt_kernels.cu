@@ -188,12 +188,106 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(int* out, long long n
         if (base + k < n) out[base + k] += add;
 }
 
-long long pgt_scan_scratch_ints(long long n) { return (n + SCAN_TILE - 1) / SCAN_TILE + 1; }
+// Single-pass variant: one kernel, each tile's total chained to its predecessors' by a decoupled look-back.
+// `state[t]`: bits 63:62 = 0 nothing yet, 1 tile total, 2 inclusive prefix; the value in the low bits, so value and flag
+// travel in one 64-bit store.  Tiles are numbered by a ticket taken when the block starts: every tile a block waits for
+// is already resident, so the look-back cannot wait on a block that has not been scheduled.  Sums are int32 arithmetic
+// (wrap-around as in the three-phase form; the callers check the published total).
+#define SCAN_TOTAL (1ull << 62)
+#define SCAN_PREFIX (2ull << 62)
+#define SCAN_VALUE 0xffffffffull
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_scan_chained(const int* in, int* out, long long n, unsigned long long* state, int* ticket)
+{
+    __shared__ int warp_sums[SCAN_THREADS / 32];
+    __shared__ int s_tile, s_base;
+    if (threadIdx.x == 0) s_tile = atomicAdd(ticket, 1);
+    __syncthreads();
+    const int tile = s_tile;
+    const long long base = (long long)tile * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
+    int v[SCAN_ITEMS];
+    int sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        v[k] = (base + k < n) ? in[base + k] : 0;
+        sum += v[k];
+    }
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int inc = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(FULL_MASK, inc, d);
+        if (lane >= d) inc += t;
+    }
+    if (lane == 31) warp_sums[w] = inc;
+    __syncthreads();
+    if (w == 0) {
+        int ws = (lane < SCAN_THREADS / 32) ? warp_sums[lane] : 0;
+        int wi = ws;
+#pragma unroll
+        for (int d = 1; d < SCAN_THREADS / 32; d <<= 1) {
+            int t = __shfl_up_sync(FULL_MASK, wi, d);
+            if (lane >= d) wi += t;
+        }
+        if (lane < SCAN_THREADS / 32) warp_sums[lane] = wi - ws;
+        const int agg = __shfl_sync(FULL_MASK, wi, SCAN_THREADS / 32 - 1);
+        int excl = 0;
+        if (tile == 0) {
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state) = SCAN_PREFIX | (unsigned)agg;
+        } else {
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + tile) = SCAN_TOTAL | (unsigned)agg;
+            int look = tile - 1;
+            while (true) {
+                const int idx = look - lane;
+                unsigned long long st = SCAN_PREFIX;                           // before tile 0: prefix 0
+                if (idx >= 0) st = *reinterpret_cast<volatile unsigned long long*>(state + idx);
+                if (__any_sync(FULL_MASK, (st >> 62) == 0)) continue;          // a predecessor has not published yet
+                const unsigned pref = __ballot_sync(FULL_MASK, (st >> 62) == 2);
+                const int stop = pref ? __ffs(pref) - 1 : 31;                  // nearest predecessor holding a prefix
+                int x = lane <= stop ? (int)(unsigned)(st & SCAN_VALUE) : 0;
+#pragma unroll
+                for (int d = 16; d >= 1; d >>= 1) x += __shfl_xor_sync(FULL_MASK, x, d);
+                excl += x;
+                if (pref) break;
+                look -= 32;
+            }
+            if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(state + tile) = SCAN_PREFIX | (unsigned)(excl + agg);
+        }
+        if (lane == 0) s_base = excl;
+    }
+    __syncthreads();
+    int excl = inc - sum + warp_sums[w] + s_base;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        if (base + k < n) out[base + k] = excl;
+        excl += v[k];
+    }
+}
+
+// scratch: ticket (one 64-bit word) + one 64-bit state per tile, or the tile sums of the three-phase form
+long long pgt_scan_scratch_ints(long long n) { return 2 * ((n + SCAN_TILE - 1) / SCAN_TILE + 2); }
+
+static int scan_single_pass()
+{
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("PGT_SCAN_SINGLE_PASS");
+        v = e ? (atoi(e) != 0) : 1;
+    }
+    return v;
+}
 
 void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* tile_sums, cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (n <= 0) return;
     const int tiles = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+    if (tiles > 1 && scan_single_pass()) {
+        unsigned long long* words = reinterpret_cast<unsigned long long*>(tile_sums);
+        cudaMemsetAsync(words, 0, sizeof(unsigned long long) * ((size_t)tiles + 1), st);
+        k_scan_chained<<<tiles, SCAN_THREADS, 0, st>>>(in, out, n, words + 1, reinterpret_cast<int*>(words));
+        lc->n++;
+        return;
+    }
     k_scan_tile<<<tiles, SCAN_THREADS, 0, st>>>(in, out, n, tile_sums);
     lc->n++;
     if (tiles > 1) {
