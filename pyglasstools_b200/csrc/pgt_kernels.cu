@@ -196,6 +196,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_add(int* out, long long n
 #define SCAN_TOTAL (1ull << 62)
 #define SCAN_PREFIX (2ull << 62)
 #define SCAN_VALUE 0xffffffffull
+static_assert(SCAN_ITEMS == 8, "k_scan_chained moves 8 items per thread as two int4");
 
 __global__ void __launch_bounds__(SCAN_THREADS) k_scan_chained(const int* in, int* out, long long n, unsigned long long* state, int* ticket)
 {
@@ -207,11 +208,16 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_chained(const int* in, in
     const long long base = (long long)tile * SCAN_TILE + (long long)threadIdx.x * SCAN_ITEMS;
     int v[SCAN_ITEMS];
     int sum = 0;
+    const bool whole = base + SCAN_ITEMS <= n;              // buffers are 16-byte aligned and base is a multiple of 8
+    if (whole) {
+        const int4 a = *reinterpret_cast<const int4*>(in + base), b = *reinterpret_cast<const int4*>(in + base + 4);
+        v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) {
-        v[k] = (base + k < n) ? in[base + k] : 0;
-        sum += v[k];
+        for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = (base + k < n) ? in[base + k] : 0;
     }
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) sum += v[k];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int inc = sum;
 #pragma unroll
@@ -257,10 +263,19 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_chained(const int* in, in
     }
     __syncthreads();
     int excl = inc - sum + warp_sums[w] + s_base;
+    int o[SCAN_ITEMS];
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        if (base + k < n) out[base + k] = excl;
+        o[k] = excl;
         excl += v[k];
+    }
+    if (whole) {
+        *reinterpret_cast<int4*>(out + base) = make_int4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<int4*>(out + base + 4) = make_int4(o[4], o[5], o[6], o[7]);
+    } else {
+#pragma unroll
+        for (int k = 0; k < SCAN_ITEMS; ++k)
+            if (base + k < n) out[base + k] = o[k];
     }
 }
 
