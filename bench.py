@@ -212,7 +212,8 @@ def main():
     ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
     ap.add_argument("--e2e-field", default="full", choices=("full", "sym"),
                     help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy)")
-    ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="host threads driving the two end-to-end lanes")
+    ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
+    ap.add_argument("--e2e-lanes", type=int, default=3, choices=(2, 3, 4), help="contexts (streams) the end-to-end trajectory loop is pipelined over")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -301,20 +302,22 @@ def main():
         ctx.build_bonds()
         ctx.ik_compute(_capi.OBS_VIRIAL)
 
-    # end to end: the trajectory loop double-buffered over two contexts (two streams): frame s+1's upload and
+    # end to end: the trajectory loop pipelined over --e2e-lanes contexts (one stream each): frame s+1's upload and
     # stages overlap frame s's field read-back; every frame is uploaded from and read back to pinned host memory
-    ctx_b = _capi.Context(local_rank)
-    ctx_b.set_potential(name, rc, prm)
-    ctx_b.set_cg(*wl["cg"])
-    ctx_b.set_max_rcut(max(rc * dmax, dmax))
-    ctx_b.set_grid_cartesian(axis, axis)
-    if args.shard == "grid" and world > 1:
-        ctx_b.set_shard(*shards[rank])
-    pin_out_b = _capi.PinnedArray((g_local, ncomp_out), np.float64)
-    lanes = [(ctx, pin_out), (ctx_b, pin_out_b)]
+    lanes = [(ctx, pin_out)]
+    for _ in range(args.e2e_lanes - 1):
+        ctx_b = _capi.Context(local_rank)
+        ctx_b.set_potential(name, rc, prm)
+        ctx_b.set_cg(*wl["cg"])
+        ctx_b.set_max_rcut(max(rc * dmax, dmax))
+        ctx_b.set_grid_cartesian(axis, axis)
+        if args.shard == "grid" and world > 1:
+            ctx_b.set_shard(*shards[rank])
+        lanes.append((ctx_b, _capi.PinnedArray((g_local, ncomp_out), np.float64)))
+    nl = len(lanes)
 
     def step_e2e(s, k):
-        c, out = lanes[s % 2]
+        c, out = lanes[s % nl]
         c.upload(pin_pos[k].array, pin_diam[k].array, box)
         c.build_cells()
         c.build_bonds()
@@ -370,8 +373,8 @@ def main():
     # ---- end to end: host buffers in, host field out -----------------------------------------
     for s in range(max(args.warmup, 3)):
         step_e2e(s, s % pool)
-    ctx.sync()
-    ctx_b.sync()
+    for c, _ in lanes:
+        c.sync()
     barrier()
     w2 = time.time()
     ctx.event_record(2)
@@ -381,10 +384,10 @@ def main():
         import threading
 
         def lane_worker(lane):
-            for s in range(lane, args.steps, 2):
+            for s in range(lane, args.steps, nl):
                 step_e2e(s, s % pool)
 
-        workers = [threading.Thread(target=lane_worker, args=(lane,)) for lane in (0, 1)]
+        workers = [threading.Thread(target=lane_worker, args=(lane,)) for lane in range(nl)]
         for t in workers:
             t.start()
         for t in workers:
@@ -392,8 +395,8 @@ def main():
     else:
         for s in range(args.steps):
             step_e2e(s, s % pool)
-    ctx_b.sync()                                   # both lanes drained: the end event below is later than all work
-    ctx.sync()
+    for c, _ in reversed(lanes):                   # every lane drained: the end event below is later than all work
+        c.sync()
     ctx.event_record(3)
     ctx.sync()
     barrier()
@@ -417,7 +420,7 @@ def main():
     value = total_units / (ms_resident * 1e-3)
     e2e_value = total_units / (ms_e2e * 1e-3)
     launches_total = int(sum_over_ranks(launches_resident))
-    e2e_check = float(np.abs(pin_out.array).sum() + np.abs(pin_out_b.array).sum())   # the read-backs are real
+    e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
     assert np.isfinite(e2e_check) and e2e_check > 0
     ik_avg_ms = float(np.mean([m for _, m in ik_ms]))
     flops_avg = float(np.mean([flops_per_frame[k] for k, _ in ik_ms])) * (g_local / G if args.shard == "grid" else 1.0)
@@ -453,7 +456,7 @@ def main():
                        "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
             "clocks": sampler.summary([(w0, w1), (w2, w3)]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames double-buffered over two contexts, %d host thread(s)" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_threads)},
+                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames pipelined over %d contexts, %s" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread")},
             "gpu_launches": launches_total,
             "stage_ms": {"cells": float(np.mean(stage_ms["cells"])), "bonds": float(np.mean(stage_ms["bonds"])), "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_gather", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
