@@ -167,7 +167,9 @@ int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
 int pgt_host_alloc(void** ptr, uint64_t bytes);
 int pgt_host_free(void* ptr);
 /* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 4 tile gather, 5 / 6 walk gather with records via L1 / staged);
- * "bond_single_search" (1 default: one neighbour search per frame, 0: separate count and fill searches). */
+ * "bond_single_search" (1 default: one neighbour search per frame, 0: separate count and fill searches);
+ * "bond_fill_flat" (1 default: warp-flattened record writer, 0: thread per particle).  Every setting gives the same
+ * bits.  Environment, read once: PGT_IK_VARIANT, PGT_BOND_FILL_FLAT, PGT_SCAN_SINGLE_PASS (0: three-kernel scan). */
 int pgt_set_option(pgt_ctx* ctx, const char* name, double value);
 
 /* ---- multi-GPU (NCCL over NVLink) ---------------------------------------------------------- */
