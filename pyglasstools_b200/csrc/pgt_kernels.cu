@@ -786,8 +786,8 @@ __device__ __forceinline__ double bond_quadrature(double c0, double c1, double c
 #define IK2_THREADS (IK2_WARPS * 32)
 #define IK2_TILE_I (IK2_WARPS * 2)
 #define IK2_TILE_J 16
-#define IK2_MAXS 32            // slots buffered per grid point per pass
-#define IK2_OWNER_CAP 256      // owner-table entries per half-warp window
+#define IK2_MAXS 24            // slots buffered per grid point per pass (shared memory per CTA sets the L1 size: see DESIGN 4.1)
+#define IK2_OWNER_CAP 128      // owner-table entries per half-warp window
 
 struct IK2WarpSmem {
     unsigned list[IK2_MAXS * 33];          // [slot][grid point], row padded to 33 words
