@@ -461,6 +461,18 @@ ORC_API double orc_bond(const OrcCG* cg, const double* x, const double* ri, cons
     return orc_bond_any(cg, gl, x, ri, rij, nullptr);
 }
 
+// gsl_integration_qag(key = 1) for a C callback: what oracle/stubs/gsl/gsl_integration.h hands the reference's
+// cgfunc/Quadrature.h when the reference's own loops are compiled against the stand-ins (oracle/ref_loops_shim.cpp)
+ORC_API int orc_gsl_qag15(double (*f)(double, void*), void* params, double a, double b, double epsabs, double epsrel, int limit,
+                          double* result, double* abserr)
+{
+    int status = 0;
+    double err = 0.0;
+    *result = orc_qag15([&](double t) { return f(t, params); }, a, b, epsabs, epsrel, limit, &status, &err);
+    if (abserr) *abserr = err;
+    return status;
+}
+
 // generic test hook: integral of one of a few closed-form integrands over [a, b] with the QAG restatement
 ORC_API double orc_qag_test(int which, double a, double b, double epsabs, double epsrel, int limit, int* status, double* abserr)
 {

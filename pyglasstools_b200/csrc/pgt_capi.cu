@@ -136,8 +136,10 @@ struct pgt_ctx {
     int n_live = 0;
     long long n_hb = 0;
     DevBuf cell_of, cell_count, cell_fill, sorted_orig, scan_scratch, eflags;
-    DevBuf sx, sy, sd, skxx, skxy, skyy;
-    DevBuf hb_cnt, hb_b, hb_cf, hb_j, nb_list;
+    DevBuf sx, sy, sxy, sd, skxx, skxy, skyy;
+    DevBuf hb_cnt, hb_b, hb_cf, hb_j, hb_pm, nb_list;
+    bool hb_pm_valid = false;         // the primary masks cover every particle's records (single-search path, <= 16 bonds each)
+    DevBuf gl_nodes, gl_weights;      // this context's quadrature rule (never shared between contexts)
     bool bond_single_search = true;   // option "bond_single_search"
     bool bond_fill_flat = true;       // option "bond_fill_flat": warp-flattened record writer (else thread per particle)
     double hb_cscale = 1.0;   // scale folded into the records' |b|^2 entry (1/R^2 of the CG function, or 1)
@@ -165,12 +167,12 @@ struct pgt_ctx {
     cudaEvent_t user_ev[16]{};
 
     // tuning
-    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 4: tile gather; 5 / 6: walk gather (records via L1 / staged)
+    int ik_variant = 0;   // 0: automatic; 2: two-phase gather; 7: quad gather (where applicable)
     int quad_mode = PGT_QUAD_FIXEDPOINT;     // PGT_QUAD_ADAPTIVE: QAG / GK15 bond quadrature
     double qag_epsabs = 0.0, qag_epsrel = 0.0;
     int qag_limit = 0;
     bool grid_monotone = false;
-    double tspan_x = -1.0, tspan_y = -1.0;   // extent of the walk gather's grid tile (cartesian grids)
+    double span_x[4] = { -1, -1, -1, -1 }, span_y[4] = { -1, -1, -1, -1 };   // extents of the quad gather's grid tiles (cartesian grids)
 
     // nccl
     pgtNcclComm comm = nullptr;
@@ -237,6 +239,7 @@ PgtFrameView frame_view(const pgt_ctx* c)
     v.n = c->n_live;
     v.sx = c->sx.as<double>();
     v.sy = c->sy.as<double>();
+    v.sxy = c->sxy.as<double2>();
     v.sd = c->sd.as<double>();
     const bool kin = c->src_vel != nullptr;
     v.skxx = kin ? c->skxx.as<double>() : nullptr;
@@ -248,6 +251,7 @@ PgtFrameView frame_view(const pgt_ctx* c)
     v.hb_b = c->hb_b.as<double2>();
     v.hb_cf = c->hb_cf.as<double2>();
     v.hb_j = c->hb_j.as<int>();
+    v.hb_pm = c->hb_pm_valid ? c->hb_pm.as<unsigned short>() : nullptr;
     v.n_hb = c->n_hb;
     v.hb_cscale = c->hb_cscale;
     return v;
@@ -310,7 +314,7 @@ int pgt_ctx_create(int device, pgt_ctx** out)
     if (const char* env = getenv("PGT_BOND_FILL_FLAT")) ctx->bond_fill_flat = atoi(env) != 0;
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
-        if (l == 0 || l == 2 || l == 4 || l == 5 || l == 6) ctx->ik_variant = l;
+        if (l == 0 || l == 2 || l == 7) ctx->ik_variant = l;
     }
     *out = ctx;
     return PGT_OK;
@@ -323,8 +327,9 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     cudaStreamSynchronize(ctx->stream);
     if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
     DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
-                       &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sd, &ctx->skxx, &ctx->skxy,
-                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->nb_list, &ctx->gxs, &ctx->gys, &ctx->gpts,
+                       &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sxy, &ctx->sd, &ctx->skxx, &ctx->skxy,
+                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->hb_pm, &ctx->nb_list, &ctx->gl_nodes,
+                       &ctx->gl_weights, &ctx->gxs, &ctx->gys, &ctx->gpts,
                        &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->out_elastic, &ctx->disp, &ctx->pack, &ctx->thermo_partials,
                        &ctx->thermo_out,
                        &ctx->comm_scratch };
@@ -428,7 +433,10 @@ int pgt_cg_set(pgt_ctx* ctx, int kernel_id, double cg_rcut, int quad_mode, int o
     }
     if (ctx->nq == 5)
         for (int k = 0; k < 5; ++k) { ctx->gl_s[k] = s[k]; ctx->gl_w[k] = ww[k]; }
-    CK(pgt_upload_gl_tables(s.data(), ww.data(), ctx->nq, ctx->stream));
+    ENSURE(ctx->gl_nodes, sizeof(double) * PGT_MAX_GL);
+    ENSURE(ctx->gl_weights, sizeof(double) * PGT_MAX_GL);
+    CK(cudaMemcpyAsync(ctx->gl_nodes.p, s.data(), sizeof(double) * ctx->nq, cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->gl_weights.p, ww.data(), sizeof(double) * ctx->nq, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));   // s/ww are stack-owned
     ctx->quad_mode = PGT_QUAD_FIXEDPOINT;
     ctx->have_cg = true;
@@ -588,6 +596,7 @@ int pgt_build_cells(pgt_ctx* ctx)
     const size_t nl = (size_t)std::max(ctx->n_live, 1);
     ENSURE(ctx->sx, sizeof(double) * nl);
     ENSURE(ctx->sy, sizeof(double) * nl);
+    ENSURE(ctx->sxy, sizeof(double2) * nl);
     ENSURE(ctx->sd, sizeof(double) * nl);
     const bool kin = ctx->src_vel != nullptr;
     if (kin) {
@@ -597,7 +606,7 @@ int pgt_build_cells(pgt_ctx* ctx)
     }
     pgt_launch_gather_sorted(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box,
                              ctx->sorted_orig.as<int>(), ctx->n_live, ctx->sx.as<double>(), ctx->sy.as<double>(),
-                             ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr, kin ? ctx->skxy.as<double>() : nullptr,
+                             ctx->sxy.as<double2>(), ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr, kin ? ctx->skxy.as<double>() : nullptr,
                              kin ? ctx->skyy.as<double>() : nullptr, ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     stage_end(ctx, PGT_STAGE_CELLS);
@@ -623,9 +632,11 @@ int pgt_build_bonds(pgt_ctx* ctx)
     bool listed = ctx->bond_single_search && n > 0 && n < (1 << 28);
     if (listed) {
         ENSURE(ctx->nb_list, sizeof(unsigned) * PGT_NB_SLOTS * (size_t)n);
+        ENSURE(ctx->hb_pm, sizeof(unsigned short) * (size_t)n);
         CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
         pgt_launch_bonds(4, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(),
-                         PgtBondOut{ nullptr, nullptr, ctx->eflags.as<int>() }, 1.0, ctx->nb_list.as<int>(), ctx->stream, &ctx->launches);
+                         PgtBondOut{ ctx->hb_pm.as<double2>(), nullptr, ctx->eflags.as<int>() }, 1.0, ctx->nb_list.as<int>(), ctx->stream,
+                         &ctx->launches);
     } else {
         pgt_launch_bonds(0, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), PgtBondOut{}, 1.0, nullptr,
                          ctx->stream, &ctx->launches);
@@ -640,6 +651,7 @@ int pgt_build_bonds(pgt_ctx* ctx)
         listed = false;
     }
     ctx->n_hb = h[0];
+    ctx->hb_pm_valid = listed;
     const size_t nb = (size_t)std::max<long long>(ctx->n_hb, 1);
     ENSURE(ctx->hb_b, sizeof(double2) * nb);
     ENSURE(ctx->hb_cf, sizeof(double2) * nb);
@@ -678,7 +690,7 @@ int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double*
     CK(cudaMemcpyAsync(ctx->gxs.p, xs, sizeof(double) * nx, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaMemcpyAsync(ctx->gys.p, ys, sizeof(double) * ny, cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    // largest extent of an aligned 16 x 8 tile of grid points (sizes the walk gather's shared-memory rectangle)
+    // largest extent of an aligned tile of grid points (sizes the quad gather's shared-memory rectangle)
     auto span = [](const double* v, int n, int t) {
         double s = 0.0;
         for (int a = 0; a < n; a += t) {
@@ -689,8 +701,10 @@ int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double*
         return s;
     };
     ctx->grid_monotone = std::is_sorted(xs, xs + nx) && std::is_sorted(ys, ys + ny);
-    ctx->tspan_x = span(xs, nx, 16);
-    ctx->tspan_y = span(ys, ny, 8);
+    for (int w = 1; w <= 4; ++w) {
+        ctx->span_x[w - 1] = nx > 0 ? span(xs, nx, 8 * w) : -1.0;
+        ctx->span_y[w - 1] = ny > 0 ? span(ys, ny, 4 * w) : -1.0;
+    }
     ctx->grid_mode = 0;
     ctx->nx = nx;
     ctx->ny = ny;
@@ -739,6 +753,8 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if ((obs_mask & PGT_OBS_ELASTIC) && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no pair potential");
     if (ctx->cg.rcut >= ctx->box.L[0] || ctx->cg.rcut >= ctx->box.L[1])
         return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
+    if (ctx->n_live >= (1 << 28))
+        return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_ik_compute: %d live particles; the gather's packed lists address 2^28", ctx->n_live);
     CK(cudaSetDevice(ctx->device));
     const long long gl = ctx->g1 - ctx->g0;
     const size_t n = (size_t)std::max<long long>(gl, 1);
@@ -810,8 +826,7 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.grid.g0 = ctx->g0;
     a.grid.g1 = ctx->g1;
     a.grid.monotone = ctx->grid_monotone ? 1 : 0;
-    a.grid.tspan_x = ctx->tspan_x;
-    a.grid.tspan_y = ctx->tspan_y;
+    for (int w = 0; w < 4; ++w) { a.grid.span_x[w] = ctx->span_x[w]; a.grid.span_y[w] = ctx->span_y[w]; }
     a.box = ctx->box;
     a.cells = ctx->cells;
     a.cg = ctx->cg;
@@ -823,6 +838,8 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.gl5_h1 = ctx->gl5[0]; a.gl5_h1sq = ctx->gl5[1]; a.gl5_h2 = ctx->gl5[2]; a.gl5_h2sq = ctx->gl5[3];
     a.gl5_w0 = ctx->gl5[4]; a.gl5_w1 = ctx->gl5[5]; a.gl5_w2 = ctx->gl5[6];
     for (int k = 0; k < 5; ++k) { a.gl_s[k] = ctx->gl_s[k]; a.gl_w[k] = ctx->gl_w[k]; }
+    a.gl_nodes = ctx->gl_nodes.as<double>();
+    a.gl_weights = ctx->gl_weights.as<double>();
     a.out_virial = ctx->out_virial.as<double>();
     a.out_kinetic = ctx->out_kinetic.as<double>();
     a.out_density = ctx->out_density.as<double>();
@@ -887,7 +904,7 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
     if (!ctx || !name) return PGT_ERR_ARG;
     if (!strcmp(name, "ik_variant")) {
         const int l = (int)value;
-        if (l != 0 && l != 2 && l != 4 && l != 5 && l != 6) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase), 4 (tile), 5 or 6 (walk)");
+        if (l != 0 && l != 2 && l != 7) return fail(ctx, PGT_ERR_ARG, "ik_variant must be 0 (auto), 2 (two-phase) or 7 (quad)");
         ctx->ik_variant = l;
         return PGT_OK;
     }

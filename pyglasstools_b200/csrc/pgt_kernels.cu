@@ -5,20 +5,16 @@
 #include "pgt_kernels.cuh"
 #include <math_constants.h>
 #include <limits.h>
+#include <stdio.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <type_traits>
 
 #define FULL_MASK 0xffffffffu
 
-__constant__ double c_gl_s[PGT_MAX_GL];   // quadrature nodes on [0,1]:  0.5 +- 0.5 x_i
-__constant__ double c_gl_w[PGT_MAX_GL];   // weights times (b-a)/2 = 0.5
-
-cudaError_t pgt_upload_gl_tables(const double* s, const double* w, int n, cudaStream_t st)
-{
-    cudaError_t e = cudaMemcpyToSymbolAsync(c_gl_s, s, sizeof(double) * n, 0, cudaMemcpyHostToDevice, st);
-    if (e != cudaSuccess) return e;
-    return cudaMemcpyToSymbolAsync(c_gl_w, w, sizeof(double) * n, 0, cudaMemcpyHostToDevice, st);
-}
+// The Gauss-Legendre nodes (0.5 +- 0.5 x_i on [0,1]) and weights (times (b-a)/2 = 0.5) belong to the CONTEXT: PgtIKArgs
+// carries the 5-point rule by value (kernel-parameter constant bank) and a per-context device table for every other
+// order, so two contexts on one device never see each other's rule.
 
 // ------------------------------------------------------------------------------------------
 // small helpers
@@ -361,8 +357,8 @@ template <bool F32>
 __global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ pos, const void* __restrict__ diam,
                                                        const void* __restrict__ mass, const void* __restrict__ vel, PgtBox box,
                                                        const int* __restrict__ sorted_orig, int n_live, double* __restrict__ sx,
-                                                       double* __restrict__ sy, double* __restrict__ sd, double* __restrict__ skxx,
-                                                       double* __restrict__ skxy, double* __restrict__ skyy)
+                                                       double* __restrict__ sy, double2* __restrict__ sxy, double* __restrict__ sd,
+                                                       double* __restrict__ skxx, double* __restrict__ skxy, double* __restrict__ skyy)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n_live) return;
@@ -371,6 +367,7 @@ __global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ 
     load_wrapped<F32>(pos, i, box, x, y, nullptr);
     sx[p] = x;
     sy[p] = y;
+    sxy[p] = make_double2(x, y);                 // 16-byte rows: what the quad gather's bulk copies move
     sd[p] = ld_real<F32>(diam, i);
     if (skxx) {
         const double m = mass ? ld_real<F32>(mass, i) : 1.0;
@@ -384,13 +381,13 @@ __global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ 
 }
 
 void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, double* sx, double* sy, double* sd, double* skxx,
+                              const int* sorted_orig, int n_live, double* sx, double* sy, double2* sxy, double* sd, double* skxx,
                               double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (n_live <= 0) return;
     const int blocks = (n_live + 255) / 256;
-    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sd, skxx, skxy, skyy);
-    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sd, skxx, skxy, skyy);
+    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sxy, sd, skxx, skxy, skyy);
+    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sxy, sd, skxx, skxy, skyy);
     lc->n++;
 }
 
@@ -496,19 +493,25 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
 // where some particle has more than PGT_NB_SLOTS bonds.
 template <int MODEL>
 __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
-                                                    int* __restrict__ counts, unsigned* __restrict__ nb_list, int* __restrict__ eflags)
+                                                    int* __restrict__ counts, unsigned* __restrict__ nb_list,
+                                                    unsigned short* __restrict__ prim_mask, int* __restrict__ eflags)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= fr.n) return;
     const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
     int n = 0;
+    unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (p < q)
     for_each_neighbor_img(fr, box, cells, p, xi, yi, rc2, [&](int q, double, double, double rsq, unsigned code) {
         const double dj = __ldg(fr.sd + q);
         if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
-        if (n < PGT_NB_SLOTS) nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
+        if (n < PGT_NB_SLOTS) {
+            nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
+            if (p < q) pm |= 1u << n;
+        }
         ++n;
     });
     counts[p] = n;
+    prim_mask[p] = (unsigned short)pm;
     if (n > PGT_NB_SLOTS) atomicOr(eflags, PGT_EFLAG_BOND_OVERFLOW);
 }
 
@@ -582,7 +585,8 @@ static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, Pgt
 {
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
-    case 4: k_bonds_find<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, reinterpret_cast<unsigned*>(nbr_j), out.j); break;
+    case 4: k_bonds_find<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, reinterpret_cast<unsigned*>(nbr_j),
+                                                        reinterpret_cast<unsigned short*>(out.b), out.j); break;
     case 5: k_bonds_fill_flat<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 6: k_bonds_fill_list<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
@@ -732,39 +736,92 @@ void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells 
 // order (FixedPointQuadrature.h:35-45) and  B S  (S = f b(x)b, precomputed per bond) goes into three
 // accumulators; 0.5 norm sum is VirialStress::compute_cg.  No global atomics anywhere.
 template <int KERNEL, int Q>
-__device__ __forceinline__ double bond_quadrature(double c0, double c1, double c2, int nq)
+__device__ __forceinline__ double bond_quadrature(const PgtIKArgs& A, double c0, double c1, double c2)
 {
     double B = 0.0;
-    if (Q > 0 && KERNEL == PGT_CG_OCTIC) {
+    if (Q == 5 && KERNEL == PGT_CG_OCTIC) {
         // octic: g = 1 - t^2 is positive exactly when t < 1, so the cut-off is a clamp of g at zero, done on the sign
         // word (a cleared high word leaves at most a denormal, whose square is zero); two partial sums
         double B1 = 0.0;
 #pragma unroll
-        for (int k = 0; k < Q; ++k) {
-            const double s = c_gl_s[k];
+        for (int k = 0; k < 5; ++k) {
+            const double s = A.gl_s[k];
             const double t = fma(fma(c2, s, c1), s, c0);
             const double g = fma(-t, t, 1.0);
             const int hi = __double2hiint(g);
             const double gc = __hiloint2double(hi & ~(hi >> 31), __double2loint(g));
-            if (k & 1) B1 = fma(c_gl_w[k] * gc, gc, B1); else B = fma(c_gl_w[k] * gc, gc, B);
+            if (k & 1) B1 = fma(A.gl_w[k] * gc, gc, B1); else B = fma(A.gl_w[k] * gc, gc, B);
         }
         B += B1;
-    } else if (Q > 0) {
+    } else if (Q == 5) {
 #pragma unroll
-        for (int k = 0; k < Q; ++k) {
-            const double s = c_gl_s[k];
+        for (int k = 0; k < 5; ++k) {
+            const double s = A.gl_s[k];
             const double t = fma(fma(c2, s, c1), s, c0);
             // t < 1 on the sign/exponent word: also true for the tiny negative t rounding can produce
-            if (__double2hiint(t) < 0x3FF00000) B = fma(c_gl_w[k], pgt_cg_shape<KERNEL>(t), B);
+            if (__double2hiint(t) < 0x3FF00000) B = fma(A.gl_w[k], pgt_cg_shape<KERNEL>(t), B);
         }
     } else {
-        for (int k = 0; k < nq; ++k) {
-            const double s = c_gl_s[k];
+        for (int k = 0; k < A.nq; ++k) {
+            const double s = __ldg(A.gl_nodes + k);
             const double t = fma(fma(c2, s, c1), s, c0);
-            if (__double2hiint(t) < 0x3FF00000) B = fma(c_gl_w[k], pgt_cg_shape<KERNEL>(t), B);
+            if (__double2hiint(t) < 0x3FF00000) B = fma(__ldg(A.gl_weights + k), pgt_cg_shape<KERNEL>(t), B);
         }
     }
     return B;
+}
+
+// Rect is discontinuous at the disc edge, so its quadrature nodes are tested in the reference's own operation order
+// (CoarseGrainFunction.h:42-45, 77-88 with ri = x - dr, rij = -dx of IrvingKirkwood.h:85-101): a node can never fall on
+// the other side of d^2 < R^2 than it does in the reference.  a = r_i - (x + kL) exactly as the search formed it.
+template <int Q>
+__device__ __forceinline__ double rect_bond_exact(const PgtIKArgs& A, double gx, double gy, double ax, double ay, double2 b)
+{
+    const double rix = gx - ax, riy = gy - ay;               // ri = x - dr
+    const double rjx = -b.x, rjy = -b.y;                     // rij = -dx
+    const double R2 = A.cg.rcutsq;
+    double B = 0.0;
+    const int nq = Q > 0 ? Q : A.nq;
+    for (int k = 0; k < nq; ++k) {
+        const double s = (Q == 5) ? A.gl_s[k] : __ldg(A.gl_nodes + k);
+        const double w = (Q == 5) ? A.gl_w[k] : __ldg(A.gl_weights + k);
+        const double px = rix + s * rjx, py = riy + s * rjy; // ri + s rij
+        const double dx = gx - px, dy = gy - py;             // x - (ri + s rij)
+        const double d2 = dx * dx + dy * dy;                 // (+ 0 for z)
+        if (d2 < R2) B += w;
+    }
+    return B;
+}
+
+// The same sum for the quad gather's integration loop: 5-point octic with the square formed once per node.
+template <int KERNEL, int Q>
+__device__ __forceinline__ double ik_quadrature(const PgtIKArgs& A, double c0, double c1, double c2)
+{
+    if (KERNEL == PGT_CG_OCTIC && Q == 5) {
+        double B0 = 0.0, B1 = 0.0;
+#pragma unroll
+        for (int k = 0; k < 5; ++k) {
+            const double s = A.gl_s[k];
+            const double t = fma(fma(c2, s, c1), s, c0);
+            const double g = fma(-t, t, 1.0);
+            const int hi = __double2hiint(g);
+            const double gc = __hiloint2double(hi & ~(hi >> 31), __double2loint(g));
+            const double gg = gc * gc;
+            if (k & 1) B1 = fma(A.gl_w[k], gg, B1); else B0 = fma(A.gl_w[k], gg, B0);
+        }
+        return B0 + B1;
+    }
+    return bond_quadrature<KERNEL, Q>(A, c0, c1, c2);
+}
+
+// at most one image can be within R < L/2: the nearest one; then the exact Aboria test (Search.h:186-193, 438-447)
+__device__ __forceinline__ bool in_disc_exact(double px, double py, double gx, double gy, const PgtBox& box, double R2)
+{
+    const double ddx = px - gx, ddy = py - gy;
+    const int kx = ddx > 0.5 * box.L[0] ? +1 : (ddx < -0.5 * box.L[0] ? -1 : 0);
+    const int ky = ddy > 0.5 * box.L[1] ? +1 : (ddy < -0.5 * box.L[1] ? -1 : 0);
+    const double ax = px - (gx + kx * box.L[0]), ay = py - (gy + ky * box.L[1]);
+    return !(ax * ax + ay * ay > R2);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -940,8 +997,8 @@ __global__ void __launch_bounds__(IK2_THREADS) k_ik_gather2(const PgtIKArgs A, c
                             hb0 = __ldg(fr.hb_off + p);
                             nb = __ldg(fr.hb_off + p + 1) - hb0;
                         }
-                        a2x = ax * (2.0 * iR2);
-                        a2y = ay * (2.0 * iR2);
+                        if (KERNEL == PGT_CG_RECT) { a2x = ax; a2y = ay; }      // rect: the exact-order node test wants a itself
+                        else { a2x = ax * (2.0 * iR2); a2y = ay * (2.0 * iR2); }
                         c0 = d2 * iR2;
                     }
                     // prefix sum of the half-bond counts inside each half
@@ -977,8 +1034,12 @@ __global__ void __launch_bounds__(IK2_THREADS) k_ik_gather2(const PgtIKArgs A, c
                                 const double2 b = __ldg(fr.hb_b + rec);
                                 const double2 cf = __ldg(fr.hb_cf + rec);
                                 const double2 a2 = sm.s_a[half][o];
-                                const double c1 = fma(a2.x, b.x, a2.y * b.y);
-                                const double B = bond_quadrature<KERNEL, Q>(sm.s_c0[half][o], c1, cf.x, A.nq);
+                                double B;
+                                if (KERNEL == PGT_CG_RECT) B = rect_bond_exact<Q>(A, gxg, gyg, a2.x, a2.y, b);
+                                else {
+                                    const double c1 = fma(a2.x, b.x, a2.y * b.y);
+                                    B = bond_quadrature<KERNEL, Q>(A, sm.s_c0[half][o], c1, cf.x);
+                                }
                                 const double wf = B * cf.y;
                                 const double tx = wf * b.x, ty = wf * b.y;
                                 axx = fma(tx, b.x, axx);
@@ -1061,22 +1122,20 @@ static cudaError_t launch_ik2(const PgtIKArgs& a, cudaStream_t st)
     }
 }
 
-#include "pgt_ik_tile.inl"
-#include "pgt_ik_walk.inl"
+#include "pgt_ik_quad.inl"
 
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc)
 {
     lc->n++;
-    // measured on B200 (cfg5, 2048^2): two-phase 1.85 ms, tile 3.5 ms (its integer bookkeeping -- staging, bitmap walks --
-    // outweighs the 1.5x fewer quadratures) -> automatic = two-phase; the tile kernel stays selectable (variant 4)
-    if (variant == 4 && ik_tile_applicable(a)) return launch_ik_tile(a, st);   // Cartesian grids, virial field only
-    if ((variant == 5 || variant == 6) && ik_walk_applicable(a)) {            // 5: records through L1, 6: staged in shared memory
-        IKWCaps caps;
+    // automatic: the quad gather (unique bonds, records staged by bulk copies) wherever it applies -- Cartesian grids,
+    // virial field only, a frame whose bond list carries primary masks; everything else (point lists, kinetic and
+    // density fields) is the two-phase kernel
+    if (variant != 2 && ik_quad_applicable(a)) {
+        IKQCaps caps;
         size_t dyn = 0;
-        const bool stage = variant == 6;
-        if (ikw_pick_caps(a, stage, &caps, &dyn)) return launch_ik_walk(a, caps, dyn, stage, st);
+        if (ikq_pick_caps(a, &caps, &dyn)) return launch_ik_quad(a, caps, dyn, st);
     }
-    return launch_ik2(a, st);                                                  // two-phase kernel (any point list, local fields)
+    return launch_ik2(a, st);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -1265,8 +1324,8 @@ __global__ void __launch_bounds__(128) k_ik_elastic(const PgtPot pot, const PgtI
                     } else {
                         B = 0.0;
                         for (int k = 0; k < A.nq; ++k) {
-                            const double t = c_gl_s[k], px = ax + t * dx, py = ay + t * dy;
-                            B += c_gl_w[k] * pgt_cg_delta_exact(cg, px * px + py * py);
+                            const double t = __ldg(A.gl_nodes + k), px = ax + t * dx, py = ay + t * dy;
+                            B += __ldg(A.gl_weights + k) * pgt_cg_delta_exact(cg, px * px + py * py);
                         }
                     }
                     const int oj = __ldg(fr.sorig + q);
@@ -1298,16 +1357,6 @@ cudaError_t pgt_launch_ik_elastic(const PgtPot& pot, const PgtIKArgs& a, const d
 // Work counter for the roofline numerator (not on the hot path): one thread per grid point.
 //   out[0] += U(x): unique force-carrying bonds with >= 1 endpoint in the disc (both tests exact)
 //   out[1] += half-bond items the gather integrates,  out[2] += particles in the disc
-__device__ __forceinline__ bool in_disc_exact(double px, double py, double gx, double gy, const PgtBox& box, double R2)
-{
-    // at most one image can be within R < L/2: the nearest one
-    const double ddx = px - gx, ddy = py - gy;
-    const int kx = ddx > 0.5 * box.L[0] ? +1 : (ddx < -0.5 * box.L[0] ? -1 : 0);
-    const int ky = ddy > 0.5 * box.L[1] ? +1 : (ddy < -0.5 * box.L[1] ? -1 : 0);
-    const double ax = px - (gx + kx * box.L[0]), ay = py - (gy + ky * box.L[1]);
-    return !(ax * ax + ay * ay > R2);
-}
-
 __global__ void __launch_bounds__(128) k_ik_count(const PgtIKArgs A, unsigned long long* __restrict__ out)
 {
     const long long g = A.grid.g0 + (long long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -3,7 +3,7 @@
 // Stage map (BASELINE.json north_star):
 //   0/1  k_wrap_count, scan, k_scatter_ids, k_cell_sort, k_gather_sorted   (cell list, counting sort)
 //   2/3  k_bonds_find<MODEL> + scan + k_bonds_fill_flat<MODEL>             (pair force + compacted half-bonds)
-//   4/5  k_ik_gather2 (default), k_ik_walk / k_ik_tile (Cartesian grids), k_ik_adaptive, k_ik_elastic   (IK field gather)
+//   4/5  k_ik_quad (Cartesian grids, virial field), k_ik_gather2 (any point list, local fields), k_ik_adaptive, k_ik_elastic
 //   6    k_thermo_pairs<MODEL>, k_thermo_final                             (global virial / energy / Born / kinetic)
 // All arithmetic is FP64; no tensor cores (there is no dense contraction on this path).
 #pragma once
@@ -35,6 +35,7 @@ struct PgtFrameView {
     int n;                       // live particles
     const double* sx;            // wrapped x
     const double* sy;            // wrapped y
+    const double2* sxy;          // (x, y) interleaved: 16-byte rows for the quad gather's bulk copies
     const double* sd;            // diameter
     const double* skxx;          // (m vx) vx   (NULL when the frame has no velocities)
     const double* skxy;          // (m vx) vy
@@ -47,6 +48,8 @@ struct PgtFrameView {
     const double2* hb_b;         // b = r_j(image) - r_i, exactly as the reference's inner search forms it
     const double2* hb_cf;        // (|b|^2 * cscale,  f = -phi'(r)/r)
     const int* hb_j;             // sorted index of j
+    const unsigned short* hb_pm; // per particle: bit k set when its k-th record is the bond's primary end (i < j); NULL when
+                                 // the list was built by the two-search path (some particle has more than 16 bonds)
     long long n_hb;              // half-bonds in the list (host-side sizing of the walk gather's tiles)
     double hb_cscale;            // scale folded into hb_cf.x: 1/R^2 of the CG function the list was built for
 };
@@ -65,7 +68,7 @@ struct PgtGridView {
     const double* pts;           // G x 3
     long long g0, g1;            // shard
     int monotone;                // cartesian: both axes non-decreasing (np.linspace)
-    double tspan_x, tspan_y;     // cartesian: largest extent of an aligned 16 (x) by 8 (y) tile of grid points; < 0 unknown
+    double span_x[4], span_y[4]; // cartesian: largest extent of an aligned tile of 8 w (x) / 4 w (y) grid points, w = index + 1; < 0 unknown
 };
 
 struct PgtIKArgs {
@@ -79,6 +82,8 @@ struct PgtIKArgs {
     // 5-point rule in symmetric form on [0,1]: nodes 0.5 +- h_k, weights w_k (already times (b-a)/2)
     double gl5_h1, gl5_h1sq, gl5_h2, gl5_h2sq, gl5_w0, gl5_w1, gl5_w2;
     double gl_s[5], gl_w[5];     // the 5-point rule in GSL's visiting order (valid when nq == 5), for constant-bank operands
+    const double* gl_nodes;      // per-context device table: nq nodes on [0,1] in GSL's visiting order
+    const double* gl_weights;    //                           nq weights times (b-a)/2
     double* out_virial;          // (g1-g0) x 4
     double* out_kinetic;         // (g1-g0) x 4
     double* out_density;         // (g1-g0)
@@ -92,8 +97,6 @@ struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 
 // ---- launch wrappers (defined in pgt_kernels.cu) ---------------------------------------------
 struct PgtLaunchCounter { long long n; };
 
-cudaError_t pgt_upload_gl_tables(const double* s, const double* w, int n, cudaStream_t st);
-
 void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
                            int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* block_sums, cudaStream_t st, PgtLaunchCounter* lc);
@@ -102,19 +105,20 @@ void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_sta
                             cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, double* sx, double* sy, double* sd, double* skxx,
+                              const int* sorted_orig, int n_live, double* sx, double* sy, double2* sxy, double* sd, double* skxx,
                               double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
 // mode 2/3: same for plain neighbours within max_rcut (export only);
-// mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word);
+// mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word, out.b = the
+//         per-particle primary masks, unsigned short[n]);
 // mode 5: fill the CSR arrays from that scratch (counts = scanned offsets), warp-flattened; mode 6: same, thread per particle.
 void pgt_launch_bonds(int mode, const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, int* counts,
                       PgtBondOut out, double cscale, int* nbr_j, cudaStream_t st, PgtLaunchCounter* lc);
 // rewrites hb_cf.x of every record for a new scale (the CG radius changed after the list was built)
 void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_hb, double cscale, cudaStream_t st,
                               PgtLaunchCounter* lc);
-// variant 0: automatic; 2: two-phase kernel; 4: tile kernel, 5 / 6: walk kernel with records through L1 / staged in shared
-// memory (4-6: Cartesian grids + virial only, else two-phase)
+// variant 0: automatic (quad gather on Cartesian grids with the virial field only, else two-phase); 2: two-phase kernel;
+// 7: quad gather where applicable
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 // virial field with the adaptive (QAG, 15-point Gauss-Kronrod) bond quadrature; failures are OR-ed into *eflags
 cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
