@@ -36,22 +36,23 @@
 #define IKQ_PY 4
 #define IKQ_MAXROWS 32
 #define IKQ_MAXRUNS (2 * IKQ_MAXROWS)
-#define IKQ_MAXCOLS 62
-#define IKQ_LCS (IKQ_MAXCOLS + 2)
 #define IKQ_MAX_THREADS 256               // 2 CTAs of 256 threads per SM (shared memory bound): up to 128 registers each
-#define IKQ_BOTH 0x8000u
-#define IKQ_MAX_NREC 0x7FFF              // a list entry addresses 15 bits
+#define IKQ_SEC 0x8000u                   // list entry: kept from the bond's secondary end (weight 1/2, no far-end test)
+#define IKQ_UNSURE 0x4000u                // list entry, transient: the far-end test fell inside the guard band
+#define IKQ_MAX_NREC 0x1FFF               // a list entry / a particle's record range addresses 13 bits
+#define IKQ_STEP_ROOM 6                   // list slots one walk step may touch (4 primary + 2 secondary)
 
 struct IKQCaps {
     int wx, wy;                          // warps per tile along i (x) and j (y)
     int rows_cap;                        // cell rows of the rectangle
+    int lcs_stride;                      // entries per row of the local cell-start table (columns of the rectangle + 1)
     int nloc_cap;                        // particles of the rectangle
     int nrec_cap;                        // half-bond records of the rectangle
-    int list_cap;                        // list entries per thread
-    int list_stride;                     // 16-bit words between two threads' lists (2 x odd: conflict-free columns)
-    int hit_cap;                         // particles of one disc the hit list holds
-    int hit_stride;                      // 16-bit words between two threads' hit lists (2 x odd)
+    int buf_cap;                         // entries of a thread's buffer: disc particles from the top down, list items from the bottom up
+    int buf_stride;                      // 16-bit words between two threads' buffers (2 x odd: conflict-free columns)
     double r2lo, r2hi;                   // |a + b|^2 <= r2lo: inside; > r2hi: outside; between: exact test
+    double t1lo, t1hi;                   // the same band for t(1) = |a + b|^2 / R^2
+    float r2lo32, r2hi32;                // the band of the single-precision disc test of phase 1 (tile-relative coordinates)
 };
 
 struct IKQStatic {
@@ -61,7 +62,7 @@ struct IKQStatic {
     int lp_base[IKQ_MAXRUNS + 1];        // tile-local index of the run's first particle
     int lr_base[IKQ_MAXRUNS + 1];        // tile-local index of the run's first record
     double2 shift[IKQ_MAXRUNS];          // (kx Lx, ky Ly) of the run's periodic image
-    int bad;                             // a particle of the tile has more records than the primary mask covers
+    int bad;                             // a particle of the tile has records the packed range cannot describe
 };
 
 // ---- mbarrier / bulk-copy primitives (PTX ISA 8.x; sm_90+)
@@ -137,14 +138,21 @@ __device__ __noinline__ void ik_slow_path(const PgtIKArgs& A, double gx, double 
     oxx = axx; oxy = axy; oyy = ayy;
 }
 
+// The run of the rectangle that holds tile-local particle l.
+__device__ __forceinline__ int ikq_run_of(const IKQStatic& S, int l, int nruns)
+{
+    int run = 0;
+    while (run + 1 < nruns && l >= S.lp_base[run + 1]) ++run;
+    return run;
+}
+
 // Are the far ends of the records k + u (u in `which`; particle l of the rectangle) found by the reference's search
 // around (gx, gy)?  The exact Aboria test on j's stored position; only reached inside the guard band of the arithmetic
 // test.  Returns `inm` with the bits of `which` replaced by the exact answers.
 __device__ __noinline__ unsigned ikq_exact_far_ends(const PgtIKArgs& A, const IKQStatic& S, int l, int k, unsigned which, unsigned inm,
                                                     double gx, double gy, int nruns)
 {
-    int run = 0;
-    while (run + 1 < nruns && l >= S.lp_base[run + 1]) ++run;      // the run that holds particle l (and so record k)
+    const int run = ikq_run_of(S, l, nruns);                       // the run that holds particle l (and so record k)
     for (int u = 0; u < 4; ++u) {
         if (!((which >> u) & 1u)) continue;
         const int e = S.h0[run] + (k + u - S.lr_base[run]);
@@ -155,16 +163,67 @@ __device__ __noinline__ unsigned ikq_exact_far_ends(const PgtIKArgs& A, const IK
     return inm;
 }
 
+// Is tile-local particle l found by the reference's search around (gx, gy)?  Exact test on its stored position; only
+// reached inside the guard band of phase 1's single-precision test.
+__device__ __noinline__ bool ikq_exact_hit(const PgtIKArgs& A, const IKQStatic& S, int l, double gx, double gy, int nruns)
+{
+    const int run = ikq_run_of(S, l, nruns);
+    const int p = S.ps[run] + (l - S.lp_base[run]);
+    return in_disc_exact(__ldg(A.fr.sx + p), __ldg(A.fr.sy + p), gx, gy, A.box, A.cg.rcutsq);
+}
+
 // shared-memory accesses by 32-bit address (the walk keeps one base register per table)
 __device__ __forceinline__ unsigned ikq_lds_u16(unsigned addr) { unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(addr)); return v; }
 __device__ __forceinline__ unsigned ikq_lds_u32(unsigned addr) { unsigned v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr)); return v; }
-__device__ __forceinline__ void ikq_sts_u16(unsigned addr, unsigned v) { asm volatile("st.shared.u16 [%0], %1;" ::"r"(addr), "h"((unsigned short)v) : "memory"); }
+template <int OFF>
+__device__ __forceinline__ void ikq_sts_u16(unsigned addr, unsigned v) { asm volatile("st.shared.u16 [%0+%2], %1;" ::"r"(addr), "h"((unsigned short)v), "n"(OFF) : "memory"); }
 template <int OFF>
 __device__ __forceinline__ double2 ikq_lds_f64x2(unsigned addr)
 {
     double2 v;
     asm volatile("ld.shared.v2.f64 {%0, %1}, [%2+%3];" : "=d"(v.x), "=d"(v.y) : "r"(addr), "n"(OFF));
     return v;
+}
+__device__ __forceinline__ float2 ikq_lds_f32x2(unsigned addr)
+{
+    float2 v;
+    asm volatile("ld.shared.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+    return v;
+}
+
+// One quad's share of a grid point's list with the far-end tests of the primary items done exactly (the reference's
+// search on j's stored position): the rare redo of a phase-3 pass in which some t(1) fell inside the guard band.
+template <int KERNEL, int Q>
+__device__ __noinline__ void ikq_pass_exact(const PgtIKArgs& A, const IKQStatic& S, const IKQCaps& caps, unsigned lp_addr, int n_p, int sub,
+                                            double gxp, double gyp, int nruns, double& oxx, double& oxy, double& oyy)
+{
+    extern __shared__ __align__(16) unsigned char ikq_dyn[];
+    const double2* const s_b = reinterpret_cast<const double2*>(ikq_dyn);
+    const double2* const s_cf = s_b + caps.nrec_cap;
+    const double2* const s_pos = s_cf + caps.nrec_cap;
+    const unsigned short* const s_own = reinterpret_cast<const unsigned short*>(ikq_dyn + (size_t)caps.nrec_cap * 32 + (size_t)caps.nloc_cap * 28) +
+                                        (size_t)blockDim.x * caps.buf_stride;
+    const double iR2 = A.inv_rcutsq, iR2x2 = 2.0 * A.inv_rcutsq;
+    double axx = 0.0, axy = 0.0, ayy = 0.0;
+    for (int s = sub; s < n_p; s += 4) {
+        const unsigned it = ikq_lds_u16(lp_addr + 2u * (unsigned)s);
+        const unsigned kk = it & (unsigned)IKQ_MAX_NREC;
+        const int l = s_own[kk];
+        const double2 p = s_pos[l], b = s_b[kk], cf = s_cf[kk];
+        const double pax = p.x - gxp, pay = p.y - gyp;
+        const double c0 = fma(pax, pax, pay * pay) * iR2;
+        const double c1 = fma(pax, b.x, pay * b.y) * iR2x2;
+        const double t1 = (c0 + cf.x) + c1;
+        bool half = (it & IKQ_SEC) != 0u || t1 > caps.t1hi;
+        if (!half && t1 > caps.t1lo) half = !(ikq_exact_far_ends(A, S, l, (int)kk, 1u, 0u, gxp, gyp, nruns) & 1u);
+        const double wf = ik_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * cf.y;
+        const double wh = half ? 0.5 : 1.0;
+        const double tx = (wf * wh) * b.x, ty = (wf * wh) * b.y;
+        axx = fma(tx, b.x, axx);
+        axy = fma(tx, b.y, axy);
+        ayy = fma(ty, b.y, ayy);
+    }
+    oxx = axx; oxy = axy; oyy = ayy;
 }
 
 template <int KERNEL, int Q>
@@ -178,18 +237,18 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
     double2* const s_b = reinterpret_cast<double2*>(ikq_dyn);
     double2* const s_cf = s_b + caps.nrec_cap;
     double2* const s_pos = s_cf + caps.nrec_cap;
-    unsigned* const s_rng = reinterpret_cast<unsigned*>(s_pos + caps.nloc_cap);          // k0 | kend << 16 per particle
-    unsigned short* const s_list = reinterpret_cast<unsigned short*>(s_rng + caps.nloc_cap);   // [thread][slot]: bonds to integrate
-    unsigned short* const s_hits = s_list + T * caps.list_stride;                        // [thread][slot]: particles of my disc
-    unsigned short* const s_own = s_hits + T * caps.hit_stride;                          // local index of i per record
-    unsigned short* const s_pm = s_own + caps.nrec_cap;                                  // primary mask per particle
-    unsigned short* const s_lcs = s_pm + caps.nloc_cap;                                  // [row][IKQ_LCS]: first particle of a cell
+    float2* const s_p32 = reinterpret_cast<float2*>(s_pos + caps.nloc_cap);             // tile-relative, single precision (phase 1)
+    unsigned* const s_rng = reinterpret_cast<unsigned*>(s_p32 + caps.nloc_cap);          // first record | secondaries << 13 | primaries << 17
+    unsigned short* const s_buf = reinterpret_cast<unsigned short*>(s_rng + caps.nloc_cap);    // [thread][slot]: disc particles / bonds to integrate
+    unsigned short* const s_own = s_buf + T * caps.buf_stride;                           // local index of i per record
+    unsigned short* const s_lcs = s_own + caps.nrec_cap;                                 // [row][lcs_stride]: first particle of a cell
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const PgtFrameView& fr = A.fr;
-    const double R = A.cg.rcut, R2 = A.cg.rcutsq, iR2 = A.inv_rcutsq;
+    const double R = A.cg.rcut, iR2 = A.inv_rcutsq;
     const int ncx = A.cells.ncx, ncy = A.cells.ncy;
     const unsigned bar = ikq_smem(&s_bar);
+    const int LCS = caps.lcs_stride;
 
     // ---- tile and my grid point: a warp covers a compact 8 x 4 patch
     const int TI = IKQ_PX * caps.wx, TJ = IKQ_PY * caps.wy;
@@ -229,7 +288,7 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
     const int uy1 = __double2int_rd((ymax + R + tpy - A.box.lo[1]) * A.cells.inv_cwy);
     const int ncols = ux1 - ux0 + 1, nrows = uy1 - uy0 + 1;
     // limits; the rectangle plus a bond's reach must not wrap onto itself (one image of every particle)
-    bool fast = ncols <= IKQ_MAXCOLS && nrows <= caps.rows_cap && ncols + 2 * A.cells.reach + 1 <= ncx &&
+    bool fast = ncols + 1 <= LCS && nrows <= caps.rows_cap && ncols + 2 * A.cells.reach + 1 <= ncx &&
                 nrows + 2 * A.cells.reach + 1 <= ncy && ux0 >= -ncx && ux1 < 2 * ncx && uy0 >= -ncy && uy1 < 2 * ncy;
 
     Seg seg[3];
@@ -238,7 +297,6 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
     if (nseg > 2) fast = false;
     const int nruns = 2 * nrows;
     const int csplit = (nseg == 2) ? (seg[0].c1 - seg[0].c0 + 1) : ncols;   // column at which the second segment starts
-    const bool seam = fast && (nseg == 2 || seg[0].k != 0 || uy0 < 0 || uy1 >= ncy);   // some run carries an image shift
 
     int nloc = 0, nrec_total = 0;
     if (fast) {
@@ -281,7 +339,8 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
         __syncthreads();
         nloc = S.lp_base[nruns];
         nrec_total = S.lr_base[nruns];
-        if (nloc > caps.nloc_cap || nrec_total > caps.nrec_cap) fast = false;     // uniform: every thread reads the same totals
+        // uniform: every thread reads the same totals; two spare records: the walk loads a pair of record slots
+        if (nloc > caps.nloc_cap || nrec_total + 2 > caps.nrec_cap) fast = false;
     }
 
     double txx = 0.0, txy = 0.0, tyy = 0.0;
@@ -314,9 +373,9 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
                 const int cell = uy * ncx + (s ? seg[1].c0 + (c - csplit) : seg[0].c0 + c);
                 v = S.lp_base[2 * r + s] + (__ldg(fr.cell_start + cell) - S.ps[2 * r + s]);
             }
-            s_lcs[r * IKQ_LCS + c] = (unsigned short)v;
+            s_lcs[r * LCS + c] = (unsigned short)v;
         }
-        // a warp takes a run: each particle's record range and primary mask, each record's owner
+        // a warp takes a run: each particle's record range (secondary records first, then primary ones), each record's owner
         const int nwarps = T >> 5;
         int bad = 0;
         for (int run = warp; run < nruns; run += nwarps) {
@@ -324,9 +383,11 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
             for (int o = lane; o < np; o += 32) {
                 const int p = ps + o, l = lpb + o;
                 const int k0 = lrb + (__ldg(fr.hb_off + p) - h0), k1 = lrb + (__ldg(fr.hb_off + p + 1) - h0);
-                s_rng[l] = (unsigned)k0 | ((unsigned)k1 << 16);
-                s_pm[l] = __ldg(fr.hb_pm + p);
-                if (k1 - k0 > 16) bad = 1;
+                const unsigned pm = __ldg(fr.hb_pm + p);
+                const int n = k1 - k0, npr = __popc(pm), nsec = n - npr;
+                // the primary records must be the last npr of the n (k_bonds_find's visiting order guarantees it)
+                if (n > 15 || nsec < 0 || pm != (((1u << n) - 1u) & ~((1u << nsec) - 1u))) bad = 1;
+                s_rng[l] = (unsigned)k0 | ((unsigned)(nsec & 15) << 13) | ((unsigned)(npr & 15) << 17);
                 for (int k = k0; k < k1; ++k) s_own[k] = (unsigned short)l;
             }
         }
@@ -344,12 +405,29 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
         return;
     }
 
+    // ---- positions of the tile's periodic image, r - kL (used for the quadrature and the guarded arithmetic tests only,
+    //      never for an exact membership test), and their single-precision copy relative to the tile's corner
+    for (int run = warp; run < nruns; run += (T >> 5)) {
+        const int np = S.np[run], lpb = S.lp_base[run];
+        const double2 sh = S.shift[run];
+        for (int o = lane; o < np; o += 32) {
+            double2 p = s_pos[lpb + o];
+            p.x -= sh.x; p.y -= sh.y;
+            s_pos[lpb + o] = p;
+            s_p32[lpb + o] = make_float2((float)(p.x - xmin), (float)(p.y - ymin));
+        }
+    }
+    __syncthreads();
+
     // ================= phase 1: the particles of my disc, as a list of tile-local indices =================
     // One flat loop over the candidates of all my window rows (a row's candidates are consecutive local indices), so
     // the 32 searches of a warp cost max-over-lanes of the TOTAL candidate count, not the sum of per-row maxima.
+    // The test runs in single precision on tile-relative coordinates (the FP64 pipe is the integration loop's); a
+    // candidate inside the guard band of that test is decided by the exact Aboria test on its stored position.
     const bool active = ingrid && warp_live;
-    bool slow = false;                                     // my disc does not fit the hit list: I take the slow path
-    const unsigned hl_addr = ikq_smem(s_hits + tid * caps.hit_stride);
+    bool slow = false;                                     // my disc does not fit the buffer: I take the slow path
+    const unsigned buf_addr = ikq_smem(s_buf + tid * caps.buf_stride);     // items grow upwards from here
+    const unsigned buf_top = buf_addr + 2u * (unsigned)caps.buf_cap;       // disc particles grow downwards from here
     int nh = 0;                                            // hits
     if (active) {
         const double padx = 1e-9 * (R + fabs(gx) + 1.0), pady = 1e-9 * (R + fabs(gy) + 1.0);
@@ -357,120 +435,131 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
         const int cx1 = min(__double2int_rd((gx + R + padx - A.box.lo[0]) * A.cells.inv_cwx), ux1) - ux0;
         const int ry0 = max(__double2int_rd((gy - R - pady - A.box.lo[1]) * A.cells.inv_cwy), uy0) - uy0;
         const int ry1 = min(__double2int_rd((gy + R + pady - A.box.lo[1]) * A.cells.inv_cwy), uy1) - uy0;
-        auto scan_rows = [&](auto SEAM) {
-            int r = ry0 - 1, l = 0, lend = 0, lsplit = 0;
-            double cpy = gy, cpxA = gx, cpxB = gx;
-            for (;;) {
-                if (l >= lend) {                               // next window row (empty rows cost one turn)
-                    if (++r > ry1) break;
-                    l = s_lcs[r * IKQ_LCS + cx0];
-                    lend = s_lcs[r * IKQ_LCS + cx1 + 1];
-                    lsplit = lend;
-                    if (SEAM.value) {                          // x + k (bmax - bmin), Search.h:186-189
-                        const double2 shA = S.shift[2 * r], shB = S.shift[2 * r + 1];
-                        cpy = gy + shA.y; cpxA = gx + shA.x; cpxB = gx + shB.x;
-                        lsplit = S.lp_base[2 * r + 1];
-                    }
-                    continue;
-                }
-                const double2 p = s_pos[l];
-                const double pax = p.x - ((SEAM.value && l >= lsplit) ? cpxB : cpxA);
-                const double pay = p.y - cpy;
-                const double d2 = pax * pax + pay * pay;
-                if (!(d2 > R2)) {
-                    if (nh < caps.hit_cap) ikq_sts_u16(hl_addr + 2u * (unsigned)nh, (unsigned)l);
-                    ++nh;
-                }
-                ++l;
+        const float g32x = (float)(gx - xmin), g32y = (float)(gy - ymin);
+        const float r2lo32 = caps.r2lo32, r2hi32 = caps.r2hi32;
+        const unsigned p32_addr = ikq_smem(s_p32);
+        const int hit_max = caps.buf_cap - IKQ_STEP_ROOM - 2;
+        int r = ry0 - 1, l = 0, lend = 0;
+        unsigned hp = buf_top;
+        const unsigned hp_min = buf_top - 2u * (unsigned)(hit_max + 1);   // reaching it means the disc does not fit
+        unsigned nu = 0u;
+        for (;;) {
+            if (l >= lend) {                               // next window row (empty rows cost one turn)
+                if (++r > ry1) break;
+                l = s_lcs[r * LCS + cx0];
+                lend = s_lcs[r * LCS + cx1 + 1];
+                continue;
             }
-        };
-        if (seam) scan_rows(std::true_type{}); else scan_rows(std::false_type{});
-        if (nh > caps.hit_cap) { slow = true; nh = 0; }
-    }
-    if (seam) {
-        // positions of the tile's periodic image: r - kL (used for the quadrature and the guarded arithmetic test only,
-        // never for an exact membership test)
-        __syncthreads();
-        for (int run = warp; run < nruns; run += (T >> 5)) {
-            const int np = S.np[run], lpb = S.lp_base[run];
-            const double2 sh = S.shift[run];
-            for (int o = lane; o < np; o += 32) {
-                const double2 p = s_pos[lpb + o];
-                s_pos[lpb + o] = make_double2(p.x - sh.x, p.y - sh.y);
-            }
+            const float2 p = ikq_lds_f32x2(p32_addr + 8u * (unsigned)l);
+            const float dx = p.x - g32x, dy = p.y - g32y;
+            const float d2 = fmaf(dx, dx, dy * dy);
+            // straight-line: the slot below the list's end is written always, the end moves for candidates only; one
+            // inside the guard band is marked (bit 15) and decided after the loop
+            const unsigned mark = d2 > r2lo32 ? 0x8000u : 0u;
+            ikq_sts_u16<-2>(hp, (unsigned)l | mark);
+            if (d2 <= r2hi32) { hp = max(hp - 2u, hp_min); nu |= mark; }
+            ++l;
         }
-        __syncthreads();
+        if (nu) {                                          // rare: exact tests, the list is compacted in place
+            unsigned rp = buf_top, wq = buf_top;
+            while (rp > hp) {
+                rp -= 2u;
+                const unsigned e = ikq_lds_u16(rp);
+                if (!(e & 0x8000u) || ikq_exact_hit(A, S, (int)(e & 0x7FFFu), gx, gy, nruns)) { wq -= 2u; ikq_sts_u16<0>(wq, e & 0x7FFFu); }
+            }
+            hp = wq;
+        }
+        nh = (int)((buf_top - hp) >> 1);
+        if (nh > hit_max) { slow = true; nh = 0; }
     }
     if (!warp_live) return;
 
     // ================= phases 2 and 3, alternating; warp-uniform control only =================
-    // explicit 32-bit shared addresses in the hot loops: one register per table, immediate offsets for the four slots
+    // explicit 32-bit shared addresses in the hot loops: one register per table, immediate offsets for the slots
     const unsigned b_addr = ikq_smem(s_b), cf_addr = ikq_smem(s_cf), pos_addr = ikq_smem(s_pos), rng_addr = ikq_smem(s_rng);
-    const unsigned own_addr = ikq_smem(s_own), pm_addr = ikq_smem(s_pm);
-    const unsigned list_addr = ikq_smem(s_list + tid * caps.list_stride);
-    const unsigned list_full = list_addr + 2u * (unsigned)(caps.list_cap - 4);   // no room for another step beyond this
-    const double r2lo = caps.r2lo, r2hi = caps.r2hi;
-    int pi = 0;                                            // next hit to walk
-    int k = 0, kend = 0, lcur = 0;
-    unsigned pm = 0u;
+    const unsigned own_addr = ikq_smem(s_own), buf_base = ikq_smem(s_buf);
+    const double r2lo = caps.r2lo, r2hi = caps.r2hi, t1lo = caps.t1lo, t1hi = caps.t1hi;
+    unsigned hp = buf_top - 2u * (unsigned)nh;             // next disc particle to walk (the last one found comes first)
+    int ks = 0, ns_rem = 0, kp = 0, np_rem = 0, lcur = 0;
     double ax = 0.0, ay = 0.0;
     const double iR2x2 = 2.0 * iR2;
     const int sub = lane & 3;
 
     for (;;) {
-        // ---- phase 2: walk.  One step = (if my particle is used up) the next particle of my disc, then four of its
-        //      half-bonds, straight-line: the four record slots are loaded and classified unconditionally (a slot past
-        //      the particle's last record reads a neighbouring record and is dropped), so they overlap in the pipeline.
-        //      A vote per step: stop when some list is nearly full or every lane has finished
-        unsigned wp = list_addr;                               // my list's write pointer
+        // ---- phase 2: walk.  One step = (if my particle is used up) the next particle i of my disc, then up to four of
+        //      its primary records -- always items: the bond is integrated once, from this end -- and up to two of its
+        //      secondary records, items only when the bond's primary end lies outside the disc (|a + b|^2 against R^2
+        //      with a guard band).  Straight-line: slots are written unconditionally and the write pointer moves past
+        //      the kept ones.  A vote per step: stop when some buffer is nearly full or every lane has finished
+        unsigned wp = buf_addr;                                // my list's write pointer
+        unsigned nu2 = 0u;
         int state;
         do {
-            if (k >= kend && pi < nh) {
-                lcur = (int)ikq_lds_u16(hl_addr + 2u * (unsigned)pi);
-                ++pi;
+            if (ns_rem <= 0 && np_rem <= 0 && hp < buf_top) {
+                lcur = (int)ikq_lds_u16(hp);
+                hp += 2u;
                 const unsigned rng = ikq_lds_u32(rng_addr + 4u * (unsigned)lcur);
-                pm = ikq_lds_u16(pm_addr + 2u * (unsigned)lcur);
                 const double2 p = ikq_lds_f64x2<0>(pos_addr + 16u * (unsigned)lcur);
-                k = (int)(rng & 0xFFFFu);
-                kend = (int)(rng >> 16);
+                ks = (int)(rng & 0x1FFFu);
+                ns_rem = (int)((rng >> 13) & 15u);
+                np_rem = (int)(rng >> 17);
+                kp = ks + ns_rem;
                 ax = p.x - gx;
                 ay = p.y - gy;
             }
-            const int krem = min(max(kend - k, 0), 4);         // record slots of this step that hold a record
-            const unsigned act = (1u << krem) - 1u;
-            const unsigned ba = b_addr + 16u * (unsigned)(krem > 0 ? k : 0);
-            const double2 b0 = ikq_lds_f64x2<0>(ba), b1 = ikq_lds_f64x2<16>(ba), b2 = ikq_lds_f64x2<32>(ba), b3 = ikq_lds_f64x2<48>(ba);
-            unsigned inm = 0u, unsure = 0u;                    // bit u: far end of slot u inside the disc / beyond the inner guard
+            // primary records
+            ikq_sts_u16<0>(wp, (unsigned)kp);
+            ikq_sts_u16<2>(wp, (unsigned)(kp + 1));
+            ikq_sts_u16<4>(wp, (unsigned)(kp + 2));
+            ikq_sts_u16<6>(wp, (unsigned)(kp + 3));
+            wp += 2u * (unsigned)min(max(np_rem, 0), 4);
+            kp += 4;
+            np_rem -= 4;
+            // secondary records
             {
+                const int nsl = min(max(ns_rem, 0), 2);
+                const unsigned act = (1u << nsl) - 1u;
+                const unsigned ba = b_addr + 16u * (unsigned)(nsl > 0 ? ks : 0);
+                const double2 b0 = ikq_lds_f64x2<0>(ba), b1 = ikq_lds_f64x2<16>(ba);
                 const double x0 = ax + b0.x, y0 = ay + b0.y, x1 = ax + b1.x, y1 = ay + b1.y;
-                const double x2 = ax + b2.x, y2 = ay + b2.y, x3 = ax + b3.x, y3 = ay + b3.y;
-                const double d0 = fma(x0, x0, y0 * y0), d1 = fma(x1, x1, y1 * y1), d2 = fma(x2, x2, y2 * y2), d3 = fma(x3, x3, y3 * y3);
-                inm = (d0 <= r2hi ? 1u : 0u) | (d1 <= r2hi ? 2u : 0u) | (d2 <= r2hi ? 4u : 0u) | (d3 <= r2hi ? 8u : 0u);
-                unsure = (d0 > r2lo ? 1u : 0u) | (d1 > r2lo ? 2u : 0u) | (d2 > r2lo ? 4u : 0u) | (d3 > r2lo ? 8u : 0u);
+                const double d0 = fma(x0, x0, y0 * y0), d1 = fma(x1, x1, y1 * y1);
+                // kept when the primary end lies outside the disc; inside the guard band: kept for now and marked
+                // (bit 14), decided by the exact test after the loop
+                const unsigned keep = ((d0 > r2lo ? 1u : 0u) | (d1 > r2lo ? 2u : 0u)) & act;
+                const unsigned m0 = d0 <= r2hi ? IKQ_UNSURE : 0u, m1 = d1 <= r2hi ? IKQ_UNSURE : 0u;
+                ikq_sts_u16<0>(wp, (unsigned)ks | IKQ_SEC | m0);
+                wp += (keep & 1u) << 1;
+                ikq_sts_u16<0>(wp, (unsigned)(ks + 1) | IKQ_SEC | m1);
+                wp += keep & 2u;
+                nu2 |= ((keep & 1u) ? m0 : 0u) | ((keep & 2u) ? m1 : 0u);
+                ks += 2;
+                ns_rem -= 2;
             }
-            unsure &= inm & act;
-            if (unsure) inm = ikq_exact_far_ends(A, S, lcur, k, unsure, inm, gx, gy, nruns);   // rounding could matter
-            // primary end: always; other end: only when the primary end is outside the disc
-            const unsigned keep = act & (pm | ~inm);
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {                      // entry: record k + u, bit 15 = both ends inside
-                ikq_sts_u16(wp, (unsigned)(k + u) | (((inm >> u) & 1u) << 15));
-                wp += ((keep >> u) & 1u) << 1;                 // the slot is overwritten unless kept
-            }
-            k += 4;
-            pm >>= 4;
-            const bool idle = k >= kend && pi >= nh;
-            state = (wp > list_full) ? 2 : (idle ? 0 : 1);
+            const bool idle = ns_rem <= 0 && np_rem <= 0 && hp >= buf_top;
+            state = (wp + 2u * IKQ_STEP_ROOM > hp) ? 2 : (idle ? 0 : 1);       // the next step's slots would reach my disc particles
             state = __reduce_max_sync(FULL_MASK, state);
         } while (state == 1);
-        const int n = (int)((wp - list_addr) >> 1);
+        if (nu2) {                                             // rare: exact far-end tests, the list is compacted in place
+            unsigned wq = buf_addr;
+            for (unsigned rp = buf_addr; rp < wp; rp += 2u) {
+                const unsigned e = ikq_lds_u16(rp);
+                bool keep = true;
+                if (e & IKQ_UNSURE) {
+                    const int k = (int)(e & (unsigned)IKQ_MAX_NREC);
+                    keep = !(ikq_exact_far_ends(A, S, (int)s_own[k], k, 1u, 0u, gx, gy, nruns) & 1u);
+                }
+                if (keep) { ikq_sts_u16<0>(wq, e & ~IKQ_UNSURE); wq += 2u; }
+            }
+            wp = wq;
+        }
+        const int n = (int)((wp - buf_addr) >> 1);
         __syncwarp();
 
         // ---- phase 3: four lanes <-> grid point; eight points per pass, longest lists first so that the eight points
         //      of a pass have lists of similar length (the pass runs to the longest of them)
         int rank = 0;                                          // my list's rank by length (ties: by lane), 0 = longest
 #pragma unroll
-        for (int bit = 5; bit >= 0; --bit) {
+        for (int bit = 7; bit >= 0; --bit) {                  // list lengths are below 256 (ikq_pick_caps)
             // radix ranking from the top bit down: lanes with a larger (n, 31 - lane) key come first
             const unsigned ones = __ballot_sync(FULL_MASK, (n >> bit) & 1);
             const unsigned same = __match_any_sync(FULL_MASK, n >> (bit + 1));   // lanes that agree on the higher bits
@@ -486,23 +575,56 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
             const int n_p = __shfl_sync(FULL_MASK, n, pt);
             if (!__any_sync(FULL_MASK, n_p > 0)) break;        // the remaining lists are shorter still
             const double gxp = __shfl_sync(FULL_MASK, gx, pt), gyp = __shfl_sync(FULL_MASK, gy, pt);
-            const unsigned short* const lp = s_list + ((warp << 5) + pt) * caps.list_stride;
+            const unsigned lp_addr = buf_base + (unsigned)(((warp << 5) + pt) * caps.buf_stride) * 2u;
             double axx = 0.0, axy = 0.0, ayy = 0.0;
-            for (int s = sub; s < n_p; s += 4) {
-                const unsigned it = lp[s];
-                const unsigned kk = it & 0x7FFFu;
-                const double wgt = (it & IKQ_BOTH) ? 1.0 : 0.5;
-                const double2 p = s_pos[s_own[kk]];
-                const double2 b = s_b[kk], cf = s_cf[kk];
-                const double pax = p.x - gxp, pay = p.y - gyp;
-                const double c0 = fma(pax, pax, pay * pay) * iR2;
-                const double c1 = fma(pax, b.x, pay * b.y) * iR2x2;
-                const double wf = ik_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * (cf.y * wgt);
-                const double tx = wf * b.x, ty = wf * b.y;
-                axx = fma(tx, b.x, axx);
-                axy = fma(tx, b.y, axy);
-                ayy = fma(ty, b.y, ayy);
+            unsigned unsure_any = 0u;
+            if (sub < n_p) {
+                // software pipeline: the next item's entry -> owner -> (position, b, (c2, f)) loads are issued before the
+                // current item's quadrature, so the three dependent shared-memory round trips hide behind ~45 FP64 operations
+                const unsigned a_last = lp_addr + 2u * (unsigned)(((n_p - 1 - sub) & ~3) + sub);   // my last entry
+                unsigned a_it = lp_addr + 2u * (unsigned)sub;
+                unsigned it0, it1;
+                double2 p0, b0, cf0, p1, b1, cf1;
+                auto fetch = [&](unsigned& it, double2& p, double2& b, double2& cf) {
+                    it = ikq_lds_u16(a_it);
+                    const unsigned kk = it & (unsigned)IKQ_MAX_NREC;
+                    p = ikq_lds_f64x2<0>(pos_addr + 16u * ikq_lds_u16(own_addr + 2u * kk));
+                    b = ikq_lds_f64x2<0>(b_addr + 16u * kk);
+                    cf = ikq_lds_f64x2<0>(cf_addr + 16u * kk);
+                };
+                auto item = [&](unsigned it, const double2& p, const double2& b, const double2& cf) {
+                    const double pax = p.x - gxp, pay = p.y - gyp;
+                    const double c0 = fma(pax, pax, pay * pay) * iR2;
+                    const double c1 = fma(pax, b.x, pay * b.y) * iR2x2;
+                    // weight: a bond whose two ends lie in the disc is visited twice by the reference, 1/2 each time; the
+                    // far end is inside when t(1) = |a + b|^2 / R^2 <= 1 (inside the guard band the pass is redone with
+                    // the exact test)
+                    const double t1 = (c0 + cf.x) + c1;
+                    const bool half = (it & IKQ_SEC) != 0u || t1 > t1hi;
+                    unsure_any |= (!half && t1 > t1lo) ? 1u : 0u;
+                    const double wf = ik_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * cf.y;
+                    const double wh = __hiloint2double(half ? 0x3FE00000 : 0x3FF00000, 0);
+                    const double tx = (wf * wh) * b.x, ty = (wf * wh) * b.y;
+                    axx = fma(tx, b.x, axx);
+                    axy = fma(tx, b.y, axy);
+                    ayy = fma(ty, b.y, ayy);
+                };
+                fetch(it0, p0, b0, cf0);
+                for (;;) {                                         // two register sets, alternating: no copies
+                    bool last = a_it >= a_last;
+                    a_it = min(a_it + 8u, a_last);
+                    fetch(it1, p1, b1, cf1);
+                    item(it0, p0, b0, cf0);
+                    if (last) break;
+                    last = a_it >= a_last;
+                    a_it = min(a_it + 8u, a_last);
+                    fetch(it0, p0, b0, cf0);
+                    item(it1, p1, b1, cf1);
+                    if (last) break;
+                }
             }
+            if (__any_sync(FULL_MASK, unsure_any != 0u))                // rounding could matter for some far end: exact weights
+                ikq_pass_exact<KERNEL, Q>(A, S, caps, lp_addr, n_p, sub, gxp, gyp, nruns, axx, axy, ayy);
             // quad reduction (same bits in all four lanes), then the sum goes to the point's own thread
             axx += __shfl_xor_sync(FULL_MASK, axx, 1); axy += __shfl_xor_sync(FULL_MASK, axy, 1); ayy += __shfl_xor_sync(FULL_MASK, ayy, 1);
             axx += __shfl_xor_sync(FULL_MASK, axx, 2); axy += __shfl_xor_sync(FULL_MASK, axy, 2); ayy += __shfl_xor_sync(FULL_MASK, ayy, 2);
@@ -513,7 +635,6 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
         __syncwarp();
         if (state == 0) break;
     }
-    (void)own_addr; (void)cf_addr;
 
     if (store) {
         if (slow) ik_slow_path<KERNEL, Q>(A, gx, gy, txx, txy, tyy);
@@ -555,6 +676,14 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
     static const int shapes[][2] = { { 2, 4 }, { 4, 2 }, { 2, 2 }, { 1, 2 }, { 1, 1 } };
     const int reg_threads = 65536 / 128;                       // __launch_bounds__(256, 2): at most 128 registers per thread
     long long best_score = -1;
+    double best_mt = 0.0;
+    // a thread's buffer holds the particles of its disc (mean rho pi R^2; 1.6 x that + 8, a fuller disc takes the slow
+    // path) and, growing towards them, the bonds to integrate (about 2/3 of the disc's half-bonds): room for a whole
+    // list saves a second walk / integrate round
+    const double nd = rho * M_PI * R * R;
+    const int buf_min = (((int)(1.6 * nd) + 8 + IKQ_STEP_ROOM + 2) + 1) & ~1;
+    if (buf_min > 250) return false;                           // phase 3 ranks the lists by an 8-bit length
+    const int buf_want = std::max(buf_min, std::min(64, (((int)(0.66 * 1.25 * nd * hb) + IKQ_STEP_ROOM + 4) + 1) & ~1));
     for (const auto& sh : shapes) {
         const int wx = sh[0], wy = sh[1];
         if (want_wx > 0 && (wx != want_wx || wy != want_wy)) continue;
@@ -562,36 +691,33 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
         const double sx = a.grid.span_x[wx - 1], sy = a.grid.span_y[wy - 1];
         if (sx < 0.0 || sy < 0.0) continue;
         const int rows_cap = (int)((sy + 2.0 * R) / cwy) + 3, cols = (int)((sx + 2.0 * R) / cwx) + 3;
-        if (rows_cap > IKQ_MAXROWS || cols > IKQ_MAXCOLS) continue;
+        if (rows_cap > IKQ_MAXROWS || cols > 254) continue;
+        const int lcs_stride = cols + 1;
         const double ep = rho * (sx + 2.0 * R + 2.0 * cwx) * (sy + 2.0 * R + 2.0 * cwy);
         const long long nloc = ((long long)(ep * m + 32.0) + 7) & ~7LL;
         const long long nrec = ((long long)(ep * hb * m + 64.0) + 7) & ~7LL;
-        if (nloc > 0xFFFF || nrec > IKQ_MAX_NREC) continue;
-        // particles of one disc: mean rho pi R^2; the list holds 1.6 x that + 8 (a fuller disc takes the slow path)
-        const int hit_cap = std::min(255, ((int)(1.6 * rho * M_PI * R * R) + 8) & ~1);
-        const int hit_stride = ((hit_cap / 2) | 1) * 2;
-        // records 32 B + owner 2 B; position 16 B, range 4 B, primary mask 2 B per particle; hit list per thread;
-        // local cell starts
-        const long long base = nrec * 34 + nloc * 22 + (long long)hit_stride * 2 * T + (long long)rows_cap * IKQ_LCS * 2 + 64;
-        const long long stat = (long long)sizeof(IKQStatic) + 16 + 1024;   // static part + the per-CTA reservation
+        if (nloc > 0x7FFF || nrec > IKQ_MAX_NREC) continue;
+        // records 32 B + owner 2 B; position 16 B + 8 B (single precision), range 4 B per particle; local cell starts
+        const long long base = nrec * 34 + nloc * 28 + (long long)rows_cap * lcs_stride * 2 + 64;
+        const long long stat = (long long)sizeof(IKQStatic) + 16 + IKQ_MAX_THREADS + 1024;   // static part + the per-CTA reservation
         const int max_ctas = std::max(1, std::min(reg_threads / T, 16));
         for (int ctas = (want_ctas > 0 ? std::min(want_ctas, max_ctas) : max_ctas); ctas >= 1; --ctas) {
             const long long avail = std::min<long long>(smem_sm / ctas, smem_cta) - stat - base;
             long long lc = avail / (2LL * T) - 2;              // the stride is rounded up to 2 x odd
-            if (lc < 12) continue;
-            lc = std::min<long long>(lc, want_list > 0 ? std::min(want_list, 62) : 40) & ~1LL;
+            if (lc < buf_min) continue;
+            lc = std::min<long long>(std::min<long long>(lc, want_list > 0 ? std::max(want_list, buf_min) : buf_want), 254) & ~1LL;
             const long long score = (long long)ctas * T * 1000 + T;   // threads per SM first, then the larger tile
             if (score > best_score) {
                 best_score = score;
+                best_mt = std::max(sx, sy) + R + 2.0 * std::max(cwx, cwy);
                 caps->wx = wx; caps->wy = wy;
                 caps->rows_cap = rows_cap;
+                caps->lcs_stride = lcs_stride;
                 caps->nloc_cap = (int)nloc;
                 caps->nrec_cap = (int)nrec;
-                caps->list_cap = (int)lc;
-                caps->list_stride = (int)(((lc / 2) | 1) * 2);             // lc is even: the next 2 x odd, lc or lc + 2
-                caps->hit_cap = hit_cap;
-                caps->hit_stride = hit_stride;
-                *dyn_bytes = (size_t)(base + (long long)caps->list_stride * 2 * T + 15) & ~(size_t)15;
+                caps->buf_cap = (int)lc;
+                caps->buf_stride = (int)(((lc / 2) | 1) * 2);              // lc is even: the next 2 x odd, lc or lc + 2
+                *dyn_bytes = (size_t)(base + (long long)caps->buf_stride * 2 * T + 15) & ~(size_t)15;
             }
             break;
         }
@@ -602,6 +728,14 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
     const double band = std::max(1e-9 * a.cg.rcutsq, 1e-11 * R * M);
     caps->r2lo = a.cg.rcutsq - band;
     caps->r2hi = a.cg.rcutsq + band;
+    caps->t1lo = 1.0 - band * a.inv_rcutsq;
+    caps->t1hi = 1.0 + band * a.inv_rcutsq;
+    // guard band of phase 1's single-precision test: coordinates relative to the tile's corner are at most Mt in
+    // magnitude, each rounded to 2^-24 relative; d^2 = dx^2 + dy^2 near R^2 then carries at most
+    // 2^-24 (2.83 R (2 Mt + R + 1) + 3 R^2); twice that on either side
+    const double e32 = std::ldexp(1.0, -23) * (2.83 * R * (2.0 * best_mt + R + 1.0) + 3.0 * R * R);
+    caps->r2lo32 = std::nextafter((float)(a.cg.rcutsq - e32), -1.0f);
+    caps->r2hi32 = std::nextafter((float)(a.cg.rcutsq + e32), 1e30f);
     return true;
 }
 

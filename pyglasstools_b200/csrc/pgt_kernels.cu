@@ -417,7 +417,12 @@ __device__ __forceinline__ int split_segments(int u0, int u1, int nc, Seg seg[3]
     return n;
 }
 
-// visit(q, dx, dy, accum, code): code = (kx + 1) | (ky + 1) << 2 names the periodic image the hit was found under
+// visit(q, dx, dy, accum, code): code = (kx + 1) | (ky + 1) << 2 names the periodic image the hit was found under;
+// bit 4 of code: q comes AFTER p in the visiting order (rows, then cells of a row in unwrapped coordinates, then sorted
+// index).  The order is the same whichever end of a pair looks, mirrored, so "after" names exactly one end of every
+// (pair, image): the bond's PRIMARY end is the one that sees the other after itself.  Away from the periodic seam this
+// is p < q; at the seam it still splits a particle's neighbours into a leading run of secondary records and a trailing
+// run of primary ones, which is what the quad gather relies on.
 template <class F>
 __device__ __forceinline__ void for_each_neighbor_img(const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, int p,
                                                       double xi, double yi, double rc2, F&& visit)
@@ -426,6 +431,8 @@ __device__ __forceinline__ void for_each_neighbor_img(const PgtFrameView& fr, co
     const int cy = cell_coord(yi, box.lo[1], cells.inv_cwy, cells.ncy);
     Seg seg[3];
     const int nseg = split_segments(cx - cells.reach, cx + cells.reach, cells.ncx, seg);
+    int s_home = 0;                                 // the segment that holds p's own cell (the one without an image shift)
+    for (int s = 1; s < nseg; ++s) if (seg[s].k == 0) s_home = s;
     for (int uy = cy - cells.reach; uy <= cy + cells.reach; ++uy) {
         int ky = 0, row = uy;
         if (uy < 0) { ky = +1; row = uy + cells.ncy; }
@@ -436,12 +443,14 @@ __device__ __forceinline__ void for_each_neighbor_img(const PgtFrameView& fr, co
             const double cpx = xi + seg[s].k * box.L[0];
             const int qb = __ldg(fr.cell_start + rbase + seg[s].c0);
             const int qe = __ldg(fr.cell_start + rbase + seg[s].c1 + 1);
+            const int dir = uy != cy ? (uy > cy ? 1 : -1) : (s != s_home ? (s > s_home ? 1 : -1) : 0);
+            const unsigned code = (unsigned)(seg[s].k + 1) | ((unsigned)(ky + 1) << 2);
             for (int q = qb; q < qe; ++q) {
                 const double dx = __ldg(fr.sx + q) - cpx;
                 const double dy = __ldg(fr.sy + q) - cpy;
                 const double accum = dx * dx + dy * dy;
                 // the particle itself is skipped (IrvingKirkwood.h:97, ThermoCalculator.h:81), tested on hits only
-                if (!(accum > rc2) && q != p) visit(q, dx, dy, accum, (unsigned)(seg[s].k + 1) | ((unsigned)(ky + 1) << 2));
+                if (!(accum > rc2) && q != p) visit(q, dx, dy, accum, code | ((dir > 0 || (dir == 0 && q > p)) ? 16u : 0u));
             }
         }
     }
@@ -500,13 +509,13 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
     if (p >= fr.n) return;
     const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
     int n = 0;
-    unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (p < q)
+    unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (q visited after p)
     for_each_neighbor_img(fr, box, cells, p, xi, yi, rc2, [&](int q, double, double, double rsq, unsigned code) {
         const double dj = __ldg(fr.sd + q);
         if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
         if (n < PGT_NB_SLOTS) {
-            nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
-            if (p < q) pm |= 1u << n;
+            nb_list[(size_t)n * fr.n + p] = (unsigned)q | ((code & 15u) << 28);
+            if (code & 16u) pm |= 1u << n;
         }
         ++n;
     });
