@@ -43,7 +43,7 @@
 #define IKQ_STEP_ROOM 6                   // list slots one walk step may touch (4 primary + 2 secondary)
 
 struct IKQCaps {
-    int wx, wy;                          // warps per tile along i (x) and j (y)
+    int wx, wy, wy_log2;                 // warps per tile along i (x) and j (y; a power of two)
     int rows_cap;                        // cell rows of the rectangle
     int lcs_stride;                      // entries per row of the local cell-start table (columns of the rectangle + 1)
     int nloc_cap;                        // particles of the rectangle
@@ -252,10 +252,9 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
 
     // ---- tile and my grid point: a warp covers a compact 8 x 4 patch
     const int TI = IKQ_PX * caps.wx, TJ = IKQ_PY * caps.wy;
-    const int tiles_j = (A.grid.ny + TJ - 1) / TJ;
-    const int i0 = (tile_i_begin + blockIdx.x / tiles_j) * TI, j0 = (blockIdx.x % tiles_j) * TJ;
+    const int i0 = (tile_i_begin + (int)blockIdx.y) * TI, j0 = (int)blockIdx.x * TJ;
     const int i1 = min(i0 + TI, A.grid.nx) - 1, j1 = min(j0 + TJ, A.grid.ny) - 1;
-    const int gi = i0 + IKQ_PX * (warp / caps.wy) + (lane >> 2), gj = j0 + IKQ_PY * (warp % caps.wy) + (lane & 3);
+    const int gi = i0 + IKQ_PX * (warp >> caps.wy_log2) + (lane >> 2), gj = j0 + IKQ_PY * (warp & (caps.wy - 1)) + (lane & 3);   // wy is 1, 2 or 4
     // every in-grid point of a warp that stores anything is computed, whatever the shard: a point's summation order
     // (and so its bits) must not depend on how the grid is split over GPUs
     const bool ingrid = gi <= i1 && gj <= j1;
@@ -362,18 +361,19 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
             }
         }
         // ---- meanwhile: the index tables.  Local cell starts
-        for (int e = tid; e < nrows * (ncols + 1); e += T) {
-            const int r = e / (ncols + 1), c = e - r * (ncols + 1);
-            int v;
-            if (c == ncols) v = S.lp_base[2 * r + 2];
-            else {
-                int uy = uy0 + r;
-                if (uy < 0) uy += ncy; else if (uy >= ncy) uy -= ncy;
-                const int s = c >= csplit;
-                const int cell = uy * ncx + (s ? seg[1].c0 + (c - csplit) : seg[0].c0 + c);
-                v = S.lp_base[2 * r + s] + (__ldg(fr.cell_start + cell) - S.ps[2 * r + s]);
+        for (int r = warp; r < nrows; r += (T >> 5)) {
+            int uy = uy0 + r;
+            if (uy < 0) uy += ncy; else if (uy >= ncy) uy -= ncy;
+            for (int c = lane; c <= ncols; c += 32) {
+                int v;
+                if (c == ncols) v = S.lp_base[2 * r + 2];
+                else {
+                    const int s = c >= csplit;
+                    const int cell = uy * ncx + (s ? seg[1].c0 + (c - csplit) : seg[0].c0 + c);
+                    v = S.lp_base[2 * r + s] + (__ldg(fr.cell_start + cell) - S.ps[2 * r + s]);
+                }
+                s_lcs[r * LCS + c] = (unsigned short)v;
             }
-            s_lcs[r * LCS + c] = (unsigned short)v;
         }
         // a warp takes a run: each particle's record range (secondary records first, then primary ones), each record's owner
         const int nwarps = T >> 5;
@@ -673,7 +673,7 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
     const double rho = (double)a.fr.n / (a.box.L[0] * a.box.L[1]);
     const double hb = a.fr.n_hb > 0 ? (double)a.fr.n_hb / (double)a.fr.n : 1.0;
     const double m = 1.0 + 0.01 * margin_pct;
-    static const int shapes[][2] = { { 2, 4 }, { 4, 2 }, { 2, 2 }, { 1, 2 }, { 1, 1 } };
+    static const int shapes[][2] = { { 4, 2 }, { 2, 4 }, { 2, 2 }, { 1, 2 }, { 1, 1 } };   // equal threads: the first listed wins (fewer, longer cell rows)
     const int reg_threads = 65536 / 128;                       // __launch_bounds__(256, 2): at most 128 registers per thread
     long long best_score = -1;
     double best_mt = 0.0;
@@ -683,7 +683,7 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
     const double nd = rho * M_PI * R * R;
     const int buf_min = (((int)(1.6 * nd) + 8 + IKQ_STEP_ROOM + 2) + 1) & ~1;
     if (buf_min > 250) return false;                           // phase 3 ranks the lists by an 8-bit length
-    const int buf_want = std::max(buf_min, std::min(64, (((int)(0.66 * 1.25 * nd * hb) + IKQ_STEP_ROOM + 4) + 1) & ~1));
+    const int buf_want = std::max(buf_min, std::min(64, (((int)(0.66 * 1.5 * nd * hb) + IKQ_STEP_ROOM + 4) + 1) & ~1));
     for (const auto& sh : shapes) {
         const int wx = sh[0], wy = sh[1];
         if (want_wx > 0 && (wx != want_wx || wy != want_wy)) continue;
@@ -706,11 +706,11 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
             long long lc = avail / (2LL * T) - 2;              // the stride is rounded up to 2 x odd
             if (lc < buf_min) continue;
             lc = std::min<long long>(std::min<long long>(lc, want_list > 0 ? std::max(want_list, buf_min) : buf_want), 254) & ~1LL;
-            const long long score = (long long)ctas * T * 1000 + T;   // threads per SM first, then the larger tile
+            const long long score = (long long)ctas * T;               // threads per SM; ties: the shape listed first
             if (score > best_score) {
                 best_score = score;
                 best_mt = std::max(sx, sy) + R + 2.0 * std::max(cwx, cwy);
-                caps->wx = wx; caps->wy = wy;
+                caps->wx = wx; caps->wy = wy; caps->wy_log2 = wy == 4 ? 2 : (wy == 2 ? 1 : 0);
                 caps->rows_cap = rows_cap;
                 caps->lcs_stride = lcs_stride;
                 caps->nloc_cap = (int)nloc;
@@ -757,8 +757,9 @@ static cudaError_t launch_ik_quad_t(const PgtIKArgs& a, const IKQCaps& caps, siz
     const int tiles_j = (a.grid.ny + TJ - 1) / TJ;
     const int i_lo = (int)(a.grid.g0 / a.grid.ny), i_hi = (int)((a.grid.g1 - 1) / a.grid.ny);
     const int tile_i_begin = i_lo / TI;
-    const long long blocks = (long long)(i_hi / TI - tile_i_begin + 1) * tiles_j;
-    k_ik_quad<KERNEL, Q><<<(unsigned)blocks, 32 * caps.wx * caps.wy, dyn, st>>>(a, tile_i_begin, caps);
+    const dim3 blocks((unsigned)tiles_j, (unsigned)(i_hi / TI - tile_i_begin + 1));
+    if (blocks.y > 65535u) return cudaErrorInvalidConfiguration;
+    k_ik_quad<KERNEL, Q><<<blocks, 32 * caps.wx * caps.wy, dyn, st>>>(a, tile_i_begin, caps);
     return cudaGetLastError();
 }
 
