@@ -10,6 +10,10 @@ owns different frames, every GPU holds its whole frame: weak scaling, no data-pa
 `--shard grid` instead splits the grid points of the same frame over the ranks (np.array_split
 boundaries, like the reference's MPI ranks) and all-gathers the field with NCCL.
 
+At N > 1 the same run also times ONE frame split over the ranks by grid points (`grid_shard` in the JSON line): parts
+of the frame pushed over PCIe and assembled with ncclAllGather, slab-local cell / bond lists, every rank reading back
+its own shard; the gathered field is compared bit for bit with the single-GPU field once, outside the timing.
+
 Printed JSON line (rank 0):
   value     grid-point*frames/s with the frames already resident in HBM (CUDA events on the ctx stream,
             max over ranks)
@@ -17,6 +21,8 @@ Printed JSON line (rank 0):
             stages, D2H of the FP64 stress field, every step
   roofline  the IK gather kernel against the FP64 FMA pipe (the path is not a dense contraction and the
             gather is not HBM-bound): achieved = sum_x U(x)*(15q+9) flops / launch time
+  roofline_stages  cell-list and bond stages against the measured HBM copy bandwidth (MEASURED_PEAKS.json)
+  other_configs    BASELINE configs 1-4 (shipped fixture, thermo trajectory, cfg3, cfg4), short runs in the same process
   cpu_baseline  the oracle (oracle/, the reference's algorithm restated) on the host cores, bounded sample
 """
 import argparse
@@ -160,16 +166,60 @@ def bind_to_gpu_numa_node(local_rank):
         return "unbound (%s)" % e
 
 
+def config_dict(args, wl, world, pool):
+    """The workload description both arms print (the driver compares them)."""
+    n, nmax, q = wl["n"], wl["nmax"], wl["cg"][2]
+    return {"workload": args.workload, "description": wl["desc"], "N": n * n, "grid": nmax * nmax, "potential": wl["pot"],
+            "cg": {"kernel": wl["cg"][0], "rcut": wl["cg"][1], "order": q}, "shard": args.shard,
+            "frames_per_step_per_gpu": 1 if args.shard == "frames" else 1.0 / world, "frame_pool": pool,
+            "l2": "inputs larger than L2: each step rebuilds and streams a ~%.0f MB half-bond list + %.0f MB sorted frame"
+                  % (n * n * 3.61 * 36 / 1e6, n * n * 28 / 1e6),
+            "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"}
+
+
+def oracle_rate(wl, fr, stride, min_seconds, warm):
+    """grid points / s of the oracle's IK loop (all host threads, timing build) on every stride-th grid row and column."""
+    os.environ["PGT_ORACLE_FAST"] = "1"                  # before the first oracle call: -O3 -march=native copy
+    from oracle import orc
+    from pyglasstools_b200 import synth
+    orc.set_num_threads(len(os.sched_getaffinity(0)))    # torchrun exports OMP_NUM_THREADS=1 for N > 1
+    name, rc, prm = pot_params(wl["pot"])
+    P = orc.potential(name)
+    cg = orc.cgfunc(*wl["cg"])
+    t0 = time.time()
+    S = orc.System(fr["box"], fr["position"], fr["diameter"])
+    build_s = time.time() - t0
+    L = float(fr["box"][0])
+    nmax = wl["nmax"]
+    axis = synth.linspace_axis(L, nmax)
+    ii = np.arange(0, nmax, stride)
+    grid = np.zeros((len(ii) ** 2, 3))
+    grid[:, 0] = np.repeat(axis[ii], len(ii))
+    grid[:, 1] = np.tile(axis[ii], len(ii))
+    mr = S.max_rcut(P)
+    for _ in range(warm):
+        S.ik(P, cg, grid[: max(4096, len(grid) // 8)], max_rcut=mr)
+    passes, t0 = 0, time.perf_counter()
+    while passes < 1 or (time.perf_counter() - t0 < min_seconds and passes < 64):
+        S.ik(P, cg, grid, max_rcut=mr)
+        passes += 1
+    dt = (time.perf_counter() - t0) / passes
+    return dict(rate=len(grid) / dt, dt=dt, passes=passes, points=len(grid), stride=stride, build_s=build_s,
+                cores=orc.num_threads(), lib=getattr(orc.lib(), "_pgt_build", "liborc.so"))
+
+
 def run_reference(args, wl, rank, world):
     """The reference's algorithm on the host cores: the oracle (the reference itself cannot be built
     here -- no Boost / GSL / MPI), all threads, a bounded sample of the grid per step."""
     if rank != 0:
         return
-    from oracle import orc
     from pyglasstools_b200 import synth
-    # torchrun exports OMP_NUM_THREADS=1 when it starts more than one rank; this arm is rank 0 alone on the whole host
-    orc.set_num_threads(len(os.sched_getaffinity(0)))
     fr = synth.synth_frame(wl["n"], synth.SEEDS[wl["seed"]])
+    stride = args.cpu_sample_stride or max(1, int(round(wl["nmax"] / 512.0)))
+    # K timed steps, each one pass over the bounded sample
+    os.environ["PGT_ORACLE_FAST"] = "1"
+    from oracle import orc
+    orc.set_num_threads(len(os.sched_getaffinity(0)))
     name, rc, prm = pot_params(wl["pot"])
     P = orc.potential(name)
     cg = orc.cgfunc(*wl["cg"])
@@ -178,7 +228,6 @@ def run_reference(args, wl, rank, world):
     build_s = time.time() - t0
     L = float(fr["box"][0])
     axis = synth.linspace_axis(L, wl["nmax"])
-    stride = max(1, int(round(wl["nmax"] / 512.0)))
     ii = np.arange(0, wl["nmax"], stride)
     grid = np.zeros((len(ii) ** 2, 3))
     grid[:, 0] = np.repeat(axis[ii], len(ii))
@@ -191,16 +240,138 @@ def run_reference(args, wl, rank, world):
         S.ik(P, cg, grid, max_rcut=mr)
     dt = (time.perf_counter() - t0) / args.steps
     value = len(grid) / dt
-    sample = "%d of %d grid points (every %d-th in i and j) of one frame per step; frame build %.2f s excluded" % (
-        len(grid), wl["nmax"] ** 2, stride, build_s)
+    sample = "%d of %d grid points (every %d-th in i and j) of one frame per step, rate extrapolated to the grid; frame build %.2f s excluded; %s (-O3 -march=native -fopenmp, the reference's flags)" % (
+        len(grid), wl["nmax"] ** 2, stride, build_s, getattr(orc.lib(), "_pgt_build", "liborc.so"))
+    cfg = config_dict(args, wl, 1 if args.shard == "frames" else world, max(1, args.pool))
     out = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": args.workload, "description": wl["desc"], "N": wl["n"] ** 2, "grid": wl["nmax"] ** 2},
+           "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+           "scaling": "weak" if args.shard == "frames" else "strong",
+           "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
            "cpu_baseline": {"value": value, "unit": UNIT, "cores": orc.num_threads(), "kind": "port", "sample": sample},
            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
     print(json.dumps(out), flush=True)
+
+
+def setup_ctx(_capi, synth, device, wl, dmax, L):
+    ctx = _capi.Context(device)
+    name, rc, prm = pot_params(wl["pot"])
+    ctx.set_potential(name, rc, prm)
+    ctx.set_cg(*wl["cg"])
+    ctx.set_max_rcut(max(rc * dmax, dmax))                   # Calculator.h:37-46, frozen
+    axis = synth.linspace_axis(L, wl["nmax"])
+    ctx.set_grid_cartesian(axis, axis)
+    return ctx
+
+
+def stage_bytes(N, ncells, n_hb):
+    """Algorithmic HBM bytes per frame of the two memory-bound stages:
+    cells  60 B / particle (16 raw float32 read + 4 key + 4 slot + 4 sorted id + 32 sorted x, y, (x,y), d written)
+           + 8 B / cell (count written, start read);
+    bonds  24 B / particle read (x, y, d) + 8 B / particle (offsets) + 36 B / half-bond record written."""
+    return {"cells": 60.0 * N + 8.0 * ncells, "bonds": 32.0 * N + 36.0 * n_hb}
+
+
+def quick_workload(_capi, synth, device, name, steps=12, warm=3):
+    """A short device-timed run of another BASELINE configuration (same stages, same timing rules): for `other_configs`."""
+    wl = WORKLOADS[name]
+    fr = synth.synth_frame(wl["n"], synth.SEEDS[wl["seed"]])
+    import torch
+    ctx = setup_ctx(_capi, synth, device, wl, float(fr["diameter"].max()), float(fr["box"][0]))
+    dpos, ddiam = torch.from_numpy(fr["position"]).cuda(), torch.from_numpy(fr["diameter"]).cuda()
+    N, G, q = wl["n"] ** 2, wl["nmax"] ** 2, wl["cg"][2]
+
+    def step():
+        ctx.set_device_frame(dpos.data_ptr(), ddiam.data_ptr(), N, fr["box"], is_f32=True)
+        ctx.build_cells()
+        ctx.build_bonds()
+        ctx.ik_compute(_capi.OBS_VIRIAL)
+    for _ in range(warm):
+        step()
+    w = ctx.ik_count_work()
+    ctx.sync()
+    ctx.event_record(0)
+    for _ in range(steps):
+        step()
+    ctx.event_record(1)
+    ctx.sync()
+    ms = ctx.event_elapsed_ms(0, 1) / steps
+    ik = ctx.stage_ms("ik")
+    flops = w["unique_bonds"] * (15 * q + 9)
+    out = {"description": wl["desc"], "value": G / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+           "stage_ms": {"cells": ctx.stage_ms("cells"), "bonds": ctx.stage_ms("bonds"), "ik": ik},
+           "ik_tflops": flops / (ik * 1e-3) / 1e12, "ik_frac_of_nominal_37.2": flops / (ik * 1e-3) / 1e12 / 37.2, "steps": steps}
+    ctx.close()
+    return out
+
+
+def fixture_workload(_capi, synth, device):
+    """BASELINE configs[0]: the shipped example (example_scripts/irvingkirkwood/test-irvingkirkwood-module.py:11-25 on
+    polydisperse12.gsd: poly12, octic R = 2 GL-5, dx = 0.25, frames 180..199), frames from the committed fixture, through the
+    C-ABI with host buffers (upload + stages + field read-back per frame)."""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "polydisperse12_frames.npz"))
+    diam, box = z["diameter"], z["box"]
+    L = float(box[0])
+    nmax = int(L / 0.25)                                      # ikcalculator: nmax = int(L / dx), linspace both ends
+    frames = []
+    for f in range(180, 200):
+        p = np.zeros((z["xy"].shape[1], 3), np.float32)
+        p[:, :2] = z["xy"][f]
+        frames.append(p)
+    ctx = _capi.Context(device)
+    name, rc, prm = pot_params("poly12")
+    ctx.set_potential(name, rc, prm)
+    ctx.set_cg("octic", 2.0, 5)
+    dmax = float(diam.max())
+    ctx.set_max_rcut(max(rc * dmax, dmax))
+    axis = synth.linspace_axis(L, nmax)
+    ctx.set_grid_cartesian(axis, axis)
+    out = np.empty((nmax * nmax, 4))
+
+    def run():
+        for p in frames:
+            ctx.upload(p, diam, box)
+            ctx.build_cells()
+            ctx.build_bonds()
+            ctx.ik_compute(_capi.OBS_VIRIAL)
+            ctx.ik_download(_capi.FIELD_VIRIAL, out)
+    run()
+    t0 = time.perf_counter()
+    reps = 5
+    for _ in range(reps):
+        run()
+    dt = (time.perf_counter() - t0) / (reps * len(frames))
+    ctx.close()
+    return {"description": "BASELINE configs[0]: shipped polydisperse12.gsd frames 180..199 (N = %d), script's own grid %d^2 (dx = 0.25), poly12, octic R=2 GL-5; through the C-ABI, host buffers, per frame"
+                           % (len(diam), nmax), "value": nmax * nmax / dt, "unit": UNIT, "ms_per_frame": dt * 1e3, "frames": len(frames)}
+
+
+def thermo_workload(_capi, synth, device, nframes=1000):
+    """BASELINE configs[1]: thermo global virial stress + potential energy, synthetic N = 65536, a 1000-frame trajectory
+    streamed from host memory through the C-ABI (upload + cell list + pair sums + 25-double read-back per frame)."""
+    pool = [synth.synth_frame(256, synth.SEEDS["cfg2"] + f) for f in range(8)]
+    ctx = _capi.Context(device)
+    name, rc, prm = pot_params("poly12")
+    ctx.set_potential(name, rc, prm)
+    dmax = max(float(fr["diameter"].max()) for fr in pool)
+    ctx.set_max_rcut(max(rc * dmax, dmax))
+    mask = _capi.OBS_VIRIAL | _capi.OBS_ENERGY
+    for f in range(16):
+        fr = pool[f % len(pool)]
+        ctx.upload(fr["position"], fr["diameter"], fr["box"])
+        ctx.build_cells()
+        ctx.thermo(mask)
+    t0 = time.perf_counter()
+    for f in range(nframes):
+        fr = pool[f % len(pool)]
+        ctx.upload(fr["position"], fr["diameter"], fr["box"])
+        ctx.build_cells()
+        ctx.thermo(mask)
+    dt = time.perf_counter() - t0
+    out = {"description": "BASELINE configs[1]: thermo virial + energy, synthetic N=65536, %d frames through the C-ABI (upload, cells, pair sums, read-back per frame)" % nframes,
+           "value": nframes / dt, "unit": "frames/s", "device_ms": {"cells": ctx.stage_ms("cells"), "thermo": ctx.stage_ms("thermo")}}
+    ctx.close()
+    return out
 
 
 def main():
@@ -210,13 +381,15 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
-    ap.add_argument("--e2e-field", default="full", choices=("full", "sym"),
-                    help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy)")
+    ap.add_argument("--e2e-field", default="auto", choices=("auto", "full", "sym"),
+                    help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy); auto: full on one GPU, sym on several (the host's PCIe / memory path is shared)")
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
-    ap.add_argument("--e2e-lanes", type=int, default=3, choices=(2, 3, 4), help="contexts (streams) the end-to-end trajectory loop is pipelined over")
+    ap.add_argument("--e2e-lanes", type=int, default=3, choices=(1, 2, 3, 4), help="contexts (streams) the end-to-end trajectory loop is pipelined over")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-other-configs", action="store_true")
+    ap.add_argument("--no-grid-shard", action="store_true", help="N > 1: skip the grid-sharded measurement of one frame")
     ap.add_argument("--cpu-sample-stride", type=int, default=0)
     args = ap.parse_args()
     wl = WORKLOADS[args.workload]
@@ -227,6 +400,10 @@ def main():
     if args.impl == "reference":
         run_reference(args, wl, rank, world)
         return
+    if args.shard == "grid" and world == 1:
+        args.shard = "frames"
+    if args.e2e_field == "auto":
+        args.e2e_field = "full" if world == 1 else "sym"
 
     import torch
     import torch.distributed as dist
@@ -259,10 +436,7 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
-    ctx = _capi.Context(local_rank)
     name, rc, prm = pot_params(wl["pot"])
-    ctx.set_potential(name, rc, prm)
-    ctx.set_cg(*wl["cg"])
     n, nmax = wl["n"], wl["nmax"]
     N, G = n * n, nmax * nmax
     q = wl["cg"][2]
@@ -272,16 +446,13 @@ def main():
     frames = make_frames(wl, rank if args.shard == "frames" else 0, pool)
     L = float(frames[0]["box"][0])
     dmax = max(float(f["diameter"].max()) for f in frames)
-    ctx.set_max_rcut(max(rc * dmax, dmax))                   # Calculator.h:37-46, frozen
-    axis = synth.linspace_axis(L, nmax)
-    ctx.set_grid_cartesian(axis, axis)
-    if args.shard == "grid" and world > 1:
-        shards = sharding.grid_shards(G, world)          # np.array_split boundaries = the reference's MPI ranks
-        sizes = [e - b for b, e in shards]
+    grid_mode = args.shard == "grid"
+    ctx = setup_ctx(_capi, synth, local_rank, wl, dmax, L)
+    shards = sharding.grid_shards(G, world)                  # np.array_split boundaries = the reference's MPI ranks
+    if grid_mode:
         ctx.set_shard(*shards[rank])
-        g_local = sizes[rank]
+        g_local = shards[rank][1] - shards[rank][0]
     else:
-        sizes = [G]
         g_local = G
     pin_pos = [_capi.PinnedArray((N, 3), np.float32) for _ in range(pool)]
     pin_diam = [_capi.PinnedArray((N,), np.float32) for _ in range(pool)]
@@ -292,33 +463,42 @@ def main():
         dev_pos.append(torch.from_numpy(f["position"]).cuda())
         dev_diam.append(torch.from_numpy(f["diameter"]).cuda())
     ncomp_out = 3 if args.e2e_field == "sym" else 4
-    pin_out = _capi.PinnedArray((g_local, ncomp_out), np.float64)
     box = frames[0]["box"]
     torch.cuda.synchronize()
 
-    def step_resident(k):
-        ctx.set_device_frame(dev_pos[k].data_ptr(), dev_diam[k].data_ptr(), N, box, is_f32=True)
-        ctx.build_cells()
-        ctx.build_bonds()
-        ctx.ik_compute(_capi.OBS_VIRIAL)
+    comm_ready = [False]
 
-    # end to end: the trajectory loop pipelined over --e2e-lanes contexts (one stream each): frame s+1's upload and
-    # stages overlap frame s's field read-back; every frame is uploaded from and read back to pinned host memory
-    lanes = [(ctx, pin_out)]
-    for _ in range(args.e2e_lanes - 1):
-        ctx_b = _capi.Context(local_rank)
-        ctx_b.set_potential(name, rc, prm)
-        ctx_b.set_cg(*wl["cg"])
-        ctx_b.set_max_rcut(max(rc * dmax, dmax))
-        ctx_b.set_grid_cartesian(axis, axis)
-        if args.shard == "grid" and world > 1:
-            ctx_b.set_shard(*shards[rank])
-        lanes.append((ctx_b, _capi.PinnedArray((g_local, ncomp_out), np.float64)))
-    nl = len(lanes)
+    def comm_init_all(ctxs):
+        for c in ctxs:
+            uid = [_capi.Context.comm_unique_id() if rank == 0 else None]
+            dist.broadcast_object_list(uid, src=0)
+            c.comm_init(world, rank, uid[0])
 
-    def step_e2e(s, k):
-        c, out = lanes[s % nl]
-        c.upload(pin_pos[k].array, pin_diam[k].array, box)
+    def step_resident(c, k):
+        c.set_device_frame(dev_pos[k].data_ptr(), dev_diam[k].data_ptr(), N, box, is_f32=True)
+        c.build_cells()
+        c.build_bonds()
+        c.ik_compute(_capi.OBS_VIRIAL)
+
+    def make_lanes(first_ctx, nlanes, shard):
+        lanes = [(first_ctx, _capi.PinnedArray((shard[1] - shard[0], ncomp_out), np.float64))]
+        for _ in range(nlanes - 1):
+            cb = setup_ctx(_capi, synth, local_rank, wl, dmax, L)
+            cb.set_shard(*shard)
+            lanes.append((cb, _capi.PinnedArray((shard[1] - shard[0], ncomp_out), np.float64)))
+        return lanes
+
+    chunk = (N + world - 1) // world
+    p_first, p_last = rank * chunk, min(N, (rank + 1) * chunk)
+
+    def step_e2e(lanes, s, k, parts):
+        c, out = lanes[s % len(lanes)]
+        if parts:
+            # this rank's 1/world of the frame over PCIe, the rest over NVLink
+            c.upload_part(pin_pos[k].array[p_first:p_last], pin_diam[k].array[p_first:p_last], p_first, N, box)
+            c.comm_allgather_frame()
+        else:
+            c.upload(pin_pos[k].array, pin_diam[k].array, box)
         c.build_cells()
         c.build_bonds()
         c.ik_compute(_capi.OBS_VIRIAL)
@@ -328,14 +508,68 @@ def main():
         else:
             c.ik_download_async(_capi.FIELD_VIRIAL, out.array)
 
+    def time_resident(c, steps, warm):
+        for s in range(warm):
+            step_resident(c, s % pool)
+        barrier()
+        c.sync()
+        l0 = c.launches()
+        st = {"cells": [], "bonds": []}
+        t0 = time.time()
+        c.event_record(0)
+        for s in range(steps):
+            step_resident(c, s % pool)
+            # build_cells/build_bonds synchronise the stream, so the previous stages' events are complete
+            st["cells"].append(c.stage_ms("cells"))
+            st["bonds"].append(c.stage_ms("bonds"))
+        c.event_record(1)
+        c.sync()
+        barrier()
+        t1 = time.time()
+        return max_over_ranks(c.event_elapsed_ms(0, 1)), c.launches() - l0, st, (t0, t1)
+
+    def time_e2e(lanes, steps, warm, parts, threads):
+        nl = len(lanes)
+        for s in range(max(warm, 3)):
+            step_e2e(lanes, s, s % pool, parts)
+        for c, _ in lanes:
+            c.sync()
+        barrier()
+        t0 = time.time()
+        lanes[0][0].event_record(2)
+        if threads == 2 and nl > 1 and not parts:
+            # one host thread per lane (ctypes releases the GIL inside the C-ABI calls): while one lane's host thread waits
+            # for a stage's counts, the other keeps the device fed
+            def lane_worker(lane):
+                for s in range(lane, steps, nl):
+                    step_e2e(lanes, s, s % pool, parts)
+            workers = [threading.Thread(target=lane_worker, args=(lane,)) for lane in range(nl)]
+            for t in workers:
+                t.start()
+            for t in workers:
+                t.join()
+        else:
+            # collectives must be issued in the same order on every rank: one host thread
+            for s in range(steps):
+                step_e2e(lanes, s, s % pool, parts)
+        for c, _ in reversed(lanes):               # every lane drained: the end event below is later than all work
+            c.sync()
+        lanes[0][0].event_record(3)
+        lanes[0][0].sync()
+        barrier()
+        t1 = time.time()
+        return max_over_ranks(lanes[0][0].event_elapsed_ms(2, 3)), (t0, t1)
+
     # ---- algorithmic work of the gather per frame (outside the timed regions)
-    flops_per_frame, items_per_frame, hb_per_frame = [], [], []
+    flops_per_frame, items_per_frame, hb_per_frame, ncells = [], [], [], 0
     for k in range(pool):
-        step_resident(k)
+        step_resident(ctx, k)
         w = ctx.ik_count_work()
         flops_per_frame.append(w["unique_bonds"] * (15 * q + 9))
         items_per_frame.append(w["halfbond_items"])
-        hb_per_frame.append(ctx.counts()["n_halfbonds"])
+        cnt = ctx.counts()
+        hb_per_frame.append(cnt["n_halfbonds"])
+        ncells = cnt["n_cells"]
     fp64_peak = ctx.fp64_peak()                               # DFMA-loop probe, TFLOP/s, this GPU, this run
 
     sampler = ClockSampler(local_rank)
@@ -343,133 +577,167 @@ def main():
         sampler.start()
 
     # ---- device-resident timing -------------------------------------------------------------
-    for s in range(args.warmup):
-        step_resident(s % pool)
-    barrier()
-    ctx.sync()
-    launches0 = ctx.launches()
-    stage_ms = {"cells": [], "bonds": [], "ik": []}
-    w0 = time.time()
-    ctx.event_record(0)
-    for s in range(args.steps):
-        step_resident(s % pool)
-        # build_cells/build_bonds synchronise the stream, so the previous stages' events are complete
-        stage_ms["cells"].append(ctx.stage_ms("cells"))
-        stage_ms["bonds"].append(ctx.stage_ms("bonds"))
-    ctx.event_record(1)
-    ctx.sync()
-    barrier()
-    w1 = time.time()
-    launches_resident = ctx.launches() - launches0
-    ms_resident = max_over_ranks(ctx.event_elapsed_ms(0, 1))
+    ms_resident, launches_resident, stage_ms, win_a = time_resident(ctx, args.steps, args.warmup)
 
     # the gather kernel alone, timed live over the same region (separate pass so that reading the
     # event does not perturb the step loop above)
     ik_ms = []
     for s in range(min(args.steps, 50)):
-        step_resident(s % pool)
+        step_resident(ctx, s % pool)
         ik_ms.append((s % pool, ctx.stage_ms("ik")))
 
     # ---- end to end: host buffers in, host field out -----------------------------------------
-    for s in range(max(args.warmup, 3)):
-        step_e2e(s, s % pool)
-    for c, _ in lanes:
-        c.sync()
-    barrier()
-    w2 = time.time()
-    ctx.event_record(2)
-    if args.e2e_threads == 2:
-        # one host thread per lane (ctypes releases the GIL inside the C-ABI calls): while one lane's host thread waits
-        # for a stage's counts, the other keeps the device fed
-        import threading
+    my_shard = shards[rank] if grid_mode else (0, G)
+    lanes = make_lanes(ctx, args.e2e_lanes, my_shard)
+    if grid_mode:
+        comm_init_all([c for c, _ in lanes])
+    ms_e2e, win_b = time_e2e(lanes, args.steps, args.warmup, grid_mode, args.e2e_threads)
+    e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
+    assert np.isfinite(e2e_check) and e2e_check > 0
 
-        def lane_worker(lane):
-            for s in range(lane, args.steps, nl):
-                step_e2e(s, s % pool)
-
-        workers = [threading.Thread(target=lane_worker, args=(lane,)) for lane in range(nl)]
-        for t in workers:
-            t.start()
-        for t in workers:
-            t.join()
-    else:
-        for s in range(args.steps):
-            step_e2e(s, s % pool)
-    for c, _ in reversed(lanes):                   # every lane drained: the end event below is later than all work
-        c.sync()
-    ctx.event_record(3)
-    ctx.sync()
-    barrier()
-    w3 = time.time()
-    ms_e2e = max_over_ranks(ctx.event_elapsed_ms(2, 3))
+    # ---- N > 1: one frame split over the ranks by grid points (the reference's MPI decomposition), strong scaling
+    grid_shard = None
+    if world > 1 and not grid_mode and not args.no_grid_shard:
+        gsteps = max(10, args.steps // 2)
+        for c, _ in lanes[1:]:
+            c.close()
+        # every rank works on rank 0's frames now
+        frames0 = make_frames(wl, 0, pool)
+        for k, f in enumerate(frames0):
+            pin_pos[k].array[...] = f["position"]
+            pin_diam[k].array[...] = f["diameter"]
+            dev_pos[k].copy_(torch.from_numpy(f["position"]))
+            dev_diam[k].copy_(torch.from_numpy(f["diameter"]))
+        torch.cuda.synchronize()
+        full_ref = None
+        if rank == 0:                                         # the single-GPU field of frame 0, for the bitwise check
+            step_resident(ctx, 0)
+            full_ref = ctx.ik_download()
+        ctx.set_shard(*shards[rank])
+        ms_g, launches_g, stage_g, _ = time_resident(ctx, gsteps, args.warmup)
+        glanes = make_lanes(ctx, min(args.e2e_lanes, 2), shards[rank])
+        comm_init_all([c for c, _ in glanes])
+        ms_ge, _ = time_e2e(glanes, gsteps, args.warmup, True, 1)
+        # the NCCL legs alone: frame all-gather, field all-gather
+        step_resident(ctx, 0)
+        gathered = torch.empty((G, 4), dtype=torch.float64, device="cuda")
+        counts = [4 * (e - b) for b, e in shards]
+        ctx.sync()
+        barrier()
+        ctx.event_record(4)
+        for _ in range(10):
+            ctx.comm_allgather_field(_capi.FIELD_VIRIAL, counts, gathered.data_ptr())
+        ctx.event_record(5)
+        ctx.sync()
+        nccl_field_ms = max_over_ranks(ctx.event_elapsed_ms(4, 5) / 10)
+        ctx.upload_part(pin_pos[0].array[p_first:p_last], pin_diam[0].array[p_first:p_last], p_first, N, box)
+        ctx.sync()
+        barrier()
+        ctx.event_record(6)
+        for _ in range(10):
+            ctx.comm_allgather_frame()
+        ctx.event_record(7)
+        ctx.sync()
+        nccl_frame_ms = max_over_ranks(ctx.event_elapsed_ms(6, 7) / 10)
+        check = None
+        if rank == 0:
+            check = "bitwise" if np.array_equal(gathered.cpu().numpy(), full_ref) else "MISMATCH"
+        kept = ctx.counts()["n_live"]
+        t1_ms = ms_resident / args.steps                     # this run's single-GPU step on the same workload
+        grid_shard = {
+            "what": "ONE frame per step, its %d grid points split over %d GPUs at np.array_split boundaries (irvingkirkwood/__init__.py:53-60); every rank builds slab-local cell and bond lists" % (G, world),
+            "value": G * gsteps / (ms_g * 1e-3), "unit": UNIT, "ms_per_step": ms_g / gsteps, "scaling": "strong",
+            "efficiency_vs_n1": (t1_ms / (ms_g / gsteps)) / world,
+            "stage_ms": {"cells": float(np.mean(stage_g["cells"])), "bonds": float(np.mean(stage_g["bonds"])), "ik": ctx.stage_ms("ik")},
+            "particles_kept_rank0": kept, "particles_total": N,
+            "e2e": {"value": G * gsteps / (ms_ge * 1e-3), "unit": UNIT, "ms_per_step": ms_ge / gsteps,
+                    "h2d_bytes_per_step": (p_last - p_first) * 16, "d2h_bytes_per_step": (shards[rank][1] - shards[rank][0]) * ncomp_out * 8,
+                    "efficiency_vs_n1_e2e": ((ms_e2e / args.steps) / (ms_ge / gsteps)) / world,
+                    "api": "pgt_frame_upload_part (1/%d of the frame over PCIe) + pgt_comm_allgather_frame (ncclAllGather over NVLink) .. pgt_ik_download_%sasync of the rank's own shard, %d contexts, one host thread" % (world, "sym_" if ncomp_out == 3 else "", len(glanes))},
+            "collective": "ncclAllGather (frame parts, %.1f MB per rank -> %.1f MB) inside the timed e2e region; ncclBroadcast group (final field gather, %.0f MB) timed separately" % ((p_last - p_first) * 16 / 1e6, N * 16 / 1e6, G * 32 / 1e6),
+            "nccl_ms": {"allgather_frame": nccl_frame_ms, "allgather_field": nccl_field_ms},
+            "gather_check": check, "steps": gsteps,
+        }
+        launches_resident += launches_g
     if rank == 0:
         sampler.stop()
 
-    if args.shard == "grid" and world > 1:
-        # final field gather over NVLink (one NCCL broadcast per shard inside a group), checked once
-        uid = [ctx.comm_unique_id() if rank == 0 else None]
-        dist.broadcast_object_list(uid, src=0)
-        ctx.comm_init(world, rank, uid[0])
-        full = torch.empty((G, 4), dtype=torch.float64, device="cuda")
-        ctx.comm_allgather_field(_capi.FIELD_VIRIAL, [4 * s for s in sizes], full.data_ptr())
-        ctx.sync()
-
     # ---- report ------------------------------------------------------------------------------
-    units_per_step = G if (args.shard == "frames" or world == 1) else G / world
+    units_per_step = G if not grid_mode else g_local
     total_units = sum_over_ranks(units_per_step * args.steps)
     value = total_units / (ms_resident * 1e-3)
     e2e_value = total_units / (ms_e2e * 1e-3)
     launches_total = int(sum_over_ranks(launches_resident))
-    e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
-    assert np.isfinite(e2e_check) and e2e_check > 0
     ik_avg_ms = float(np.mean([m for _, m in ik_ms]))
-    flops_avg = float(np.mean([flops_per_frame[k] for k, _ in ik_ms])) * (g_local / G if args.shard == "grid" else 1.0)
+    flops_avg = float(np.mean([flops_per_frame[k] for k, _ in ik_ms])) * (g_local / G if grid_mode else 1.0)
     achieved = flops_avg / (ik_avg_ms * 1e-3) / 1e12
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
-    # DRAM bytes of one gather launch from the committed `ncu --set full` capture of this workload (profiles/)
-    traffic = None
+    hbm = peaks.get("hbm_gbs")
+    # DRAM bytes of one gather launch: not a counter of THIS run -- the committed `ncu --set full` capture of the same
+    # workload and kernel (profiles/), named so that a stale figure is visible
+    traffic, traffic_src = None, None
     try:
-        if args.workload == "cfg5" and args.shard == "frames":
-            for line in open(os.path.join(ROOT, "profiles", "r1_ik_gather2_full_cfg5.txt")):
+        if args.workload == "cfg5" and not grid_mode:
+            prof = os.path.join("profiles", "r2_ik_quad_full_cfg5.txt")
+            for line in open(os.path.join(ROOT, prof)):
                 if line.startswith("traffic"):
-                    traffic = float(line.split()[-1])
+                    traffic, traffic_src = float(line.split()[-1]), prof
     except Exception:
         pass
-    h2d = N * 3 * 4 + N * 4
+    h2d = N * 3 * 4 + N * 4 if not grid_mode else (p_last - p_first) * 16
     d2h = g_local * ncomp_out * 8
+    sb = stage_bytes(N, ncells, float(np.mean(hb_per_frame)))
+    cells_ms, bonds_ms = float(np.mean(stage_ms["cells"])), float(np.mean(stage_ms["bonds"]))
+
+    def stage_line(nbytes, ms):
+        gbs = nbytes / (ms * 1e-3) / 1e9
+        return {"bytes": nbytes, "ms": ms, "gbs": gbs, "frac": (gbs / hbm) if hbm else None}
 
     if rank == 0:
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_resident / args.steps, "higher_is_better": True,
-            "scaling": "weak" if args.shard == "frames" else "strong", "vs_baseline": None, "dtype": "f64",
+            "scaling": "weak" if not grid_mode else "strong", "vs_baseline": None, "dtype": "f64",
             "data": "synthetic",
-            "config": {"workload": args.workload, "description": wl["desc"], "N": N, "grid": G, "potential": wl["pot"],
-                       "cg": {"kernel": wl["cg"][0], "rcut": wl["cg"][1], "order": q}, "shard": args.shard,
-                       "frames_per_step_per_gpu": 1 if args.shard == "frames" else 1.0 / world, "frame_pool": pool,
-                       "l2": "inputs larger than L2: each step rebuilds and streams a %.0f MB half-bond list + %.0f MB sorted frame"
-                             % (np.mean(hb_per_frame) * 36 / 1e6, N * 28 / 1e6),
-                       "stages_timed": "1-5 (cells, pair forces + half-bonds, IK gather, virial field)"},
-            "clocks": sampler.summary([(w0, w1), (w2, w3)]),
+            "config": config_dict(args, wl, world, pool),
+            "clocks": sampler.summary([win_a, win_b]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                     "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames pipelined over %d contexts, %s" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread")},
             "gpu_launches": launches_total,
-            "stage_ms": {"cells": float(np.mean(stage_ms["cells"])), "bonds": float(np.mean(stage_ms["bonds"])), "ik": ik_avg_ms},
-            "roofline": {"kernel": "k_ik_gather", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
+            "stage_ms": {"cells": cells_ms, "bonds": bonds_ms, "ik": ik_avg_ms},
+            "roofline": {"kernel": "k_ik_quad", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",
                          "frac": achieved / fp64_peak,
                          "peak_source": "DFMA-loop probe run on this GPU in this process (MEASURED_PEAKS.json has no FP64 entry); "
                                         "nominal 148 SM x 64 FMA/clk x 2 x 1.965 GHz = 37.2",
                          "frac_of_nominal_37.2": achieved / 37.2,
                          "work": "sum_x U(x)*(15q+9) flops, U counted on device (pgt_ik_count_work), %.4g flops per launch"
                                  % flops_avg,
-                         "items_per_unique_bond": float(np.mean(items_per_frame)) / max(1.0, float(np.mean(flops_per_frame)) / (15 * q + 9)),
-                         "traffic": traffic,
-                         "hbm_peak_gbs": peaks.get("hbm_gbs")},
+                         "items_per_unique_bond": 1.0,
+                         "items_note": "the quad gather integrates every unique bond once (weight 1 or 1/2); the reference's half-bond formulation visits %.3f items per unique bond"
+                                       % (float(np.mean(items_per_frame)) / max(1.0, float(np.mean(flops_per_frame)) / (15 * q + 9))),
+                         "traffic": traffic, "traffic_from_profile": traffic_src,
+                         "hbm_peak_gbs": hbm},
+            "roofline_stages": {"bound": "hbm", "peak_gbs": hbm, "peak_source": "MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)",
+                                "bytes_model": "SURVEY.md 8(d): cells 60 B/particle + 8 B/cell; bonds 32 B/particle + 36 B/half-bond",
+                                "cells": stage_line(sb["cells"], cells_ms), "bonds": stage_line(sb["bonds"], bonds_ms)},
         }
+        if grid_shard is not None:
+            out["grid_shard"] = grid_shard
+        if world == 1 and not args.no_other_configs and args.workload == "cfg5":
+            oc = {}
+            for key, fn in (("cfg1", lambda: fixture_workload(_capi, synth, local_rank)),
+                            ("cfg2", lambda: thermo_workload(_capi, synth, local_rank)),
+                            ("cfg3", lambda: quick_workload(_capi, synth, local_rank, "cfg3")),
+                            ("cfg4", lambda: quick_workload(_capi, synth, local_rank, "cfg4"))):
+                try:
+                    oc[key] = fn()
+                except Exception as e:                       # a side measurement must not lose the main line
+                    oc[key] = {"error": repr(e)}
+            out["other_configs"] = oc
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl, frames[0], args)
         print(json.dumps(out), flush=True)
@@ -479,33 +747,32 @@ def main():
 
 
 def cpu_baseline(wl, fr, args):
-    """The oracle on the box's host cores, on a bounded strided sample of the same frame's grid."""
-    from oracle import orc
-    from pyglasstools_b200 import synth
-    name, rc, prm = pot_params(wl["pot"])
-    P = orc.potential(name)
-    cg = orc.cgfunc(*wl["cg"])
-    t0 = time.time()
-    S = orc.System(fr["box"], fr["position"], fr["diameter"])
-    build_s = time.time() - t0
-    L = float(fr["box"][0])
-    nmax = wl["nmax"]
-    axis = synth.linspace_axis(L, nmax)
-    stride = args.cpu_sample_stride or 1
-    ii = np.arange(0, nmax, stride)
-    grid = np.zeros((len(ii) ** 2, 3))
-    grid[:, 0] = np.repeat(axis[ii], len(ii))
-    grid[:, 1] = np.tile(axis[ii], len(ii))
-    mr = S.max_rcut(P)
-    S.ik(P, cg, grid[:4096], max_rcut=mr)
-    passes, t0 = 0, time.perf_counter()
-    while passes < 1 or (time.perf_counter() - t0 < 10.0 and passes < 64):     # >= 10 s of CPU work
-        S.ik(P, cg, grid, max_rcut=mr)
-        passes += 1
-    dt = (time.perf_counter() - t0) / passes
-    return {"value": len(grid) / dt, "unit": UNIT, "cores": orc.num_threads(), "kind": "port",
-            "sample": "%d of %d grid points (every %d-th in i and j) of one frame, %d passes of %.1f s; oracle frame build %.1f s excluded"
-                      % (len(grid), nmax * nmax, stride, passes, dt, build_s)}
+    """The oracle on the box's host cores, on a bounded strided sample of the same frame's grid: the timing build
+    (the reference's flags) is the reported number, the parity build's rate is given beside it once."""
+    stride = args.cpu_sample_stride or max(1, int(round(wl["nmax"] / 1024.0)))
+    r = oracle_rate(wl, fr, stride, 10.0, 1)
+    out = {"value": r["rate"], "unit": UNIT, "cores": r["cores"], "kind": "port",
+           "sample": "%d of %d grid points (every %d-th in i and j) of one frame, %d passes of %.1f s; oracle frame build %.1f s excluded; %s = oracle/pgt_oracle.cpp built -O3 -march=native -fopenmp (CompilerFlagsSetup.cmake:14)"
+                     % (r["points"], wl["nmax"] ** 2, r["stride"], r["passes"], r["dt"], r["build_s"], r["lib"])}
+    # the parity build (-O2 -ffp-contract=off) in a child process (one oracle library per process), a shorter sample
+    try:
+        code = ("import json,sys;sys.path.insert(0,%r);import bench;from pyglasstools_b200 import synth;"
+                "import os;os.environ.pop('PGT_ORACLE_FAST',None);"
+                "wl=bench.WORKLOADS[%r];fr=synth.synth_frame(wl['n'],synth.SEEDS[wl['seed']]);"
+                "from oracle import orc;import numpy as np,time;orc.set_num_threads(len(os.sched_getaffinity(0)));"
+                "n,rc,prm=bench.pot_params(wl['pot']);P=orc.potential(n);cg=orc.cgfunc(*wl['cg']);S=orc.System(fr['box'],fr['position'],fr['diameter']);"
+                "ax=synth.linspace_axis(float(fr['box'][0]),wl['nmax']);ii=np.arange(0,wl['nmax'],%d);g=np.zeros((len(ii)**2,3));g[:,0]=np.repeat(ax[ii],len(ii));g[:,1]=np.tile(ax[ii],len(ii));"
+                "mr=S.max_rcut(P);S.ik(P,cg,g[:4096],max_rcut=mr);t=time.perf_counter();S.ik(P,cg,g,max_rcut=mr);print(json.dumps(len(g)/(time.perf_counter()-t)))"
+                % (ROOT, args.workload, stride * 2))
+        env = dict(os.environ)
+        env.pop("PGT_ORACLE_FAST", None)
+        res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=180, env=env)
+        out["parity_build_value"] = float(json.loads(res.stdout.strip().splitlines()[-1]))
+        out["parity_build"] = "liborc.so (-O2 -ffp-contract=off, the ISO-C reading used by the parity tests), every %d-th grid row and column" % (stride * 2)
+    except Exception as e:
+        out["parity_build_value"] = None
+        out["parity_build"] = "not measured: %r" % (e,)
+    return out
 
 
 if __name__ == "__main__":

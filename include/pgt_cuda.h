@@ -84,6 +84,14 @@ int pgt_set_cell_size(pgt_ctx* ctx, double cell_side);
  * is asynchronous on the ctx stream from the caller's (ideally pinned) memory.               */
 int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel,
                      int is_f32, int64_t N, const double box[3], int dim);
+/* One rank's PART of a frame (grid-point sharding over GPUs: every GPU needs the whole frame, but each rank pushes
+ * only 1/nranks of it over PCIe and pgt_comm_allgather_frame assembles it on every GPU over NVLink).  Parts are
+ * ceil(N / nranks) particles each, rank r's starting at particle r * ceil(N / nranks) (the last may be short):
+ * pos_part / diam_part point at the first particle of THIS rank's part, `first` and `count` name it.  float32 or
+ * float64 positions and diameters only (no mass / velocity).  Replaces the per-rank GSD read of the whole frame
+ * (utils.py:97-121 under MPI: every rank reads every frame).                                                       */
+int pgt_frame_upload_part(pgt_ctx* ctx, const void* pos_part, const void* diam_part, int is_f32, int64_t first, int64_t count,
+                          int64_t N, const double box[3], int dim);
 /* Same, from DEVICE pointers already resident in HBM on ctx's device (no host copy).           */
 int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, const void* d_mass, const void* d_vel,
                          int is_f32, int64_t N, const double box[3], int dim);
@@ -100,7 +108,10 @@ int pgt_frame_counts(pgt_ctx* ctx, int64_t* n_live, int64_t* n_halfbonds, int64_
 int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double* ys, int ny);
 /* Arbitrary points (radialcalculator, irvingkirkwood/__init__.py:80-166): xyz is G x 3.        */
 int pgt_grid_set_points(pgt_ctx* ctx, const double* xyz, int64_t G);
-/* This ctx computes global points [g0,g1) (np.array_split boundaries are the caller's job).    */
+/* This ctx computes global points [g0,g1) (np.array_split boundaries are the caller's job).  On a Cartesian grid with
+ * non-decreasing axes a strict sub-range also restricts stages 1-3 to the particles the shard's tiles can reach
+ * (option "slab_cull", default 1): the field is bit-identical, pgt_frame_counts reports the particles kept, and
+ * pgt_thermo_compute refuses such a frame (build it with the whole grid, or set "slab_cull" to 0).                 */
 int pgt_grid_set_shard(pgt_ctx* ctx, int64_t g0, int64_t g1);
 
 /* ---- compute ------------------------------------------------------------------------------- */
@@ -125,6 +136,11 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
  * then Dim^4 Born tensor (col-major flat); all already multiplied by 1/vol.  Entries whose
  * observable is not in obs_mask are 0.  out must hold 2*Dim^2 + 1 + Dim^4 doubles.              */
 int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out);
+/* Particle-sharded thermo sums over GPUs: this ctx sums the pairs (id_i < id_j) visited from part `part` of `nparts`
+ * equal shares of the sorted particles; the nparts partial results add up to pgt_thermo_compute's (sum them with
+ * pgt_comm_allreduce_sum: the role of MPI reductions the reference never needed, ThermoCalculator being serial).
+ * (0, 1) restores the whole frame.                                                                                  */
+int pgt_thermo_set_shard(pgt_ctx* ctx, int part, int nparts);
 /* Replaces: ParticleSystem::setDisplacement (ParticleSystem.cc:60-67): N x 3 doubles, one row per particle of the frame
  * last uploaded, in the frame's own order.  A new frame starts with zero displacements (ParticleSystem.cc:28).   */
 int pgt_frame_set_displacement(pgt_ctx* ctx, const double* disp_xyz, int64_t N);
@@ -166,7 +182,8 @@ int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
 /* Page-locked host memory for the caller's frame / field buffers (cudaHostAlloc / cudaFreeHost). */
 int pgt_host_alloc(void** ptr, uint64_t bytes);
 int pgt_host_free(void* ptr);
-/* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 4 tile gather, 5 / 6 walk gather with records via L1 / staged);
+/* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 7 quad gather where it applies);
+ * "slab_cull" (1 default: a grid shard restricts stages 1-3 to the particles it can reach, 0: every rank builds the whole frame);
  * "bond_single_search" (1 default: one neighbour search per frame, 0: separate count and fill searches);
  * "bond_fill_flat" (1 default: warp-flattened record writer, 0: thread per particle).  Every setting gives the same
  * bits.  Environment, read once: PGT_IK_VARIANT, PGT_BOND_FILL_FLAT, PGT_SCAN_SINGLE_PASS (0: three-kernel scan). */
@@ -179,6 +196,9 @@ int pgt_comm_init(pgt_ctx* ctx, int nranks, int rank, const void* id128);
 /* Final field gather: every rank contributes its shard, out_dev (device, G_total*ncomp doubles
  * on every rank) receives all shards in rank order.  counts[r] = doubles contributed by rank r. */
 int pgt_comm_allgather_field(pgt_ctx* ctx, int field_id, const int64_t* counts, void* out_dev);
+/* Assembles the frame on every GPU from the parts pushed by pgt_frame_upload_part: one ncclAllGather per array on the
+ * ctx stream (NVLink / NVSwitch), in place in the frame's device buffers.  No host synchronisation.              */
+int pgt_comm_allgather_frame(pgt_ctx* ctx);
 /* Sum-reduce n doubles in place on the host buffer via the device (thermo partial sums).       */
 int pgt_comm_allreduce_sum(pgt_ctx* ctx, double* inout_host, int n);
 int pgt_comm_destroy(pgt_ctx* ctx);

@@ -49,10 +49,29 @@ def _ip(a):
 
 
 def lib():
+    """liborc.so (ISO-C reading, -ffp-contract=off: the PARITY build); with PGT_ORACLE_FAST=1 in the environment before the
+    first call, liborc_fast.so: the same source built with the reference's own flags (-O3 -march=native,
+    CompilerFlagsSetup.cmake:14), the TIMING build of bench.py's CPU legs."""
     global _lib
     if _lib is None:
         build()
-        L = C.CDLL(os.path.join(_HERE, "liborc.so"))
+        name = "liborc.so"
+        if os.environ.get("PGT_ORACLE_FAST") == "1":
+            # -march=native binds the build to the CPU it was made on: rebuilt when this host's CPU is another model
+            fast = os.path.join(_HERE, "liborc_fast.so")
+            src = os.path.join(_HERE, "pgt_oracle.cpp")
+            tag = os.path.join(_HERE, "liborc_fast.cpu")
+            try:
+                cpu = [l for l in open("/proc/cpuinfo") if l.startswith("model name")][0].split(":", 1)[1].strip()
+            except Exception:
+                cpu = "unknown"
+            built_for = open(tag).read().strip() if os.path.exists(tag) else ""
+            if not os.path.exists(fast) or os.path.getmtime(fast) < os.path.getmtime(src) or built_for != cpu:
+                subprocess.check_call(["make", "-B", "-C", _HERE, "liborc_fast.so"], stdout=subprocess.DEVNULL)
+                open(tag, "w").write(cpu + "\n")
+            name = "liborc_fast.so"
+        L = C.CDLL(os.path.join(_HERE, name))
+        L._pgt_build = name
         L.orc_pair_eval.restype = C.c_double
         L.orc_pair_eval.argtypes = [C.POINTER(OrcPot), C.POINTER(C.c_double), C.c_double, C.c_double, C.c_int]
         L.orc_cg_compute.restype = C.c_double
@@ -99,6 +118,73 @@ def ref_lib():
             return None
         _ref = C.CDLL(path)
     return _ref
+
+
+_refloops = None
+
+
+def refloops_lib():
+    """The reference's OWN calculators (IrvingKirkwood::compute, ThermoCalculator::compute, observables, CG functions,
+    ParticleSystem, SimBox) compiled from /root/reference against the stand-ins of oracle/stubs/
+    (oracle/ref_loops_shim.cpp -> oracle/_ref/libpgt_refloops.so).  None when not built."""
+    global _refloops
+    if _refloops is None:
+        build()
+        path = os.path.join(_HERE, "_ref", "libpgt_refloops.so")
+        if not os.path.exists(path):
+            return None
+        lib()                                            # liborc.so first: the stand-in GSL rules resolve into it
+        L = C.CDLL(path)
+        L.ref_ik_compute.restype = C.c_int
+        L.ref_thermo_compute.restype = C.c_int
+        L.ref_cg_bond.restype = C.c_double
+        _refloops = L
+    return _refloops
+
+
+def ref_ik(box, pos, diam, P, cg_kernel, cg_rcut, order, grid, vel=None, mass=None, obs_mask=1):
+    """IrvingKirkwood::compute (irvingkirkwood/IrvingKirkwood.h:74-110) of the reference itself on `grid` (G x 3)."""
+    L = refloops_lib()
+    box = np.ascontiguousarray(np.asarray(box, np.float64)[:3])
+    pos = np.ascontiguousarray(pos, np.float64)
+    diam = np.ascontiguousarray(diam, np.float64)
+    vel = None if vel is None else np.ascontiguousarray(vel, np.float64)
+    mass = None if mass is None else np.ascontiguousarray(mass, np.float64)
+    grid = np.ascontiguousarray(grid, np.float64)
+    prm = np.ascontiguousarray(pot_params(P), np.float64)
+    G = len(grid)
+    vir = np.zeros((G, 4)) if obs_mask & 1 else None
+    kin = np.zeros((G, 4)) if obs_mask & 2 else None
+    mr, nl = C.c_double(0.0), C.c_int64(0)
+    vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    kid = {"octic": 0, "rect": 1, "mollifier": 2}[cg_kernel]
+    rc = L.ref_ik_compute(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), None, C.c_int(P.model),
+                          C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_int(kid), C.c_double(cg_rcut), C.c_int(order),
+                          C.c_int(0), C.c_double(0.0), C.c_double(0.0), C.c_int(0), C.c_int64(G), vp(grid), C.c_uint(obs_mask),
+                          vp(vir), vp(kin), None, C.byref(mr), C.byref(nl))
+    if rc != 0:
+        raise RuntimeError("ref_ik_compute failed (%d)" % rc)
+    return dict(virial=vir, kinetic=kin, max_rcut=mr.value, n_live=nl.value)
+
+
+def ref_thermo(box, pos, diam, P, vel=None, mass=None, obs_mask=1 | 4 | 8):
+    """ThermoCalculator::compute (thermo/ThermoCalculator.h:68-90) of the reference itself; obs_mask bit0 virial,
+    bit1 kinetic, bit2 energy, bit3 Born tensor."""
+    L = refloops_lib()
+    box = np.ascontiguousarray(np.asarray(box, np.float64)[:3])
+    pos = np.ascontiguousarray(pos, np.float64)
+    diam = np.ascontiguousarray(diam, np.float64)
+    vel = None if vel is None else np.ascontiguousarray(vel, np.float64)
+    mass = None if mass is None else np.ascontiguousarray(mass, np.float64)
+    prm = np.ascontiguousarray(pot_params(P), np.float64)
+    out = np.zeros(29)
+    mr = C.c_double(0.0)
+    vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+    rc = L.ref_thermo_compute(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), None, C.c_int(P.model),
+                              C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_uint(obs_mask), vp(out), C.byref(mr))
+    if rc != 0:
+        raise RuntimeError("ref_thermo_compute failed (%d)" % rc)
+    return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy(), max_rcut=mr.value)
 
 
 # ---------------------------------------------------------------------------

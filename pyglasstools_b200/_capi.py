@@ -27,9 +27,17 @@ EXPORTED = [
     "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
+    "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard",
 ]
 
 _lib = None
+
+
+def device_count():
+    """CUDA devices visible to this process (0 without a driver)."""
+    n = C.c_int(0)
+    lib().pgt_device_count(C.byref(n))
+    return n.value
 
 
 def cg_bond_adaptive(kernel, rcut, relerr, abserr, maxiter, x, ri, rij):
@@ -112,6 +120,10 @@ def lib():
         L.pgt_comm_allgather_field.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_int64), C.c_void_p]
         L.pgt_comm_allreduce_sum.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int]
         L.pgt_comm_destroy.argtypes = [C.c_void_p]
+        L.pgt_frame_upload_part.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int64, C.c_int64,
+                                            C.POINTER(C.c_double), C.c_int]
+        L.pgt_comm_allgather_frame.argtypes = [C.c_void_p]
+        L.pgt_thermo_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
         _lib = L
     return _lib
 
@@ -179,6 +191,18 @@ class Context:
         b = (C.c_double * 3)(*[float(x) for x in box[:3]])
         vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
         self._ck(lib().pgt_frame_upload(self._h, vp(pos), vp(diam), vp(mass), vp(vel), int(f32), len(diam), b, dim))
+
+    def upload_part(self, pos_part, diam_part, first, n_total, box, dim=2):
+        """This rank's part of a frame (rows [first, first + len(diam_part)) of the N x 3 positions); assemble the frame
+        on every GPU with comm_allgather_frame()."""
+        f32 = pos_part.dtype == np.float32
+        dt = np.float32 if f32 else np.float64
+        pos_part = np.ascontiguousarray(pos_part, dt)
+        diam_part = np.ascontiguousarray(diam_part, dt)
+        self._keep["frame"] = (pos_part, diam_part)          # the copy is asynchronous
+        b = (C.c_double * 3)(*[float(x) for x in box[:3]])
+        self._ck(lib().pgt_frame_upload_part(self._h, pos_part.ctypes.data_as(C.c_void_p), diam_part.ctypes.data_as(C.c_void_p),
+                                             int(f32), int(first), len(diam_part), int(n_total), b, dim))
 
     def set_device_frame(self, d_pos, d_diam, n, box, is_f32=True, d_mass=None, d_vel=None, dim=2):
         b = (C.c_double * 3)(*[float(x) for x in box[:3]])
@@ -340,6 +364,12 @@ class Context:
     def comm_allgather_field(self, field, counts, out_dev_ptr):
         c = (C.c_int64 * len(counts))(*[int(x) for x in counts])
         self._ck(lib().pgt_comm_allgather_field(self._h, int(field), c, C.c_void_p(out_dev_ptr)))
+
+    def comm_allgather_frame(self):
+        self._ck(lib().pgt_comm_allgather_frame(self._h))
+
+    def thermo_set_shard(self, part, nparts):
+        self._ck(lib().pgt_thermo_set_shard(self._h, int(part), int(nparts)))
 
     def comm_allreduce_sum(self, arr):
         a = np.ascontiguousarray(arr, np.float64)

@@ -31,6 +31,7 @@ struct NcclApi {
     int (*CommDestroy)(pgtNcclComm) = nullptr;
     int (*AllReduce)(const void*, void*, size_t, int, int, pgtNcclComm, cudaStream_t) = nullptr;
     int (*Broadcast)(const void*, void*, size_t, int, int, pgtNcclComm, cudaStream_t) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, pgtNcclComm, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
@@ -41,10 +42,13 @@ NcclApi g_nccl;
 bool load_nccl(std::string& err)
 {
     if (g_nccl.ok) return true;
-    const char* names[] = { "libnccl.so.2", "libnccl.so" };
+    // A copy the process has already loaded (a host program that bundles NCCL, e.g. torch) wins: two libnccl.so.2 in one
+    // process break whichever is loaded second.  Otherwise the system copy by absolute path, then the loader's search.
+    g_nccl.handle = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    const char* names[] = { "/usr/lib/x86_64-linux-gnu/libnccl.so.2", "libnccl.so.2", "libnccl.so" };
     for (const char* n : names) {
-        g_nccl.handle = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
         if (g_nccl.handle) break;
+        g_nccl.handle = dlopen(n, RTLD_NOW | RTLD_LOCAL);    // local: never interposes on a copy loaded later
     }
     if (!g_nccl.handle) { err = std::string("cannot dlopen libnccl: ") + dlerror(); return false; }
 #define PGT_SYM(field, name)                                                      \
@@ -55,6 +59,7 @@ bool load_nccl(std::string& err)
     PGT_SYM(CommDestroy, "ncclCommDestroy")
     PGT_SYM(AllReduce, "ncclAllReduce")
     PGT_SYM(Broadcast, "ncclBroadcast")
+    PGT_SYM(AllGather, "ncclAllGather")
     PGT_SYM(GroupStart, "ncclGroupStart")
     PGT_SYM(GroupEnd, "ncclGroupEnd")
     PGT_SYM(GetErrorString, "ncclGetErrorString")
@@ -172,6 +177,13 @@ struct pgt_ctx {
     double qag_epsabs = 0.0, qag_epsrel = 0.0;
     int qag_limit = 0;
     bool grid_monotone = false;
+    std::vector<double> h_xs;         // host copy of the Cartesian x axis (slab of a grid shard)
+    bool slab_cull = true;            // option "slab_cull"
+    bool culled = false;              // the frame in HBM holds only the particles the grid shard can reach
+    double slab_lo = 0.0, slab_hi = 0.0;
+    int64_t part_chunk = 0;           // pgt_frame_upload_part: particles per rank part (0: whole-frame upload)
+    int thermo_part = 0, thermo_nparts = 1;
+    long long field_g0 = 0, field_g1 = 0;   // the shard the fields in HBM were computed for (pgt_ik_compute)
     double span_x[4] = { -1, -1, -1, -1 }, span_y[4] = { -1, -1, -1, -1 };   // extents of the quad gather's grid tiles (cartesian grids)
 
     // nccl
@@ -523,6 +535,38 @@ int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void
         ctx->src_vel = ctx->raw_vel.p;
     }
     stage_end(ctx, PGT_STAGE_UPLOAD);
+    ctx->part_chunk = 0;
+    return PGT_OK;
+}
+
+int pgt_frame_upload_part(pgt_ctx* ctx, const void* pos_part, const void* diam_part, int is_f32, int64_t first, int64_t count,
+                          int64_t N, const double box[3], int dim)
+{
+    if (!ctx || !box || (count > 0 && (!pos_part || !diam_part))) return fail(ctx, PGT_ERR_ARG, "pgt_frame_upload_part: null argument");
+    if (first < 0 || count < 0 || first + count > N) return fail(ctx, PGT_ERR_ARG, "pgt_frame_upload_part: part [%lld, %lld) outside [0, %lld)", (long long)first, (long long)(first + count), (long long)N);
+    const int nr = std::max(ctx->nranks, 1);
+    const int64_t chunk = (N + nr - 1) / nr;
+    if (ctx->comm && (first != (int64_t)ctx->rank * chunk || count != std::max<int64_t>(0, std::min(chunk, N - first))))
+        return fail(ctx, PGT_ERR_ARG, "pgt_frame_upload_part: rank %d of %d owns particles [%lld, %lld)", ctx->rank, nr,
+                    (long long)(ctx->rank * chunk), (long long)std::min<int64_t>(N, (ctx->rank + 1) * chunk));
+    CK(cudaSetDevice(ctx->device));
+    int rc = set_frame_common(ctx, is_f32, N, box, dim);
+    if (rc != PGT_OK) return rc;
+    const size_t es = is_f32 ? 4 : 8;
+    stage_begin(ctx, PGT_STAGE_UPLOAD);
+    ENSURE(ctx->raw_pos, (size_t)chunk * nr * 3 * es);          // room for nranks equal parts: ncclAllGather moves equal counts
+    ENSURE(ctx->raw_diam, (size_t)chunk * nr * es);
+    if (count > 0) {
+        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_pos.p) + (size_t)first * 3 * es, pos_part, (size_t)count * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_diam.p) + (size_t)first * es, diam_part, (size_t)count * es, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    stage_end(ctx, PGT_STAGE_UPLOAD);
+    ctx->src_pos = ctx->raw_pos.p;
+    ctx->src_diam = ctx->raw_diam.p;
+    ctx->src_mass = nullptr;
+    ctx->src_vel = nullptr;
+    ctx->have_disp = false;
+    ctx->part_chunk = chunk;
     return PGT_OK;
 }
 
@@ -538,6 +582,23 @@ int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, co
     ctx->src_vel = d_vel;
     ctx->have_disp = false;
     return PGT_OK;
+}
+
+// The x interval of the particles a grid shard can reach (Cartesian grid, non-decreasing axes): the shard's grid columns,
+// widened to whole gather tiles (32 columns: a warp's control flow, and so a point's summation order, depends on its
+// tile-mates), plus the coarse-graining radius, the cell rounding of a tile's rectangle and the reach of the bond search.
+static bool shard_slab(const pgt_ctx* ctx, const PgtCells& c, double* lo, double* hi)
+{
+    if (!ctx->slab_cull || ctx->grid_mode != 0 || !ctx->grid_monotone || !ctx->have_cg || ctx->dim != 2) return false;
+    if (ctx->nx <= 0 || ctx->ny <= 0 || ctx->g1 <= ctx->g0 || (ctx->g0 == 0 && ctx->g1 == ctx->G)) return false;
+    if ((int)ctx->h_xs.size() != ctx->nx) return false;
+    const int i_lo = (int)(ctx->g0 / ctx->ny), i_hi = (int)((ctx->g1 - 1) / ctx->ny);
+    const int a_lo = (i_lo / 32) * 32, a_hi = std::min(ctx->nx - 1, (i_hi / 32) * 32 + 31);
+    const double cw = 1.0 / c.inv_cwx;
+    const double margin = ctx->cg.rcut + (c.reach + 4) * cw;
+    *lo = ctx->h_xs[a_lo] - margin;
+    *hi = ctx->h_xs[a_hi] + margin;
+    return *hi - *lo < ctx->box.L[0];
 }
 
 int pgt_build_cells(pgt_ctx* ctx)
@@ -577,8 +638,12 @@ int pgt_build_cells(pgt_ctx* ctx)
     CK(cudaMemsetAsync(ctx->cell_fill.p, 0, sizeof(int) * (size_t)ncells, ctx->stream));
     CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream));
 
+    double slab_lo = 0.0, slab_hi = 0.0;
+    ctx->culled = shard_slab(ctx, c, &slab_lo, &slab_hi);
+    ctx->slab_lo = slab_lo;
+    ctx->slab_hi = slab_hi;
     pgt_launch_wrap_count(ctx->src_pos, ctx->is_f32, N, ctx->box, c, ctx->cell_of.as<int>(), ctx->cell_count.as<int>(),
-                          ctx->eflags.as<int>(), ctx->stream, &ctx->launches);
+                          ctx->eflags.as<int>(), ctx->culled ? 1 : 0, slab_lo, slab_hi, ctx->stream, &ctx->launches);
     pgt_launch_scan_exclusive(ctx->cell_count.as<int>(), ctx->cell_count.as<int>(), (long long)ncells + 1,
                               ctx->scan_scratch.as<int>(), ctx->stream, &ctx->launches);
     pgt_launch_scatter_ids(ctx->cell_of.as<int>(), N, ctx->cell_count.as<int>(), ctx->cell_fill.as<int>(),
@@ -701,6 +766,7 @@ int pgt_grid_set_cartesian(pgt_ctx* ctx, const double* xs, int nx, const double*
         return s;
     };
     ctx->grid_monotone = std::is_sorted(xs, xs + nx) && std::is_sorted(ys, ys + ny);
+    ctx->h_xs.assign(xs, xs + nx);
     for (int w = 1; w <= 4; ++w) {
         ctx->span_x[w - 1] = nx > 0 ? span(xs, nx, 8 * w) : -1.0;
         ctx->span_y[w - 1] = ny > 0 ? span(ys, ny, 4 * w) : -1.0;
@@ -755,8 +821,15 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
         return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
     if (ctx->n_live >= (1 << 28))
         return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_ik_compute: %d live particles; the gather's packed lists address 2^28", ctx->n_live);
+    if (ctx->culled) {
+        double lo = 0.0, hi = 0.0;
+        if (!shard_slab(ctx, ctx->cells, &lo, &hi) || lo < ctx->slab_lo || hi > ctx->slab_hi)
+            return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: the frame was built for another grid shard (rebuild the cells after changing the grid, the shard or the coarse-graining radius)");
+    }
     CK(cudaSetDevice(ctx->device));
     const long long gl = ctx->g1 - ctx->g0;
+    ctx->field_g0 = ctx->g0;                                 // read-backs, device_ptr and the NCCL gather size their copies from these
+    ctx->field_g1 = ctx->g1;
     const size_t n = (size_t)std::max<long long>(gl, 1);
     if (obs_mask & PGT_OBS_VIRIAL) ENSURE(ctx->out_virial, sizeof(double) * 4 * n);
     if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 4 * n);
@@ -831,6 +904,8 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
     a.cells = ctx->cells;
     a.cg = ctx->cg;
     a.inv_rcutsq = 1.0 / ctx->cg.rcutsq;
+    a.n_frame = ctx->N;
+    a.max_rcut = ctx->max_rcut;
     a.nq = ctx->nq;
     a.qag_epsabs = ctx->qag_epsabs;
     a.qag_epsrel = ctx->qag_epsrel;
@@ -908,6 +983,12 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
         ctx->ik_variant = l;
         return PGT_OK;
     }
+    if (!strcmp(name, "slab_cull")) {
+        ctx->slab_cull = value != 0.0;
+        ctx->cells_built = false;
+        ctx->bonds_built = false;
+        return PGT_OK;
+    }
     if (!strcmp(name, "bond_fill_flat")) {
         ctx->bond_fill_flat = value != 0.0;
         ctx->bonds_built = false;
@@ -945,7 +1026,7 @@ static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
     if (rc == -2) return fail(ctx, PGT_ERR_ARG, "unknown field %d", field_id);
     if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
     CK(cudaSetDevice(ctx->device));
-    const long long gl = ctx->g1 - ctx->g0;
+    const long long gl = ctx->field_g1 - ctx->field_g0;   // the shard the field was computed for
     if (wait) {
         stage_begin(ctx, PGT_STAGE_DOWNLOAD);
         if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->stream));
@@ -973,7 +1054,7 @@ int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out)
     if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
     if (nc != 4) return fail(ctx, PGT_ERR_ARG, "field %d is not a 2x2 tensor field", field_id);
     CK(cudaSetDevice(ctx->device));
-    const long long gl = ctx->g1 - ctx->g0;
+    const long long gl = ctx->field_g1 - ctx->field_g0;   // the shard the field was computed for
     if (ctx->dl_pending) CK(cudaStreamSynchronize(ctx->dl_stream));      // the pack buffer is still being read back
     ENSURE(ctx->pack, sizeof(double) * 3 * (size_t)std::max<long long>(gl, 1));
     CK(cudaEventRecord(ctx->ev_field_ready, ctx->stream));
@@ -1004,7 +1085,7 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
     if (rc == -2) return fail(ctx, PGT_ERR_ARG, "unknown field %d", field_id);
     if (rc == -1) return fail(ctx, PGT_ERR_STATE, "field %d was not computed by the last pgt_ik_compute", field_id);
     *d_ptr = b->p;
-    if (n_doubles) *n_doubles = (int64_t)nc * (ctx->g1 - ctx->g0);
+    if (n_doubles) *n_doubles = (int64_t)nc * (ctx->field_g1 - ctx->field_g0);
     return PGT_OK;
 }
 
@@ -1013,13 +1094,16 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: no pair potential");
+    if (ctx->culled) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: the frame holds a grid shard's particles only (set the whole grid or option slab_cull = 0 and rebuild the cells)");
     CK(cudaSetDevice(ctx->device));
     const int blocks = pgt_thermo_blocks(ctx->n_live);
+    const int p_begin = (int)((long long)ctx->n_live * ctx->thermo_part / ctx->thermo_nparts);
+    const int p_end = (int)((long long)ctx->n_live * (ctx->thermo_part + 1) / ctx->thermo_nparts);
     ENSURE(ctx->thermo_partials, sizeof(double) * 25 * (size_t)blocks);
     ENSURE(ctx->thermo_out, sizeof(double) * 32);
     stage_begin(ctx, PGT_STAGE_THERMO);
     pgt_launch_thermo(ctx->pot, frame_view(ctx), ctx->box, ctx->cells, ctx->max_rcut, obs_mask, 1 / ctx->vol,
-                      ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), ctx->stream, &ctx->launches);
+                      ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), p_begin, p_end, ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     stage_end(ctx, PGT_STAGE_THERMO);
     pgt_launch_publish(ctx->thermo_out.p, 50, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
@@ -1316,7 +1400,11 @@ int pgt_comm_allgather_field(pgt_ctx* ctx, int field_id, const int64_t* counts, 
     int nc;
     int rc = field_info(ctx, field_id, &b, &nc);
     if (rc != 0) return fail(ctx, PGT_ERR_STATE, "field %d not available", field_id);
+    if (counts[ctx->rank] != (int64_t)nc * (ctx->field_g1 - ctx->field_g0))
+        return fail(ctx, PGT_ERR_ARG, "pgt_comm_allgather_field: counts[%d] = %lld, the local field holds %lld doubles", ctx->rank,
+                    (long long)counts[ctx->rank], (long long)nc * (ctx->field_g1 - ctx->field_g0));
     CK(cudaSetDevice(ctx->device));
+    if (ctx->dl_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_dl_done, 0));   // a read-back of this field may still be in flight
     // variable-size all-gather = one broadcast per rank inside a group (NVLink / NVSwitch transport)
     const int ncclDouble = 8;
     int nrc = g_nccl.GroupStart();
@@ -1329,6 +1417,35 @@ int pgt_comm_allgather_field(pgt_ctx* ctx, int field_id, const int64_t* counts, 
     }
     int nrc2 = g_nccl.GroupEnd();
     if (nrc != 0 || nrc2 != 0) return fail(ctx, PGT_ERR_NCCL, "ncclBroadcast group: %s", g_nccl.GetErrorString(nrc ? nrc : nrc2));
+    return PGT_OK;
+}
+
+int pgt_comm_allgather_frame(pgt_ctx* ctx)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (!ctx->comm) return fail(ctx, PGT_ERR_STATE, "pgt_comm_allgather_frame: communicator not initialised");
+    if (!ctx->have_frame || ctx->part_chunk <= 0) return fail(ctx, PGT_ERR_STATE, "pgt_comm_allgather_frame: no frame part uploaded (pgt_frame_upload_part)");
+    CK(cudaSetDevice(ctx->device));
+    const size_t es = ctx->is_f32 ? 4 : 8;
+    const int dtype = ctx->is_f32 ? 7 /* ncclFloat32 */ : 8 /* ncclFloat64 */;
+    const size_t chunk = (size_t)ctx->part_chunk;
+    char* pos = static_cast<char*>(ctx->raw_pos.p);
+    char* diam = static_cast<char*>(ctx->raw_diam.p);
+    // in place: this rank's part already sits at its offset of the receive buffer
+    int nrc = g_nccl.GroupStart();
+    if (nrc == 0) nrc = g_nccl.AllGather(pos + (size_t)ctx->rank * chunk * 3 * es, pos, chunk * 3, dtype, ctx->comm, ctx->stream);
+    if (nrc == 0) nrc = g_nccl.AllGather(diam + (size_t)ctx->rank * chunk * es, diam, chunk, dtype, ctx->comm, ctx->stream);
+    const int nrc2 = g_nccl.GroupEnd();
+    if (nrc != 0 || nrc2 != 0) return fail(ctx, PGT_ERR_NCCL, "ncclAllGather: %s", g_nccl.GetErrorString(nrc ? nrc : nrc2));
+    return PGT_OK;
+}
+
+int pgt_thermo_set_shard(pgt_ctx* ctx, int part, int nparts)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (nparts < 1 || part < 0 || part >= nparts) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_set_shard: part %d of %d", part, nparts);
+    ctx->thermo_part = part;
+    ctx->thermo_nparts = nparts;
     return PGT_OK;
 }
 

@@ -660,7 +660,7 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
         cudaDeviceGetAttribute(&smem_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, dev);
         cudaDeviceGetAttribute(&smem_cta, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     }
-    static int want_wx = -1, want_wy = 0, margin_pct = 10, want_list = 0, want_ctas = 0;
+    static int want_wx = -1, want_wy = 0, margin_pct = 10, want_list = 0, want_ctas = 0, slack_pct = 5;
     if (want_wx < 0) {
         const char* e = getenv("PGT_IKQ_TILE");              // "wx,wy"
         want_wx = 0;
@@ -668,10 +668,17 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
         if ((e = getenv("PGT_IKQ_MARGIN"))) margin_pct = atoi(e);
         if ((e = getenv("PGT_IKQ_LIST"))) want_list = atoi(e);
         if ((e = getenv("PGT_IKQ_CTAS"))) want_ctas = atoi(e);
+        if ((e = getenv("PGT_IKQ_SLACK"))) slack_pct = atoi(e);
     }
     const double R = a.cg.rcut, cwx = 1.0 / a.cells.inv_cwx, cwy = 1.0 / a.cells.inv_cwy;
-    const double rho = (double)a.fr.n / (a.box.L[0] * a.box.L[1]);
-    const double hb = a.fr.n_hb > 0 ? (double)a.fr.n_hb / (double)a.fr.n : 1.0;
+    // Every capacity below comes from quantities that do not depend on the grid shard -- the frame's particle count as
+    // uploaded, the box, the cell geometry, the grid's tile extents -- never from the particles or bonds a slab-culled
+    // frame happens to hold: a point's summation order (its rounds, its path) must be the same on 1 GPU and on 8.
+    const double rho = (double)std::max<long long>(a.n_frame, 1) / (a.box.L[0] * a.box.L[1]);
+    // half-bonds per particle, estimated: a share of the neighbours within max_rcut (0.29 on polydisperse liquids: the
+    // pair cut-off scales with the pair's diameters, the search radius with the largest); it sizes the lists only,
+    // the record store takes whatever shared memory is left
+    const double hb = std::max(1.0, 0.29 * rho * M_PI * a.max_rcut * a.max_rcut);
     const double m = 1.0 + 0.01 * margin_pct;
     static const int shapes[][2] = { { 4, 2 }, { 2, 4 }, { 2, 2 }, { 1, 2 }, { 1, 1 } };   // equal threads: the first listed wins (fewer, longer cell rows)
     const int reg_threads = 65536 / 128;                       // __launch_bounds__(256, 2): at most 128 registers per thread
@@ -695,31 +702,39 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
         const int lcs_stride = cols + 1;
         const double ep = rho * (sx + 2.0 * R + 2.0 * cwx) * (sy + 2.0 * R + 2.0 * cwy);
         const long long nloc = ((long long)(ep * m + 32.0) + 7) & ~7LL;
-        const long long nrec = ((long long)(ep * hb * m + 64.0) + 7) & ~7LL;
-        if (nloc > 0x7FFF || nrec > IKQ_MAX_NREC) continue;
-        // records 32 B + owner 2 B; position 16 B + 8 B (single precision), range 4 B per particle; local cell starts
-        const long long base = nrec * 34 + nloc * 28 + (long long)rows_cap * lcs_stride * 2 + 64;
+        const long long nrec_want = ((long long)(ep * hb * m + 64.0) + 7) & ~7LL;    // records of a rectangle, with margin
+        const long long nrec_need = ((long long)(ep * hb * 1.05 + 32.0) + 7) & ~7LL;  // fewer than this: tiles would overflow
+        if (nloc > 0x7FFF) continue;
+        const long long lc_top = want_list > 0 ? std::min(254, std::max(want_list, buf_min)) & ~1 : buf_want;
         const long long stat = (long long)sizeof(IKQStatic) + 16 + IKQ_MAX_THREADS + 1024;   // static part + the per-CTA reservation
         const int max_ctas = std::max(1, std::min(reg_threads / T, 16));
-        for (int ctas = (want_ctas > 0 ? std::min(want_ctas, max_ctas) : max_ctas); ctas >= 1; --ctas) {
-            const long long avail = std::min<long long>(smem_sm / ctas, smem_cta) - stat - base;
-            long long lc = avail / (2LL * T) - 2;              // the stride is rounded up to 2 x odd
-            if (lc < buf_min) continue;
-            lc = std::min<long long>(std::min<long long>(lc, want_list > 0 ? std::max(want_list, buf_min) : buf_want), 254) & ~1LL;
-            const long long score = (long long)ctas * T;               // threads per SM; ties: the shape listed first
-            if (score > best_score) {
-                best_score = score;
-                best_mt = std::max(sx, sy) + R + 2.0 * std::max(cwx, cwy);
-                caps->wx = wx; caps->wy = wy; caps->wy_log2 = wy == 4 ? 2 : (wy == 2 ? 1 : 0);
-                caps->rows_cap = rows_cap;
-                caps->lcs_stride = lcs_stride;
-                caps->nloc_cap = (int)nloc;
-                caps->nrec_cap = (int)nrec;
-                caps->buf_cap = (int)lc;
-                caps->buf_stride = (int)(((lc / 2) | 1) * 2);              // lc is even: the next 2 x odd, lc or lc + 2
-                *dyn_bytes = (size_t)(base + (long long)caps->buf_stride * 2 * T + 15) & ~(size_t)15;
+        bool placed = false;
+        for (int ctas = (want_ctas > 0 ? std::min(want_ctas, max_ctas) : max_ctas); ctas >= 1 && !placed; --ctas) {
+            // the longest per-thread buffer (down to 8 entries below the wish) that leaves room for the records
+            for (long long lc = lc_top; lc >= std::max<long long>(buf_min, lc_top - 8) && !placed; lc -= 2) {
+                const long long stride = ((lc / 2) | 1) * 2;   // lc is even: the next 2 x odd, lc or lc + 2
+                // position 16 B + 8 B (single precision), range 4 B per particle; local cell starts; the threads' buffers
+                const long long base = nloc * 28 + (long long)rows_cap * lcs_stride * 2 + stride * 2 * T + 64;
+                // records 32 B + owner 2 B: the shared memory that is left, up to a slack over the wish (the rest stays L1)
+                const long long avail = std::min<long long>(smem_sm / ctas, smem_cta) - stat - base - 16;
+                const long long nrec = std::min<long long>(std::min<long long>((avail / 34) & ~7LL, IKQ_MAX_NREC & ~7),
+                                                          (nrec_want * (100 + slack_pct) / 100 + 7) & ~7LL);
+                if (nrec < nrec_need) continue;
+                placed = true;
+                const long long score = (long long)ctas * T;           // threads per SM; ties: the shape listed first
+                if (score > best_score) {
+                    best_score = score;
+                    best_mt = std::max(sx, sy) + R + 2.0 * std::max(cwx, cwy);
+                    caps->wx = wx; caps->wy = wy; caps->wy_log2 = wy == 4 ? 2 : (wy == 2 ? 1 : 0);
+                    caps->rows_cap = rows_cap;
+                    caps->lcs_stride = lcs_stride;
+                    caps->nloc_cap = (int)nloc;
+                    caps->nrec_cap = (int)nrec;
+                    caps->buf_cap = (int)lc;
+                    caps->buf_stride = (int)stride;
+                    *dyn_bytes = (size_t)(base + nrec * 34 + 15) & ~(size_t)15;
+                }
             }
-            break;
         }
     }
     if (best_score < 0) return false;

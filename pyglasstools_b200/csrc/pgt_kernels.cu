@@ -64,31 +64,43 @@ __device__ __forceinline__ bool load_wrapped(const void* pos, long long i, const
 }
 
 // ------------------------------------------------------------------------------------------
-// Stage 0/1a: promote + wrap + cell key + histogram
+// Stage 0/1a: promote + wrap + cell key + histogram.  With a slab (grid-point sharding over GPUs: this rank owns a range
+// of grid columns) a particle whose wrapped x lies outside [slab_lo, slab_hi] under every periodic image is dropped here,
+// exactly like a particle outside the z slab, so that the cell list, the bond list and the gather's staging shrink with
+// the shard.  The slab already includes everything the shard's tiles can reach (pgt_build_cells).
 template <bool F32>
 __global__ void __launch_bounds__(256) k_wrap_count(const void* __restrict__ pos, long long N, PgtBox box, PgtCells cells,
-                                                    int* __restrict__ cell_of, int* __restrict__ cell_count, int* eflags)
+                                                    int* __restrict__ cell_of, int* __restrict__ cell_count, int* eflags,
+                                                    int slab_on, double slab_lo, double slab_hi)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     double x, y;
     int c = -1;
     if (load_wrapped<F32>(pos, i, box, x, y, eflags)) {
-        const int cx = cell_coord(x, box.lo[0], cells.inv_cwx, cells.ncx);
-        const int cy = cell_coord(y, box.lo[1], cells.inv_cwy, cells.ncy);
-        c = cy * cells.ncx + cx;
-        atomicAdd(&cell_count[c], 1);
+        bool keep = true;
+        if (slab_on) {
+            const double xm = x - box.L[0], xp = x + box.L[0];
+            keep = (x >= slab_lo && x <= slab_hi) || (xm >= slab_lo && xm <= slab_hi) || (xp >= slab_lo && xp <= slab_hi);
+        }
+        if (keep) {
+            const int cx = cell_coord(x, box.lo[0], cells.inv_cwx, cells.ncx);
+            const int cy = cell_coord(y, box.lo[1], cells.inv_cwy, cells.ncy);
+            c = cy * cells.ncx + cx;
+            atomicAdd(&cell_count[c], 1);
+        }
     }
     cell_of[i] = c;
 }
 
 void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
-                           int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc)
+                           int* cell_count, int* eflags, int slab_on, double slab_lo, double slab_hi, cudaStream_t st,
+                           PgtLaunchCounter* lc)
 {
     if (N <= 0) return;
     const int blocks = (int)((N + 255) / 256);
-    if (is_f32) k_wrap_count<true><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags);
-    else k_wrap_count<false><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags);
+    if (is_f32) k_wrap_count<true><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags, slab_on, slab_lo, slab_hi);
+    else k_wrap_count<false><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags, slab_on, slab_lo, slab_hi);
     lc->n++;
 }
 
@@ -647,14 +659,15 @@ __device__ __forceinline__ double warp_sum(double v)
 
 template <int MODEL>
 __global__ void __launch_bounds__(THERMO_THREADS) k_thermo_pairs(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
-                                                                 unsigned obs_mask, double* __restrict__ partials)
+                                                                 unsigned obs_mask, double* __restrict__ partials, int p_begin, int p_end)
 {
     __shared__ double red[THERMO_THREADS / 32][THERMO_NVAL];
     double acc[THERMO_NVAL];
 #pragma unroll
     for (int k = 0; k < THERMO_NVAL; ++k) acc[k] = 0.0;
 
-    for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < fr.n; p += gridDim.x * blockDim.x) {
+    // [p_begin, p_end): this rank's share of the sorted particles (pgt_thermo_set_shard; the whole frame by default)
+    for (int p = p_begin + blockIdx.x * blockDim.x + threadIdx.x; p < p_end; p += gridDim.x * blockDim.x) {
         const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
         const int oi = fr.sorig[p];
         if ((obs_mask & PGT_OBS_KINETIC) && fr.skxx) {
@@ -720,18 +733,19 @@ int pgt_thermo_blocks(int n)
 
 template <int MODEL>
 static void launch_thermo_model(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2, unsigned obs_mask,
-                                double* partials, int blocks, cudaStream_t st)
+                                double* partials, int blocks, int p_begin, int p_end, cudaStream_t st)
 {
-    k_thermo_pairs<MODEL><<<blocks, THERMO_THREADS, 0, st>>>(pot, fr, box, cells, rc2, obs_mask, partials);
+    k_thermo_pairs<MODEL><<<blocks, THERMO_THREADS, 0, st>>>(pot, fr, box, cells, rc2, obs_mask, partials, p_begin, p_end);
 }
 
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
-                       double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc)
+                       double inv_vol, double* partials, int max_blocks, double* out_dev, int p_begin, int p_end, cudaStream_t st,
+                       PgtLaunchCounter* lc)
 {
     int blocks = pgt_thermo_blocks(fr.n);
     if (blocks > max_blocks) blocks = max_blocks;
     const double rc2 = max_rcut * max_rcut;
-    PGT_DISPATCH_MODEL(pot.model, (launch_thermo_model<M>(pot, fr, box, cells, rc2, obs_mask, partials, blocks, st)));
+    PGT_DISPATCH_MODEL(pot.model, (launch_thermo_model<M>(pot, fr, box, cells, rc2, obs_mask, partials, blocks, p_begin, p_end, st)));
     k_thermo_final<<<1, 32 * THERMO_NVAL, 0, st>>>(partials, blocks, inv_vol, out_dev);
     lc->n += 2;
 }

@@ -78,6 +78,8 @@ struct PgtIKArgs {
     PgtCells cells;
     PgtCG cg;
     double inv_rcutsq;           // 1 / R^2
+    long long n_frame;           // particles of the frame as uploaded (before any kill or slab cull): sizes shard-independent capacities
+    double max_rcut;             // the frozen neighbour-search radius
     int nq;                      // quadrature nodes (generic path)
     // 5-point rule in symmetric form on [0,1]: nodes 0.5 +- h_k, weights w_k (already times (b-a)/2)
     double gl5_h1, gl5_h1sq, gl5_h2, gl5_h2sq, gl5_w0, gl5_w1, gl5_w2;
@@ -97,8 +99,10 @@ struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 
 // ---- launch wrappers (defined in pgt_kernels.cu) ---------------------------------------------
 struct PgtLaunchCounter { long long n; };
 
+// slab_on: drop particles whose wrapped x lies outside [slab_lo, slab_hi] under every periodic image (grid-point sharding)
 void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
-                           int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
+                           int* cell_count, int* eflags, int slab_on, double slab_lo, double slab_hi, cudaStream_t st,
+                           PgtLaunchCounter* lc);
 void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* block_sums, cudaStream_t st, PgtLaunchCounter* lc);
 long long pgt_scan_scratch_ints(long long n);
 void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_start, int* cell_fill, int* sorted_orig,
@@ -122,8 +126,10 @@ void pgt_launch_rescale_bonds(const double2* hb_b, double2* hb_cf, long long n_h
 cudaError_t pgt_launch_ik(const PgtIKArgs& a, int variant, cudaStream_t st, PgtLaunchCounter* lc);
 // virial field with the adaptive (QAG, 15-point Gauss-Kronrod) bond quadrature; failures are OR-ed into *eflags
 cudaError_t pgt_launch_ik_adaptive(const PgtIKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
+// [p_begin, p_end): the sorted particles whose pairs (orig_i < orig_j, visited from i) this launch sums
 void pgt_launch_thermo(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, unsigned obs_mask,
-                       double inv_vol, double* partials, int max_blocks, double* out_dev, cudaStream_t st, PgtLaunchCounter* lc);
+                       double inv_vol, double* partials, int max_blocks, double* out_dev, int p_begin, int p_end, cudaStream_t st,
+                       PgtLaunchCounter* lc);
 int pgt_thermo_blocks(int n);
 // ElasticVirialStress (needs per-particle displacements, rows of the original particle order): global sum and field
 void pgt_launch_thermo_elastic(const PgtPot& pot, PgtFrameView fr, PgtBox box, PgtCells cells, double max_rcut, const double* disp,
