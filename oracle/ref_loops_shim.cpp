@@ -231,7 +231,9 @@ int ref_ik_compute(const double* box, int64_t n, const double* pos, const double
     for (int64_t g = 0; g < G; ++g)
         for (int q = 0; q < 4; ++q) {
             if (fv && virial) virial[4 * g + q] = fv->val[g].data()[q];
-            if (fk && kinetic) kinetic[4 * g + q] = fk->val[g].data()[q];
+            // LocalField never sizes its tensors (CoarseGrainedField.h:58-64: resize of the vector only), so the reference's
+            // kinetic field is a list of EMPTY tensors; nothing to read then
+            if (fk && kinetic && fk->val[g].size() == 4) kinetic[4 * g + q] = fk->val[g].data()[q];
             if (fe && elastic) elastic[4 * g + q] = fe->val[g].data()[q];
         }
     return 0;
