@@ -381,10 +381,11 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="cfg5", choices=sorted(WORKLOADS))
-    ap.add_argument("--e2e-field", default="auto", choices=("auto", "full", "sym"),
+    ap.add_argument("--e2e-field", default="sym", choices=("auto", "full", "sym"),
                     help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy); auto: full on one GPU, sym on several (the host's PCIe / memory path is shared)")
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
-    ap.add_argument("--e2e-lanes", type=int, default=3, choices=(1, 2, 3, 4), help="contexts (streams) the end-to-end trajectory loop is pipelined over")
+    ap.add_argument("--e2e-lanes", type=int, default=1, choices=(1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over; 1 (default): one context pipelines upload / stages / read-back on its own three streams")
+    ap.add_argument("--e2e-buffers", type=int, default=3, choices=(2, 3, 4), help="host field buffers the single-context loop reads back into in turn")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -403,7 +404,7 @@ def main():
     if args.shard == "grid" and world == 1:
         args.shard = "frames"
     if args.e2e_field == "auto":
-        args.e2e_field = "full" if world == 1 else "sym"
+        args.e2e_field = "sym"
 
     import torch
     import torch.distributed as dist
@@ -485,6 +486,9 @@ def main():
         for _ in range(nlanes - 1):
             cb = setup_ctx(_capi, synth, local_rank, wl, dmax, L)
             cb.set_shard(*shard)
+            # several contexts: each stage waits for its count, which keeps the kernels of different frames from
+            # co-running on the device (measured: 2.46 against 2.58 ms per frame at cfg5 with deferred counts)
+            cb.set_option("async_counts", 0)
             lanes.append((cb, _capi.PinnedArray((shard[1] - shard[0], ncomp_out), np.float64)))
         return lanes
 
@@ -514,22 +518,68 @@ def main():
         barrier()
         c.sync()
         l0 = c.launches()
-        st = {"cells": [], "bonds": []}
         t0 = time.time()
         c.event_record(0)
-        for s in range(steps):
+        for s in range(steps):                     # no host synchronisation inside: the frames' counts are deferred
             step_resident(c, s % pool)
-            # build_cells/build_bonds synchronise the stream, so the previous stages' events are complete
-            st["cells"].append(c.stage_ms("cells"))
-            st["bonds"].append(c.stage_ms("bonds"))
         c.event_record(1)
         c.sync()
         barrier()
         t1 = time.time()
-        return max_over_ranks(c.event_elapsed_ms(0, 1)), c.launches() - l0, st, (t0, t1)
+        ms = max_over_ranks(c.event_elapsed_ms(0, 1))
+        nl = c.launches() - l0
+        # per-stage device times, read in a separate pass so that waiting for the events does not perturb the loop above
+        st = {"cells": [], "bonds": [], "ik": []}
+        for s in range(min(steps, 30)):
+            step_resident(c, s % pool)
+            for k in st:
+                st[k].append(c.stage_ms(k))
+        return ms, nl, st, (t0, t1)
+
+    def run_pipelined(c, outs, steps, parts):
+        """The trajectory loop in ONE context and one host thread: frame s+1 is uploaded (upload stream) while frame s is
+        computed (main stream, counts deferred: no host wait between stages) and frame s-1 is read back (read-back stream)
+        into one of a few host buffers used in turn; the host only waits for the oldest read-back in flight."""
+        def up(s):
+            k = s % pool
+            if parts:
+                c.upload_part(pin_pos[k].array[p_first:p_last], pin_diam[k].array[p_first:p_last], p_first, N, box)
+            else:
+                c.upload(pin_pos[k].array, pin_diam[k].array, box)
+        up(0)
+        for s in range(steps):
+            if parts:
+                c.comm_allgather_frame()
+            c.build_cells()
+            c.build_bonds()
+            c.ik_compute(_capi.OBS_VIRIAL)
+            if s + 1 < steps:
+                up(s + 1)
+            if args.e2e_field == "sym":
+                c.ik_download_sym_async(_capi.FIELD_VIRIAL, outs[s % len(outs)].array)
+            else:
+                c.ik_download_async(_capi.FIELD_VIRIAL, outs[s % len(outs)].array)
+            c.ik_download_wait_keep(len(outs) - 1)   # the oldest of the host buffers has landed (consumed here)
+        c.ik_download_wait()
 
     def time_e2e(lanes, steps, warm, parts, threads):
         nl = len(lanes)
+        if nl == 1:
+            c = lanes[0][0]
+            outs = [lanes[0][1]] + [_capi.PinnedArray(lanes[0][1].array.shape, np.float64) for _ in range(args.e2e_buffers - 1)]
+            run_pipelined(c, outs, max(warm, 4), parts)
+            c.sync()
+            barrier()
+            t0 = time.time()
+            c.event_record(2)
+            run_pipelined(c, outs, steps, parts)
+            c.event_record(3)
+            c.sync()
+            barrier()
+            t1 = time.time()
+            for o in outs[1:]:
+                lanes.append((c, o))               # every buffer takes part in the read-back check
+            return max_over_ranks(c.event_elapsed_ms(2, 3)), (t0, t1)
         for s in range(max(warm, 3)):
             step_e2e(lanes, s, s % pool, parts)
         for c, _ in lanes:
@@ -591,9 +641,22 @@ def main():
     lanes = make_lanes(ctx, args.e2e_lanes, my_shard)
     if grid_mode:
         comm_init_all([c for c, _ in lanes])
+    if len(lanes) > 1:
+        ctx.set_option("async_counts", 0)
     ms_e2e, win_b = time_e2e(lanes, args.steps, args.warmup, grid_mode, args.e2e_threads)
+    ctx.set_option("async_counts", 1)
     e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
     assert np.isfinite(e2e_check) and e2e_check > 0
+    # for comparison, the round-1 arrangement: three contexts, one host thread each, every stage waiting for its count
+    e2e_alt = None
+    if len(lanes) == 1 + (args.e2e_buffers - 1) and args.e2e_lanes == 1 and not grid_mode and world == 1:
+        alt = make_lanes(ctx, 3, my_shard)
+        ctx.set_option("async_counts", 0)
+        ms_alt, _ = time_e2e(alt, args.steps, args.warmup, False, 2)
+        ctx.set_option("async_counts", 1)
+        e2e_alt = ms_alt / args.steps
+        for c, _ in alt[1:]:
+            c.close()
 
     # ---- N > 1: one frame split over the ranks by grid points (the reference's MPI decomposition), strong scaling
     grid_shard = None
@@ -615,7 +678,7 @@ def main():
             full_ref = ctx.ik_download()
         ctx.set_shard(*shards[rank])
         ms_g, launches_g, stage_g, _ = time_resident(ctx, gsteps, args.warmup)
-        glanes = make_lanes(ctx, min(args.e2e_lanes, 2), shards[rank])
+        glanes = make_lanes(ctx, 1, shards[rank])
         comm_init_all([c for c, _ in glanes])
         ms_ge, _ = time_e2e(glanes, gsteps, args.warmup, True, 1)
         # the NCCL legs alone: frame all-gather, field all-gather
@@ -642,18 +705,19 @@ def main():
         check = None
         if rank == 0:
             check = "bitwise" if np.array_equal(gathered.cpu().numpy(), full_ref) else "MISMATCH"
+        step_resident(ctx, 0)
         kept = ctx.counts()["n_live"]
         t1_ms = ms_resident / args.steps                     # this run's single-GPU step on the same workload
         grid_shard = {
             "what": "ONE frame per step, its %d grid points split over %d GPUs at np.array_split boundaries (irvingkirkwood/__init__.py:53-60); every rank builds slab-local cell and bond lists" % (G, world),
             "value": G * gsteps / (ms_g * 1e-3), "unit": UNIT, "ms_per_step": ms_g / gsteps, "scaling": "strong",
             "efficiency_vs_n1": (t1_ms / (ms_g / gsteps)) / world,
-            "stage_ms": {"cells": float(np.mean(stage_g["cells"])), "bonds": float(np.mean(stage_g["bonds"])), "ik": ctx.stage_ms("ik")},
+            "stage_ms": {k: float(np.mean(v)) for k, v in stage_g.items()},
             "particles_kept_rank0": kept, "particles_total": N,
             "e2e": {"value": G * gsteps / (ms_ge * 1e-3), "unit": UNIT, "ms_per_step": ms_ge / gsteps,
                     "h2d_bytes_per_step": (p_last - p_first) * 16, "d2h_bytes_per_step": (shards[rank][1] - shards[rank][0]) * ncomp_out * 8,
                     "efficiency_vs_n1_e2e": ((ms_e2e / args.steps) / (ms_ge / gsteps)) / world,
-                    "api": "pgt_frame_upload_part (1/%d of the frame over PCIe) + pgt_comm_allgather_frame (ncclAllGather over NVLink) .. pgt_ik_download_%sasync of the rank's own shard, %d contexts, one host thread" % (world, "sym_" if ncomp_out == 3 else "", len(glanes))},
+                    "api": "pgt_frame_upload_part (1/%d of the frame over PCIe) + pgt_comm_allgather_frame (ncclAllGather over NVLink) .. pgt_ik_download_%sasync of the rank's own shard; one context, one host thread" % (world, "sym_" if ncomp_out == 3 else "")},
             "collective": "ncclAllGather (frame parts, %.1f MB per rank -> %.1f MB) inside the timed e2e region; ncclBroadcast group (final field gather, %.0f MB) timed separately" % ((p_last - p_first) * 16 / 1e6, N * 16 / 1e6, G * 32 / 1e6),
             "nccl_ms": {"allgather_frame": nccl_frame_ms, "allgather_field": nccl_field_ms},
             "gather_check": check, "steps": gsteps,
@@ -706,7 +770,11 @@ def main():
             "config": config_dict(args, wl, world, pool),
             "clocks": sampler.summary([win_a, win_b]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers, frames pipelined over %d contexts, %s" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread")},
+                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers; %s" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", "one context (upload, compute and read-back streams), one host thread, counts deferred" if args.e2e_lanes == 1 else "frames spread over %d contexts, %s" % (args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread"))},
+            "e2e_three_contexts": None if e2e_alt is None else {
+                "value": G / (e2e_alt * 1e-3), "unit": UNIT, "ms_per_step": e2e_alt,
+                "api": "round-1 arrangement for comparison: three contexts, one host thread each, every stage waits for its count"},
+            "e2e_link": "both end-to-end figures are bound by the host link: %.0f MB per frame cross PCIe (H2D %.0f + D2H %.0f); alone the directions run at ~55 / ~57 GB/s (tools/copy_rates.py), with both busy this VM sustains ~65-70 GB/s in total" % ((h2d + d2h) / 1e6, h2d / 1e6, d2h / 1e6),
             "gpu_launches": launches_total,
             "stage_ms": {"cells": cells_ms, "bonds": bonds_ms, "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_quad", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",

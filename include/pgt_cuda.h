@@ -129,6 +129,12 @@ int pgt_ik_download_async(pgt_ctx* ctx, int field_id, double* out);
 int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out);
 /* Waits for the read-backs enqueued by pgt_ik_download_async only (not for kernels of later frames).        */
 int pgt_ik_download_wait(pgt_ctx* ctx);
+/* Waits until at most `keep` (0..3) of the asynchronous read-backs enqueued so far are still in flight.  With keep + 1
+ * host buffers used in turn the caller consumes frame s - keep while later frames are on the device and frame s + 1 is
+ * being uploaded -- one context, one host thread, the trajectory loop of pyglasstools.analyze fully pipelined (uploads,
+ * stages and read-backs run on three streams of the context; frames whose counts are deferred never make the host wait
+ * in between).                                                                                                       */
+int pgt_ik_download_wait_keep(pgt_ctx* ctx, int keep);
 /* Device pointer of a field of the local shard (for NCCL / zero-copy consumers).               */
 int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubles);
 /* Stage 6.  Replaces ThermoCalculator::compute + divideByVolume (thermo/ThermoCalculator.h:58-90).
@@ -183,6 +189,9 @@ int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
 int pgt_host_alloc(void** ptr, uint64_t bytes);
 int pgt_host_free(void* ptr);
 /* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 7 quad gather where it applies);
+ * "async_counts" (1 default: a frame of the same shape as the last one counted sizes its arrays from that frame's particle
+ *   and half-bond counts plus a margin and does not wait for its own; counts and errors reach the host at the next
+ *   pgt_synchronize / pgt_ik_download / pgt_ik_download_wait / pgt_frame_counts; 0: every stage waits for its count);
  * "slab_cull" (1 default: a grid shard restricts stages 1-3 to the particles it can reach, 0: every rank builds the whole frame);
  * "bond_single_search" (1 default: one neighbour search per frame, 0: separate count and fill searches);
  * "bond_fill_flat" (1 default: warp-flattened record writer, 0: thread per particle).  Every setting gives the same

@@ -27,7 +27,7 @@ EXPORTED = [
     "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
-    "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard",
+    "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep",
 ]
 
 _lib = None
@@ -124,6 +124,7 @@ def lib():
                                             C.POINTER(C.c_double), C.c_int]
         L.pgt_comm_allgather_frame.argtypes = [C.c_void_p]
         L.pgt_thermo_set_shard.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        L.pgt_ik_download_wait_keep.argtypes = [C.c_void_p, C.c_int]
         _lib = L
     return _lib
 
@@ -263,6 +264,10 @@ class Context:
 
     def ik_download_wait(self):
         self._ck(lib().pgt_ik_download_wait(self._h))
+
+    def ik_download_wait_keep(self, keep):
+        """Waits until at most `keep` asynchronous read-backs are still in flight."""
+        self._ck(lib().pgt_ik_download_wait_keep(self._h, int(keep)))
 
     def ik_device_ptr(self, field=FIELD_VIRIAL):
         p, n = C.c_void_p(), C.c_int64()

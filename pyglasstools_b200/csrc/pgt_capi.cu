@@ -113,7 +113,9 @@ struct pgt_ctx {
     cudaStream_t stream = nullptr;
     cudaStream_t dl_stream = nullptr;      // read-backs issued by pgt_ik_download_async (overlap the next upload)
     cudaEvent_t ev_field_ready = nullptr;  // main stream: the field of the last gather is complete
-    cudaEvent_t ev_dl_done = nullptr;      // dl_stream: the last asynchronous read-back is complete
+    cudaEvent_t ev_dl_copy[4] = { nullptr, nullptr, nullptr, nullptr };   // dl_stream: the last four asynchronous read-backs have landed in host memory
+    long long dl_seq = 0, dl_waited = 0;   // read-backs enqueued / known to have landed
+    cudaEvent_t ev_dl_done = nullptr;      // dl_stream: the last asynchronous read-back no longer reads the field buffers
     bool dl_pending = false;
     std::string err;
     PgtLaunchCounter launches{ 0 };
@@ -136,7 +138,15 @@ struct pgt_ctx {
     PgtBox box{};
     double vol = 0.0;
     const void *src_pos = nullptr, *src_diam = nullptr, *src_mass = nullptr, *src_vel = nullptr;
-    DevBuf raw_pos, raw_diam, raw_mass, raw_vel;
+    // positions and diameters are double-buffered and uploaded on their own stream: frame s+1 crosses PCIe while frame s
+    // is computed on the main stream -- one context pipelines a trajectory (kernels of different frames never co-run)
+    DevBuf raw_pos2[2], raw_diam2[2], raw_mass, raw_vel;
+    int raw_slot = 0;                 // buffer pair of the frame last uploaded
+    int raw_cur = -1;                 // buffer pair the current frame's stage 1 reads (-1: caller's device pointers)
+    int ul_wait_slot = -1;            // the main stream has yet to wait for this upload
+    cudaStream_t ul_stream = nullptr;
+    cudaEvent_t ev_ul_done[2] = { nullptr, nullptr }, ev_raw_free[2] = { nullptr, nullptr };
+    bool raw_free_valid[2] = { false, false };
     PgtCells cells{};
     int n_live = 0;
     long long n_hb = 0;
@@ -183,6 +193,17 @@ struct pgt_ctx {
     double slab_lo = 0.0, slab_hi = 0.0;
     int64_t part_chunk = 0;           // pgt_frame_upload_part: particles per rank part (0: whole-frame upload)
     int thermo_part = 0, thermo_nparts = 1;
+    // deferred counts (option "async_counts"): once a frame has been counted exactly, the following frames of the same
+    // shape size their arrays from its counts (with a margin) and do not wait for their own; the counts and any error
+    // reach the host at its next synchronisation point
+    bool async_counts = true;
+    bool counts_pending = false;      // n_live / n_hb below are bounds, the exact values sit in mapped memory
+    bool cells_deferred = false;      // this frame's cell stage did not wait
+    bool eflags_init = false;
+    int known_nlive = -1;             // exact counts of the last frame counted (or resolved)
+    long long known_nhb = -1;
+    long long known_sig[8] = { 0, 0, 0, 0, 0, 0, 0, 0 };   // the shape those counts belong to
+    long long hb_cap = 0;             // records the half-bond arrays hold
     long long field_g0 = 0, field_g1 = 0;   // the shard the fields in HBM were computed for (pgt_ik_compute)
     double span_x[4] = { -1, -1, -1, -1 }, span_y[4] = { -1, -1, -1, -1 };   // extents of the quad gather's grid tiles (cartesian grids)
 
@@ -245,10 +266,60 @@ int check_eflags(pgt_ctx* ctx, int flags)
     return PGT_OK;
 }
 
+// mapped slots of the stage counts (ints): [0] n_live, [1] cell-stage flags, [2] n_hb, [3] bond-stage flags, [4] sticky
+int* h_counts(const pgt_ctx* c) { return reinterpret_cast<int*>(c->h_small) + 512; }
+int* d_counts(const pgt_ctx* c) { return reinterpret_cast<int*>(c->d_small) + 512; }
+
+void frame_signature(const pgt_ctx* c, long long sig[8])
+{
+    sig[0] = c->N;
+    memcpy(&sig[1], &c->box.L[0], 8);
+    memcpy(&sig[2], &c->box.L[1], 8);
+    sig[3] = ((long long)c->cells.ncx << 32) | (unsigned)c->cells.ncy;
+    sig[4] = c->culled ? 1 : 0;
+    memcpy(&sig[5], &c->slab_lo, 8);
+    memcpy(&sig[6], &c->slab_hi, 8);
+    sig[7] = c->is_f32;
+}
+
+int sticky_error(pgt_ctx* ctx, int sticky)
+{
+    // the context falls back to exact counting until a frame has been counted again
+    ctx->known_nlive = -1;
+    ctx->known_nhb = -1;
+    cudaMemsetAsync(ctx->eflags.as<int>() + 2, 0, sizeof(int), ctx->stream);
+    h_counts(ctx)[4] = 0;
+    int rc = check_eflags(ctx, sticky);
+    if (rc != PGT_OK) return rc;
+    if (sticky & PGT_EFLAG_BOND_OVERFLOW)
+        return fail(ctx, PGT_ERR_DATA, "a particle has more than %d bonds in a frame whose counts were deferred: submit the frames since the last synchronisation again (the context counts exactly now)", PGT_NB_SLOTS);
+    return fail(ctx, PGT_ERR_DATA, "a frame's particle or bond count outgrew the previous frame's by more than the margin while its counts were deferred: submit the frames since the last synchronisation again (the context counts exactly now)");
+}
+
+// Exact counts on the host: waits for the stream when the last frame deferred them.
+int resolve_counts(pgt_ctx* ctx)
+{
+    if (!ctx->counts_pending) return PGT_OK;
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->counts_pending = false;
+    const int* h = h_counts(ctx);
+    if (h[4]) return sticky_error(ctx, h[4]);
+    ctx->n_live = h[0];
+    ctx->known_nlive = h[0];
+    if (ctx->bonds_built) { ctx->n_hb = h[2]; ctx->known_nhb = h[2]; }
+    return PGT_OK;
+}
+#define RESOLVE()                                   \
+    do {                                            \
+        int rc_ = resolve_counts(ctx);              \
+        if (rc_ != PGT_OK) return rc_;              \
+    } while (0)
+
 PgtFrameView frame_view(const pgt_ctx* c)
 {
     PgtFrameView v{};
     v.n = c->n_live;
+    v.n_dev = c->counts_pending ? c->cell_count.as<int>() + (size_t)c->cells.ncx * c->cells.ncy : nullptr;
     v.sx = c->sx.as<double>();
     v.sy = c->sy.as<double>();
     v.sxy = c->sxy.as<double2>();
@@ -315,14 +386,22 @@ int pgt_ctx_create(int device, pgt_ctx** out)
         return PGT_ERR_CUDA;
     }
     cudaStreamCreateWithFlags(&ctx->dl_stream, cudaStreamNonBlocking);
+    cudaStreamCreateWithFlags(&ctx->ul_stream, cudaStreamNonBlocking);
+    for (int k = 0; k < 2; ++k) {
+        cudaEventCreateWithFlags(&ctx->ev_ul_done[k], cudaEventDisableTiming);
+        cudaEventCreateWithFlags(&ctx->ev_raw_free[k], cudaEventDisableTiming);
+    }
     cudaEventCreateWithFlags(&ctx->ev_field_ready, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&ctx->ev_dl_done, cudaEventDisableTiming);
+    for (auto& e : ctx->ev_dl_copy) cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
     for (int s = 0; s < PGT_STAGE_COUNT; ++s) {
         cudaEventCreate(&ctx->ev0[s]);
         cudaEventCreate(&ctx->ev1[s]);
     }
     cudaHostAlloc((void**)&ctx->h_small, 4096, cudaHostAllocMapped);
     cudaHostGetDevicePointer(&ctx->d_small, ctx->h_small, 0);
+    if (ctx->h_small) memset(ctx->h_small, 0, 4096);
+    if (const char* env = getenv("PGT_ASYNC_COUNTS")) ctx->async_counts = atoi(env) != 0;
     if (const char* env = getenv("PGT_BOND_FILL_FLAT")) ctx->bond_fill_flat = atoi(env) != 0;
     if (const char* env = getenv("PGT_IK_VARIANT")) {
         int l = atoi(env);
@@ -337,8 +416,10 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     if (!ctx) return PGT_OK;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->ul_stream) cudaStreamSynchronize(ctx->ul_stream);
+    if (ctx->dl_stream) cudaStreamSynchronize(ctx->dl_stream);
     if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
-    DevBuf* bufs[] = { &ctx->raw_pos, &ctx->raw_diam, &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
+    DevBuf* bufs[] = { &ctx->raw_pos2[0], &ctx->raw_pos2[1], &ctx->raw_diam2[0], &ctx->raw_diam2[1], &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sxy, &ctx->sd, &ctx->skxx, &ctx->skxy,
                        &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->hb_pm, &ctx->nb_list, &ctx->gl_nodes,
                        &ctx->gl_weights, &ctx->gxs, &ctx->gys, &ctx->gpts,
@@ -356,7 +437,14 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
         if (e) cudaEventDestroy(e);
     if (ctx->ev_field_ready) cudaEventDestroy(ctx->ev_field_ready);
     if (ctx->ev_dl_done) cudaEventDestroy(ctx->ev_dl_done);
+    for (auto& e : ctx->ev_dl_copy)
+        if (e) cudaEventDestroy(e);
     if (ctx->dl_stream) cudaStreamDestroy(ctx->dl_stream);
+    if (ctx->ul_stream) cudaStreamDestroy(ctx->ul_stream);
+    for (int k = 0; k < 2; ++k) {
+        if (ctx->ev_ul_done[k]) cudaEventDestroy(ctx->ev_ul_done[k]);
+        if (ctx->ev_raw_free[k]) cudaEventDestroy(ctx->ev_raw_free[k]);
+    }
     cudaStreamDestroy(ctx->stream);
     delete ctx;
     return PGT_OK;
@@ -372,7 +460,7 @@ int pgt_synchronize(pgt_ctx* ctx)
         CK(cudaStreamSynchronize(ctx->dl_stream));
         ctx->dl_pending = false;
     }
-    return PGT_OK;
+    return resolve_counts(ctx);                              // deferred counts and errors of the frames in flight
 }
 
 void* pgt_stream(pgt_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
@@ -506,6 +594,38 @@ static int set_frame_common(pgt_ctx* ctx, int is_f32, int64_t N, const double bo
     return PGT_OK;
 }
 
+// The buffer pair of the next upload: the other one than the frame in flight uses.  The upload stream waits until the
+// last reader of that pair (stage 1 of the frame before last) is done.
+static int upload_slot(pgt_ctx* ctx, size_t pos_bytes, size_t diam_bytes)
+{
+    const int k = ctx->raw_slot ^ 1;
+    if (pos_bytes > ctx->raw_pos2[k].cap || diam_bytes > ctx->raw_diam2[k].cap) cudaStreamSynchronize(ctx->stream);   // re-allocation
+    int rc = ensure(ctx, ctx->raw_pos2[k], pos_bytes);
+    if (rc == PGT_OK) rc = ensure(ctx, ctx->raw_diam2[k], diam_bytes);
+    if (rc != PGT_OK) return -1;
+    if (ctx->raw_free_valid[k]) cudaStreamWaitEvent(ctx->ul_stream, ctx->ev_raw_free[k], 0);
+    ctx->raw_slot = k;
+    return k;
+}
+
+static void upload_done(pgt_ctx* ctx, int k)
+{
+    cudaEventRecord(ctx->ev_ul_done[k], ctx->ul_stream);
+    ctx->ul_wait_slot = k;
+    ctx->raw_cur = k;
+    ctx->src_pos = ctx->raw_pos2[k].p;
+    ctx->src_diam = ctx->raw_diam2[k].p;
+}
+
+// The main stream joins the upload of the frame it is about to use.
+static void wait_upload(pgt_ctx* ctx)
+{
+    if (ctx->ul_wait_slot >= 0) {
+        cudaStreamWaitEvent(ctx->stream, ctx->ev_ul_done[ctx->ul_wait_slot], 0);
+        ctx->ul_wait_slot = -1;
+    }
+}
+
 int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel, int is_f32,
                      int64_t N, const double box[3], int dim)
 {
@@ -514,13 +634,14 @@ int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void
     int rc = set_frame_common(ctx, is_f32, N, box, dim);
     if (rc != PGT_OK) return rc;
     const size_t es = is_f32 ? 4 : 8;
-    stage_begin(ctx, PGT_STAGE_UPLOAD);
-    ENSURE(ctx->raw_pos, (size_t)N * 3 * es);
-    ENSURE(ctx->raw_diam, (size_t)N * es);
-    CK(cudaMemcpyAsync(ctx->raw_pos.p, pos, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->raw_diam.p, diam, (size_t)N * es, cudaMemcpyHostToDevice, ctx->stream));
-    ctx->src_pos = ctx->raw_pos.p;
-    ctx->src_diam = ctx->raw_diam.p;
+    const int k = upload_slot(ctx, (size_t)N * 3 * es, (size_t)N * es);
+    if (k < 0) return PGT_ERR_CUDA;
+    cudaEventRecord(ctx->ev0[PGT_STAGE_UPLOAD], ctx->ul_stream);
+    CK(cudaMemcpyAsync(ctx->raw_pos2[k].p, pos, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->ul_stream));
+    CK(cudaMemcpyAsync(ctx->raw_diam2[k].p, diam, (size_t)N * es, cudaMemcpyHostToDevice, ctx->ul_stream));
+    cudaEventRecord(ctx->ev1[PGT_STAGE_UPLOAD], ctx->ul_stream);
+    ctx->ev_valid[PGT_STAGE_UPLOAD] = true;
+    upload_done(ctx, k);
     ctx->src_mass = nullptr;
     ctx->src_vel = nullptr;
     ctx->have_disp = false;
@@ -534,7 +655,6 @@ int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void
         CK(cudaMemcpyAsync(ctx->raw_vel.p, vel, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
         ctx->src_vel = ctx->raw_vel.p;
     }
-    stage_end(ctx, PGT_STAGE_UPLOAD);
     ctx->part_chunk = 0;
     return PGT_OK;
 }
@@ -553,16 +673,17 @@ int pgt_frame_upload_part(pgt_ctx* ctx, const void* pos_part, const void* diam_p
     int rc = set_frame_common(ctx, is_f32, N, box, dim);
     if (rc != PGT_OK) return rc;
     const size_t es = is_f32 ? 4 : 8;
-    stage_begin(ctx, PGT_STAGE_UPLOAD);
-    ENSURE(ctx->raw_pos, (size_t)chunk * nr * 3 * es);          // room for nranks equal parts: ncclAllGather moves equal counts
-    ENSURE(ctx->raw_diam, (size_t)chunk * nr * es);
+    // room for nranks equal parts: ncclAllGather moves equal counts
+    const int k = upload_slot(ctx, (size_t)chunk * nr * 3 * es, (size_t)chunk * nr * es);
+    if (k < 0) return PGT_ERR_CUDA;
+    cudaEventRecord(ctx->ev0[PGT_STAGE_UPLOAD], ctx->ul_stream);
     if (count > 0) {
-        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_pos.p) + (size_t)first * 3 * es, pos_part, (size_t)count * 3 * es, cudaMemcpyHostToDevice, ctx->stream));
-        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_diam.p) + (size_t)first * es, diam_part, (size_t)count * es, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_pos2[k].p) + (size_t)first * 3 * es, pos_part, (size_t)count * 3 * es, cudaMemcpyHostToDevice, ctx->ul_stream));
+        CK(cudaMemcpyAsync(static_cast<char*>(ctx->raw_diam2[k].p) + (size_t)first * es, diam_part, (size_t)count * es, cudaMemcpyHostToDevice, ctx->ul_stream));
     }
-    stage_end(ctx, PGT_STAGE_UPLOAD);
-    ctx->src_pos = ctx->raw_pos.p;
-    ctx->src_diam = ctx->raw_diam.p;
+    cudaEventRecord(ctx->ev1[PGT_STAGE_UPLOAD], ctx->ul_stream);
+    ctx->ev_valid[PGT_STAGE_UPLOAD] = true;
+    upload_done(ctx, k);
     ctx->src_mass = nullptr;
     ctx->src_vel = nullptr;
     ctx->have_disp = false;
@@ -578,6 +699,8 @@ int pgt_frame_set_device(pgt_ctx* ctx, const void* d_pos, const void* d_diam, co
     if (rc != PGT_OK) return rc;
     ctx->src_pos = d_pos;
     ctx->src_diam = d_diam;
+    ctx->raw_cur = -1;
+    ctx->ul_wait_slot = -1;
     ctx->src_mass = d_mass;
     ctx->src_vel = d_vel;
     ctx->have_disp = false;
@@ -627,6 +750,7 @@ int pgt_build_cells(pgt_ctx* ctx)
                     ctx->max_rcut, 2 * c.reach + 1);
     const int ncells = c.ncx * c.ncy;
 
+    wait_upload(ctx);
     stage_begin(ctx, PGT_STAGE_CELLS);
     ENSURE(ctx->cell_of, sizeof(int) * (size_t)std::max<long long>(N, 1));
     ENSURE(ctx->cell_count, sizeof(int) * ((size_t)ncells + 1));
@@ -636,7 +760,8 @@ int pgt_build_cells(pgt_ctx* ctx)
     ENSURE(ctx->eflags, sizeof(int) * 4);
     CK(cudaMemsetAsync(ctx->cell_count.p, 0, sizeof(int) * ((size_t)ncells + 1), ctx->stream));
     CK(cudaMemsetAsync(ctx->cell_fill.p, 0, sizeof(int) * (size_t)ncells, ctx->stream));
-    CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream));
+    if (!ctx->eflags_init) { CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream)); ctx->eflags_init = true; }
+    CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 2, ctx->stream));      // [0] stage flags; [2] is the sticky word
 
     double slab_lo = 0.0, slab_hi = 0.0;
     ctx->culled = shard_slab(ctx, c, &slab_lo, &slab_hi);
@@ -650,13 +775,28 @@ int pgt_build_cells(pgt_ctx* ctx)
                            ctx->sorted_orig.as<int>(), ctx->stream, &ctx->launches);
     pgt_launch_cell_sort(ctx->sorted_orig.as<int>(), ctx->cell_count.as<int>(), ncells, ctx->stream, &ctx->launches);
 
-    // live count and error flags (two ints) back to the host
-    int* h = reinterpret_cast<int*>(ctx->h_small);
-    pgt_launch_publish(ctx->cell_count.as<int>() + ncells, 1, ctx->eflags.p, 1, ctx->d_small, ctx->stream, &ctx->launches);
-    CK(cudaStreamSynchronize(ctx->stream));
-    ctx->n_live = h[0];
-    int rc = check_eflags(ctx, h[1]);
-    if (rc != PGT_OK) return rc;
+    // live count and error flags to the host (mapped memory).  A frame of the same shape as the last one counted does not
+    // wait for them: its arrays are sized from that frame's count with a margin, the kernels read the live count on the
+    // device, and a count beyond the margin raises the sticky error word
+    long long sig[8];
+    frame_signature(ctx, sig);
+    const bool defer = ctx->async_counts && ctx->known_nlive >= 0 && !memcmp(sig, ctx->known_sig, sizeof(sig));
+    const long long bound = defer ? std::min<long long>(N, (long long)ctx->known_nlive + ctx->known_nlive / 8 + 1024) : N;
+    pgt_launch_publish_count(ctx->cell_count.as<int>() + ncells, ctx->eflags.as<int>(), bound, ctx->eflags.as<int>() + 2, d_counts(ctx),
+                             d_counts(ctx) + 4, ctx->stream, &ctx->launches);
+    ctx->cells_deferred = defer;
+    if (defer) {
+        ctx->n_live = (int)bound;
+        ctx->counts_pending = true;
+    } else {
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->counts_pending = false;
+        const int* h = h_counts(ctx);
+        if (h[4]) return sticky_error(ctx, h[4]);
+        ctx->n_live = h[0];
+        ctx->known_nlive = -1;                               // valid again once the bond stage has counted too
+        memcpy(ctx->known_sig, sig, sizeof(sig));
+    }
 
     const size_t nl = (size_t)std::max(ctx->n_live, 1);
     ENSURE(ctx->sx, sizeof(double) * nl);
@@ -670,10 +810,14 @@ int pgt_build_cells(pgt_ctx* ctx)
         ENSURE(ctx->skyy, sizeof(double) * nl);
     }
     pgt_launch_gather_sorted(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box,
-                             ctx->sorted_orig.as<int>(), ctx->n_live, ctx->sx.as<double>(), ctx->sy.as<double>(),
+                             ctx->sorted_orig.as<int>(), ctx->n_live, ctx->cell_count.as<int>() + ncells, ctx->sx.as<double>(), ctx->sy.as<double>(),
                              ctx->sxy.as<double2>(), ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr, kin ? ctx->skxy.as<double>() : nullptr,
                              kin ? ctx->skyy.as<double>() : nullptr, ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
+    if (ctx->raw_cur >= 0) {                                 // stage 1 was the last reader of the raw frame
+        CK(cudaEventRecord(ctx->ev_raw_free[ctx->raw_cur], ctx->stream));
+        ctx->raw_free_valid[ctx->raw_cur] = true;
+    }
     stage_end(ctx, PGT_STAGE_CELLS);
     ctx->cells_built = true;
     ctx->bonds_built = false;
@@ -686,12 +830,19 @@ int pgt_build_bonds(pgt_ctx* ctx)
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: no pair potential");
     CK(cudaSetDevice(ctx->device));
+    // deferred counts: the record arrays keep last frame's size plus a margin, the writer drops records beyond it and the
+    // sticky word reports it; needs the single-search path and the warp-flattened writer (the one with the capacity guard)
+    const bool defer = ctx->cells_deferred && ctx->counts_pending && ctx->known_nhb >= 0 && ctx->bond_single_search &&
+                       ctx->bond_fill_flat && ctx->hb_pm_valid && ctx->n_live > 0 && ctx->n_live < (1 << 28);
+    if (ctx->counts_pending && !defer) {                       // this stage counts exactly: so must the frame
+        int rc = resolve_counts(ctx);
+        if (rc != PGT_OK) return rc;
+    }
     const int n = ctx->n_live;
     stage_begin(ctx, PGT_STAGE_BONDS);
     ENSURE(ctx->hb_cnt, sizeof(int) * ((size_t)n + 1));
     CK(cudaMemsetAsync(ctx->hb_cnt.as<int>() + n, 0, sizeof(int), ctx->stream));
     PgtFrameView fr = frame_view(ctx);
-    int* h = reinterpret_cast<int*>(ctx->h_small);
     // single search: count and keep the neighbours; a particle with more than PGT_NB_SLOTS bonds sends the frame
     // down the two-search path below
     bool listed = ctx->bond_single_search && n > 0 && n < (1 << 28);
@@ -708,22 +859,36 @@ int pgt_build_bonds(pgt_ctx* ctx)
     }
     pgt_launch_scan_exclusive(ctx->hb_cnt.as<int>(), ctx->hb_cnt.as<int>(), (long long)n + 1, ctx->scan_scratch.as<int>(),
                               ctx->stream, &ctx->launches);
-    pgt_launch_publish(ctx->hb_cnt.as<int>() + n, 1, ctx->eflags.p, 1, ctx->d_small, ctx->stream, &ctx->launches);
-    CK(cudaStreamSynchronize(ctx->stream));
-    if (h[0] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
-    if (listed && (h[1] & PGT_EFLAG_BOND_OVERFLOW)) {
-        // the counts are right, the kept lists are truncated: fill by a second search
-        listed = false;
+    const long long bound = defer ? ctx->known_nhb + ctx->known_nhb / 8 + 4096 : 0x7FFFFFFFLL;
+    pgt_launch_publish_count(ctx->hb_cnt.as<int>() + n, ctx->eflags.as<int>(), bound, ctx->eflags.as<int>() + 2, d_counts(ctx) + 2,
+                             d_counts(ctx) + 4, ctx->stream, &ctx->launches);
+    if (defer) {
+        ctx->n_hb = ctx->known_nhb;                            // an estimate until the counts are resolved
+    } else {
+        CK(cudaStreamSynchronize(ctx->stream));
+        const int* h = h_counts(ctx);
+        if (h[2] < 0) return fail(ctx, PGT_ERR_DATA, "half-bond count overflows int32");
+        if (listed && (h[3] & PGT_EFLAG_BOND_OVERFLOW)) {
+            // the counts are right, the kept lists are truncated: fill by a second search
+            listed = false;
+            CK(cudaMemsetAsync(ctx->eflags.as<int>() + 2, 0, sizeof(int), ctx->stream));   // handled here, not an error
+            h_counts(ctx)[4] = 0;
+        } else if (h[4]) {
+            return sticky_error(ctx, h[4]);
+        }
+        ctx->n_hb = h[2];
+        ctx->known_nhb = ctx->n_hb;                            // the next frame of this shape may defer
+        ctx->known_nlive = ctx->n_live;
     }
-    ctx->n_hb = h[0];
     ctx->hb_pm_valid = listed;
-    const size_t nb = (size_t)std::max<long long>(ctx->n_hb, 1);
+    const size_t nb = (size_t)std::max<long long>(defer ? bound : ctx->n_hb, 1);
     ENSURE(ctx->hb_b, sizeof(double2) * nb);
     ENSURE(ctx->hb_cf, sizeof(double2) * nb);
     ENSURE(ctx->hb_j, sizeof(int) * nb);
+    ctx->hb_cap = (long long)nb;
     ctx->hb_cscale = ctx->have_cg ? 1.0 / ctx->cg.rcutsq : 1.0;
     fr = frame_view(ctx);
-    const PgtBondOut out{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>() };
+    const PgtBondOut out{ ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->hb_j.as<int>(), ctx->hb_cap };
     if (listed)
         pgt_launch_bonds(ctx->bond_fill_flat ? 5 : 6, ctx->pot, fr, ctx->box, ctx->cells, ctx->max_rcut, ctx->hb_cnt.as<int>(), out, ctx->hb_cscale,
                          ctx->nb_list.as<int>(), ctx->stream, &ctx->launches);
@@ -739,6 +904,7 @@ int pgt_build_bonds(pgt_ctx* ctx)
 int pgt_frame_counts(pgt_ctx* ctx, int64_t* n_live, int64_t* n_halfbonds, int64_t* n_cells)
 {
     if (!ctx) return PGT_ERR_ARG;
+    RESOLVE();
     if (n_live) *n_live = ctx->cells_built ? ctx->n_live : -1;
     if (n_halfbonds) *n_halfbonds = ctx->bonds_built ? ctx->n_hb : -1;
     if (n_cells) *n_cells = ctx->cells_built ? (int64_t)ctx->cells.ncx * ctx->cells.ncy : -1;
@@ -821,6 +987,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
         return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
     if (ctx->n_live >= (1 << 28))
         return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_ik_compute: %d live particles; the gather's packed lists address 2^28", ctx->n_live);
+    if (ctx->quad_mode == PGT_QUAD_ADAPTIVE || (obs_mask & PGT_OBS_ELASTIC)) RESOLVE();   // not throughput paths: exact counts
     if (ctx->culled) {
         double lo = 0.0, hi = 0.0;
         if (!shard_slab(ctx, ctx->cells, &lo, &hi) || lo < ctx->slab_lo || hi > ctx->slab_hi)
@@ -844,6 +1011,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     stage_begin(ctx, PGT_STAGE_IK);
     if ((obs_mask & PGT_OBS_VIRIAL) && ctx->hb_cscale != 1.0 / ctx->cg.rcutsq) {
         // the CG radius changed after the bond list was built: refresh the records' scaled |b|^2
+        RESOLVE();                                           // the exact record count
         ctx->hb_cscale = 1.0 / ctx->cg.rcutsq;
         pgt_launch_rescale_bonds(ctx->hb_b.as<double2>(), ctx->hb_cf.as<double2>(), ctx->n_hb, ctx->hb_cscale, ctx->stream, &ctx->launches);
     }
@@ -924,6 +1092,7 @@ static PgtIKArgs ik_args_impl(pgt_ctx* ctx, unsigned obs_mask)
 
 int pgt_ik_count_work(pgt_ctx* ctx, int64_t* sum_unique_bonds, int64_t* sum_halfbond_items, int64_t* sum_particles)
 {
+    if (ctx) RESOLVE();
     if (!ctx) return PGT_ERR_ARG;
     if (!ctx->bonds_built || !ctx->have_cg || ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_count_work: frame, bonds, cg and grid required");
     CK(cudaSetDevice(ctx->device));
@@ -983,6 +1152,12 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
         ctx->ik_variant = l;
         return PGT_OK;
     }
+    if (!strcmp(name, "async_counts")) {
+        ctx->async_counts = value != 0.0;
+        ctx->known_nlive = -1;
+        ctx->known_nhb = -1;
+        return PGT_OK;
+    }
     if (!strcmp(name, "slab_cull")) {
         ctx->slab_cull = value != 0.0;
         ctx->cells_built = false;
@@ -1032,7 +1207,7 @@ static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
         if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->stream));
         stage_end(ctx, PGT_STAGE_DOWNLOAD);
         CK(cudaStreamSynchronize(ctx->stream));
-        return PGT_OK;
+        return resolve_counts(ctx);
     }
     // asynchronous: the copy runs on its own stream behind the gather, so that the next frame's upload and
     // stages (main stream) are not queued behind it
@@ -1040,6 +1215,8 @@ static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
     CK(cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_field_ready, 0));
     if (gl > 0) CK(cudaMemcpyAsync(out, b->p, sizeof(double) * nc * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
     CK(cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
+    CK(cudaEventRecord(ctx->ev_dl_copy[ctx->dl_seq & 3], ctx->dl_stream));
+    ctx->dl_seq++;
     ctx->dl_pending = true;
     return PGT_OK;
 }
@@ -1055,13 +1232,18 @@ int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out)
     if (nc != 4) return fail(ctx, PGT_ERR_ARG, "field %d is not a 2x2 tensor field", field_id);
     CK(cudaSetDevice(ctx->device));
     const long long gl = ctx->field_g1 - ctx->field_g0;   // the shard the field was computed for
-    if (ctx->dl_pending) CK(cudaStreamSynchronize(ctx->dl_stream));      // the pack buffer is still being read back
+    // the pack buffer may still be read back by the previous copy: the read-back stream is in order, the pack below queues
+    // behind it (only a re-allocation of the buffer has to wait on the host)
+    if (ctx->dl_pending && sizeof(double) * 3 * (size_t)std::max<long long>(gl, 1) > ctx->pack.cap) CK(cudaStreamSynchronize(ctx->dl_stream));
     ENSURE(ctx->pack, sizeof(double) * 3 * (size_t)std::max<long long>(gl, 1));
     CK(cudaEventRecord(ctx->ev_field_ready, ctx->stream));
     CK(cudaStreamWaitEvent(ctx->dl_stream, ctx->ev_field_ready, 0));
     pgt_launch_pack_sym(static_cast<const double*>(b->p), ctx->pack.as<double>(), gl, ctx->dl_stream, &ctx->launches);
-    if (gl > 0) CK(cudaMemcpyAsync(out, ctx->pack.p, sizeof(double) * 3 * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
+    // the next gather may overwrite the field as soon as it has been packed; the copy reads the pack buffer
     CK(cudaEventRecord(ctx->ev_dl_done, ctx->dl_stream));
+    if (gl > 0) CK(cudaMemcpyAsync(out, ctx->pack.p, sizeof(double) * 3 * (size_t)gl, cudaMemcpyDeviceToHost, ctx->dl_stream));
+    CK(cudaEventRecord(ctx->ev_dl_copy[ctx->dl_seq & 3], ctx->dl_stream));
+    ctx->dl_seq++;
     ctx->dl_pending = true;
     return PGT_OK;
 }
@@ -1072,6 +1254,31 @@ int pgt_ik_download_wait(pgt_ctx* ctx)
     if (ctx->dl_pending) {
         CK(cudaStreamSynchronize(ctx->dl_stream));
         ctx->dl_pending = false;
+        ctx->dl_waited = ctx->dl_seq;
+        // the frame whose field has just landed published its counts before its gather ran: an error word raised by it
+        // (or by a later frame) is visible now, without waiting for the frames still in flight on the main stream
+        if (ctx->counts_pending && h_counts(ctx)[4]) {
+            CK(cudaStreamSynchronize(ctx->stream));
+            ctx->counts_pending = false;
+            return sticky_error(ctx, h_counts(ctx)[4]);
+        }
+    }
+    return PGT_OK;
+}
+
+int pgt_ik_download_wait_keep(pgt_ctx* ctx, int keep)
+{
+    if (!ctx) return PGT_ERR_ARG;
+    if (keep < 0 || keep > 3) return fail(ctx, PGT_ERR_ARG, "pgt_ik_download_wait_keep: keep must be 0..3");
+    const long long upto = ctx->dl_seq - keep;               // read-backs [0, upto) must have landed
+    if (upto > ctx->dl_waited) {
+        CK(cudaEventSynchronize(ctx->ev_dl_copy[(upto - 1) & 3]));   // the stream is in order: the youngest of them suffices
+        ctx->dl_waited = upto;
+        if (ctx->counts_pending && h_counts(ctx)[4]) {       // see pgt_ik_download_wait
+            CK(cudaStreamSynchronize(ctx->stream));
+            ctx->counts_pending = false;
+            return sticky_error(ctx, h_counts(ctx)[4]);
+        }
     }
     return PGT_OK;
 }
@@ -1091,6 +1298,7 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
 
 int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
 {
+    if (ctx) RESOLVE();
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: no pair potential");
@@ -1140,6 +1348,7 @@ int pgt_frame_set_displacement(pgt_ctx* ctx, const double* disp_xyz, int64_t N)
 
 int pgt_thermo_elastic(pgt_ctx* ctx, double* out)
 {
+    if (ctx) RESOLVE();
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_elastic: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: no pair potential");
@@ -1163,6 +1372,7 @@ int pgt_thermo_elastic(pgt_ctx* ctx, double* out)
 // ---------------------------------------------------------------------------------- exports
 static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32_t* oi, int32_t* oj, double* rij_xy, double* fdivr)
 {
+    if (ctx) RESOLVE();
     if (!ctx || !n) return fail(ctx, PGT_ERR_ARG, "export: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "export: cells not built");
     CK(cudaSetDevice(ctx->device));
@@ -1239,6 +1449,7 @@ int pgt_export_wrapped(pgt_ctx* ctx, double* xy, uint8_t* alive)
     if (!ctx || !xy) return fail(ctx, PGT_ERR_ARG, "pgt_export_wrapped: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_export_wrapped: cells not built");
     CK(cudaSetDevice(ctx->device));
+    RESOLVE();
     const int np = ctx->n_live;
     std::vector<int> orig((size_t)std::max(np, 1));
     std::vector<double> x((size_t)std::max(np, 1)), y((size_t)std::max(np, 1));
@@ -1429,8 +1640,10 @@ int pgt_comm_allgather_frame(pgt_ctx* ctx)
     const size_t es = ctx->is_f32 ? 4 : 8;
     const int dtype = ctx->is_f32 ? 7 /* ncclFloat32 */ : 8 /* ncclFloat64 */;
     const size_t chunk = (size_t)ctx->part_chunk;
-    char* pos = static_cast<char*>(ctx->raw_pos.p);
-    char* diam = static_cast<char*>(ctx->raw_diam.p);
+    if (ctx->raw_cur < 0) return fail(ctx, PGT_ERR_STATE, "pgt_comm_allgather_frame: the frame was not uploaded by pgt_frame_upload_part");
+    wait_upload(ctx);
+    char* pos = static_cast<char*>(ctx->raw_pos2[ctx->raw_cur].p);
+    char* diam = static_cast<char*>(ctx->raw_diam2[ctx->raw_cur].p);
     // in place: this rank's part already sits at its offset of the receive buffer
     int nrc = g_nccl.GroupStart();
     if (nrc == 0) nrc = g_nccl.AllGather(pos + (size_t)ctx->rank * chunk * 3 * es, pos, chunk * 3, dtype, ctx->comm, ctx->stream);

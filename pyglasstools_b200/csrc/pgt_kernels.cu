@@ -368,12 +368,15 @@ void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, c
 template <bool F32>
 __global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ pos, const void* __restrict__ diam,
                                                        const void* __restrict__ mass, const void* __restrict__ vel, PgtBox box,
-                                                       const int* __restrict__ sorted_orig, int n_live, double* __restrict__ sx,
+                                                       const int* __restrict__ sorted_orig, int n_live, const int* __restrict__ n_live_dev,
+                                                       double* __restrict__ sx,
                                                        double* __restrict__ sy, double2* __restrict__ sxy, double* __restrict__ sd,
                                                        double* __restrict__ skxx, double* __restrict__ skxy, double* __restrict__ skyy)
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n_live) return;
+    // n_live is the host's bound (exact, or last frame's count with a margin when the host did not wait for this frame's
+    // count); the live count itself sits in device memory
+    if (p >= n_live || p >= __ldg(n_live_dev)) return;
     const long long i = sorted_orig[p];
     double x, y;
     load_wrapped<F32>(pos, i, box, x, y, nullptr);
@@ -393,13 +396,13 @@ __global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ 
 }
 
 void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, double* sx, double* sy, double2* sxy, double* sd, double* skxx,
-                              double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
+                              const int* sorted_orig, int n_live, const int* n_live_dev, double* sx, double* sy, double2* sxy, double* sd,
+                              double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (n_live <= 0) return;
     const int blocks = (n_live + 255) / 256;
-    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sxy, sd, skxx, skxy, skyy);
-    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, sx, sy, sxy, sd, skxx, skxy, skyy);
+    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, n_live_dev, sx, sy, sxy, sd, skxx, skxy, skyy);
+    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, n_live_dev, sx, sy, sxy, sd, skxx, skxy, skyy);
     lc->n++;
 }
 
@@ -519,6 +522,11 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
 {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= fr.n) return;
+    if (fr.n_dev && p >= __ldg(fr.n_dev)) {        // fr.n is only a bound (the host did not wait for the live count)
+        counts[p] = 0;
+        prim_mask[p] = 0;
+        return;
+    }
     const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
     int n = 0;
     unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (q visited after p)
@@ -567,6 +575,7 @@ __global__ void __launch_bounds__(128) k_bonds_fill_flat(PgtPot pot, PgtFrameVie
                                                          const unsigned* __restrict__ nb_list, PgtBondOut out, double cscale)
 {
     const int lane = threadIdx.x & 31;
+    const long long cap = out.cap;                 // records the arrays hold (an estimate when the host did not wait for the count)
     const int p0 = (blockIdx.x * blockDim.x + threadIdx.x) & ~31;
     if (p0 >= fr.n) return;
     const bool have = p0 + lane < fr.n;
@@ -585,7 +594,7 @@ __global__ void __launch_bounds__(128) k_bonds_fill_flat(PgtPot pot, PgtFrameVie
         }
         const int k = e - __shfl_sync(FULL_MASK, w0, o);
         const double xo = __shfl_sync(FULL_MASK, xi, o), yo = __shfl_sync(FULL_MASK, yi, o), dio = __shfl_sync(FULL_MASK, di, o);
-        if (e < W1) {
+        if (e < W1 && e < cap) {
             const unsigned en = __ldg(nb_list + (size_t)k * fr.n + (p0 + o));
             const int q = (int)(en & 0x0FFFFFFFu);
             const int kx = (int)((en >> 28) & 3u) - 1, ky = (int)(en >> 30) - 1;
@@ -1473,6 +1482,28 @@ __global__ void k_publish(const void* __restrict__ s0, int n0, const void* __res
     const int t = threadIdx.x;
     if (t < n0) dst[t] = static_cast<const int*>(s0)[t];
     else if (t < n0 + n1) dst[t] = static_cast<const int*>(s1)[t - n0];
+}
+
+// A stage's count and error flags to the mapped slots dst[0], dst[1]; the flags -- and "the count exceeds the bound the host
+// sized this frame's arrays for" -- are OR-ed into a sticky word that survives later frames (dst[4] mirrors it), so that a
+// host that did not wait for this frame still learns of it at its next synchronisation point.
+__global__ void k_publish_count(const int* __restrict__ count, const int* __restrict__ flags, long long bound, int* __restrict__ sticky,
+                                int* __restrict__ dst, int* __restrict__ dst_sticky)
+{
+    if (threadIdx.x != 0) return;
+    const int c = *count, f = *flags;
+    dst[0] = c;
+    dst[1] = f;
+    const int s = *sticky | f | (((long long)c > bound || c < 0) ? PGT_EFLAG_BOUND : 0);
+    *sticky = s;
+    *dst_sticky = s;
+}
+
+void pgt_launch_publish_count(const int* count, const int* flags, long long bound, int* sticky, int* dst_mapped, int* dst_sticky,
+                              cudaStream_t st, PgtLaunchCounter* lc)
+{
+    k_publish_count<<<1, 32, 0, st>>>(count, flags, bound, sticky, dst_mapped, dst_sticky);
+    lc->n++;
 }
 
 void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc)

@@ -17,7 +17,7 @@
 
 // error bits raised by kernels (checked by the host after each stage)
 enum { PGT_EFLAG_Z_NONZERO = 1, PGT_EFLAG_WRAP_RUNAWAY = 2, PGT_EFLAG_BOND_OVERFLOW = 4, PGT_EFLAG_QAG_FAILED = 8,
-       PGT_EFLAG_QAG_CAPACITY = 16 };
+       PGT_EFLAG_QAG_CAPACITY = 16, PGT_EFLAG_BOUND = 32 /* a count exceeded the bound the host sized the frame's arrays for */ };
 
 struct PgtBox {
     double lo[3], hi[3], L[3];
@@ -32,7 +32,8 @@ struct PgtCells {
 
 // Sorted (by cell, row-major) structure-of-arrays view of the live particles + half-bond CSR.
 struct PgtFrameView {
-    int n;                       // live particles
+    int n;                       // live particles (a bound when n_dev is set)
+    const int* n_dev;            // device copy of the live count when the host did not wait for it (else NULL)
     const double* sx;            // wrapped x
     const double* sy;            // wrapped y
     const double2* sxy;          // (x, y) interleaved: 16-byte rows for the quad gather's bulk copies
@@ -58,6 +59,7 @@ struct PgtBondOut {              // destination of k_bonds<.,FILL>
     double2* b;
     double2* cf;
     int* j;
+    long long cap;               // records the arrays hold
 };
 
 struct PgtGridView {
@@ -109,8 +111,8 @@ void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_sta
                             cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, double* sx, double* sy, double2* sxy, double* sd, double* skxx,
-                              double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
+                              const int* sorted_orig, int n_live, const int* n_live_dev, double* sx, double* sy, double2* sxy, double* sd,
+                              double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
 // mode 2/3: same for plain neighbours within max_rcut (export only);
 // mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word, out.b = the
@@ -137,6 +139,9 @@ void pgt_launch_thermo_elastic(const PgtPot& pot, PgtFrameView fr, PgtBox box, P
 cudaError_t pgt_launch_ik_elastic(const PgtPot& pot, const PgtIKArgs& a, const double* disp, double max_rcut, int adaptive, double* out,
                                   int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
 void pgt_launch_ik_count(const PgtIKArgs& a, unsigned long long* out3, cudaStream_t st, PgtLaunchCounter* lc);
+// count + flags of a stage to mapped host memory, flags and bound violations OR-ed into a sticky device word
+void pgt_launch_publish_count(const int* count, const int* flags, long long bound, int* sticky, int* dst_mapped, int* dst_sticky,
+                              cudaStream_t st, PgtLaunchCounter* lc);
 // copies nwords0 + nwords1 (<= 64) 32-bit words to mapped host memory
 void pgt_launch_publish(const void* s0, int nwords0, const void* s1, int nwords1, void* dst_mapped, cudaStream_t st, PgtLaunchCounter* lc);
 // (xx, xy, yx, yy) per point -> (xx, xy, yy) per point

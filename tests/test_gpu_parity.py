@@ -551,6 +551,105 @@ def test_full_size_frames_properties_and_sampled_oracle(gpu_ctx, orc, n, nsample
     assert np.array_equal(np.sort(bi.astype(np.int64) * (n * n) + bj), np.sort(bj.astype(np.int64) * (n * n) + bi))
 
 
+def test_full_size_cfg4_other_potential_wide_kernel(gpu_ctx, orc):
+    """BASELINE configs[3] at full size: polydisperse10 (q = 3, rcut 1.48), octic R = 4, GL-5, N = 1 048 576 on a 1024^2
+    grid.  The oracle on a random sample of grid points (with the seam corners); over the whole field the two gather
+    formulations agree, the duplicated end rows / columns agree and a 4-way np.array_split sharding (slab-local cell and
+    bond lists) reproduces the field bit for bit."""
+    n = 1024
+    fr = synth.synth_frame(n, synth.SEEDS["cfg4"])
+    pos, diam, box = fr["position"], fr["diameter"], fr["box"]
+    P = orc.potential("poly10")
+    S = setup_ctx(gpu_ctx, orc, P, "poly10", pos, diam, box)
+    gpu_ctx.build_bonds()
+    gpu_ctx.set_cg("octic", 4.0, 5)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, n)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    fields = {}
+    for variant in (2, 7):
+        gpu_ctx.set_option("ik_variant", variant)
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        fields[variant] = gpu_ctx.ik_download()
+    gpu_ctx.set_option("ik_variant", 0)
+    full = fields[7].reshape(n, n, 4)
+    assert_close(fields[7], fields[2])
+    assert_close(full[0], full[-1])
+    assert_close(full[:, 0], full[:, -1])
+    rng = np.random.default_rng(44)
+    ii = np.concatenate([rng.integers(0, n, 150), [0, n - 1, 0, n - 1]])
+    jj = np.concatenate([rng.integers(0, n, 150), [0, n - 1, n - 1, 0]])
+    grid = np.zeros((len(ii), 3)); grid[:, 0] = axis[ii]; grid[:, 1] = axis[jj]
+    want = S.ik(P, orc.cgfunc("octic", 4.0, 5), grid)["virial"]
+    assert_close(full[ii, jj], want)
+    # sharded: every shard re-builds its own slab of the frame
+    G = n * n
+    parts, g0, kept = [], 0, []
+    for s in [len(c) for c in np.array_split(np.arange(G), 4)]:
+        gpu_ctx.set_shard(g0, g0 + s)
+        gpu_ctx.upload(pos, diam, box)
+        gpu_ctx.build_cells()
+        gpu_ctx.build_bonds()
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        parts.append(gpu_ctx.ik_download())
+        kept.append(gpu_ctx.counts()["n_live"])
+        g0 += s
+    gpu_ctx.set_shard(0, G)
+    assert max(kept) < 0.4 * n * n
+    assert np.array_equal(np.vstack(parts), fields[7])
+
+
+def test_deferred_counts_same_bits_and_late_errors(orc, fixture_frames):
+    """Frames of the same shape as one already counted do not wait for their own particle / half-bond counts (option
+    "async_counts", default on): same fields bit for bit as with exact counting; a frame whose bond count outgrows the
+    margin is reported at the next synchronisation point and the frame can be submitted again."""
+    diam, box = fixture_frames.diameter, fixture_frames.box
+    P = orc.potential("poly12")
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 64)
+    fields = {}
+    for mode in (1, 0):
+        ctx = _capi.Context(0)
+        ctx.set_option("async_counts", mode)
+        ctx.set_potential("poly12", P.scaled_rcut, orc.pot_params(P))
+        ctx.set_cg("octic", 2.0, 5)
+        ctx.set_max_rcut(orc.System(box, fixture_frames.position(0), diam).max_rcut(P))
+        ctx.set_grid_cartesian(axis, axis)
+        out = []
+        pinned = [_capi.PinnedArray((64 * 64, 4), np.float64) for _ in range(6)]
+        for k, f in enumerate((0, 40, 80, 120, 160, 199)):
+            ctx.upload(fixture_frames.position(f), diam, box)
+            ctx.build_cells()
+            ctx.build_bonds()
+            ctx.ik_compute(_capi.OBS_VIRIAL)
+            ctx.ik_download_async(_capi.FIELD_VIRIAL, pinned[k].array)
+        ctx.sync()
+        fields[mode] = [p.array.copy() for p in pinned]
+        counts = ctx.counts()
+        assert counts["n_live"] == len(diam) and counts["n_halfbonds"] > 0
+        if mode == 1:
+            # a frame with many more bonds than the margin allows: the error arrives late, then the frame goes through
+            big = (diam * 2.5).astype(np.float32)               # every neighbour within max_rcut bonds: beyond the margin (and 16 slots)
+            ctx.upload(fixture_frames.position(199), big, box)
+            ctx.build_cells()
+            ctx.build_bonds()
+            ctx.ik_compute(_capi.OBS_VIRIAL)
+            with pytest.raises(_capi.PgtError):
+                ctx.sync()
+            ctx.upload(fixture_frames.position(199), big, box)
+            ctx.build_cells()
+            ctx.build_bonds()
+            ctx.ik_compute(_capi.OBS_VIRIAL)
+            got = ctx.ik_download()
+            S = orc.System(box, fixture_frames.position(199), big)
+            grid = np.zeros((64 * 64, 3)); grid[:, 0] = np.repeat(axis, 64); grid[:, 1] = np.tile(axis, 64)
+            want = S.ik(P, orc.cgfunc("octic", 2.0, 5), grid, max_rcut=orc.System(box, fixture_frames.position(0), diam).max_rcut(P))["virial"]
+            assert_close(got, want)
+        ctx.close()
+    for a, b in zip(fields[1], fields[0]):
+        assert np.array_equal(a, b)
+
+
 def test_symmetric_packed_readback(gpu_ctx, orc, fixture_frames):
     """pgt_ik_download_sym_async: (xx, xy, yy) per grid point equals columns 0, 1, 3 of the full read-back, and the
     dropped column 2 (yx) is bit-identical to column 1 in the full field."""

@@ -116,6 +116,46 @@ def test_thermo_example_script_and_readme_known_answer(workdir, fixture_gsd, fix
     assert_close(pglass.loggers_list[1].global_obs['virialstress'].values(), np.asarray(w["virial"]).ravel())
 
 
+def test_thermo_trajectory_synthetic_gsd_through_analyze(workdir, orc):
+    """BASELINE configs[1] in miniature: a synthetic polydisperse12 trajectory written to GSD (N = 4096, 40 frames), read
+    back with utils.read_gsd and run through pglass.analyze with thermo loggers -- the whole script surface over many
+    frames -- against the oracle's ThermoCalculator loop frame by frame."""
+    import pyglasstools as pglass
+    import pyglasstools.utils as utils
+    import pyglasstools.io as io
+    import pyglasstools.potential as pot
+    import pyglasstools.thermo as thermo
+    from pyglasstools import gsdio
+    from pyglasstools_b200 import synth
+
+    nframes = 40
+    frames = [synth.synth_frame(64, synth.SEEDS["cfg2"] + f) for f in range(nframes)]
+    gsdio.write_trajectory("traj.gsd", [dict(box=fr["box"], position=fr["position"], diameter=fr["diameter"]) for fr in frames])
+    poly12 = pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)                                    # noqa: F841
+    mysystem = utils.read_gsd(filename="traj.gsd", checkpointfile="restart.log")              # noqa: F841
+    calc = thermo.calculator()
+    log = io.logfile(filename="thermo.log", names=['virialstress_00', 'virialstress_11', 'virialstress_01', 'potentialenergy'], solver=calc)
+    pglass.analyze(frame_list=range(nframes))
+    del log
+    got = np.loadtxt("thermo.log", skiprows=1)
+    assert got.shape == (nframes, 5)
+    P = orc.potential("poly12")
+    # the reference freezes max_rcut at the calculator's construction (Calculator.h:37-46): the first frame's value
+    S0 = orc.System(frames[0]["box"], frames[0]["position"], frames[0]["diameter"])
+    mr = S0.max_rcut(P)
+    for f in range(nframes):
+        S = orc.System(frames[f]["box"], frames[f]["position"], frames[f]["diameter"])
+        w = S.thermo(P, born=False, max_rcut=mr)
+        want = [w["virial"][0], w["virial"][3], w["virial"][2], w["energy"]]
+        assert got[f, 0] == f
+        np.testing.assert_allclose(got[f, 1:], want, rtol=0, atol=1.0e-6)                      # "%f" log
+    obs = pglass.loggers_list[-1].global_obs
+    S = orc.System(frames[-1]["box"], frames[-1]["position"], frames[-1]["diameter"])
+    w = S.thermo(P, born=False, max_rcut=mr)
+    assert_close(obs['virialstress'].values(), np.asarray(w["virial"]).ravel())
+    assert_close(obs['potentialenergy'].values(), [w["energy"]])
+
+
 def test_thermo_and_ik_share_one_frame_upload(workdir, fixture_gsd):
     """Two calculators on the same ParticleSystem upload and build the cell list once per frame."""
     import pyglasstools as pglass
