@@ -530,15 +530,54 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
     const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
     int n = 0;
     unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (q visited after p)
-    for_each_neighbor_img(fr, box, cells, p, xi, yi, rc2, [&](int q, double, double, double rsq, unsigned code) {
-        const double dj = __ldg(fr.sd + q);
-        if (!pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) return;
-        if (n < PGT_NB_SLOTS) {
-            nb_list[(size_t)n * fr.n + p] = (unsigned)q | ((code & 15u) << 28);
-            if (code & 16u) pm |= 1u << n;
+    // The neighbour enumeration of for_each_neighbor_img (same cells, same order, same operations on the same operands),
+    // written as ONE flat loop over the candidates of all (row, segment) spans: the 32 searches of a warp then cost the
+    // largest TOTAL candidate count among its lanes, not the sum over the spans of the largest span.
+    const int cx = cell_coord(xi, box.lo[0], cells.inv_cwx, cells.ncx);
+    const int cy = cell_coord(yi, box.lo[1], cells.inv_cwy, cells.ncy);
+    Seg seg[3];
+    const int nseg = split_segments(cx - cells.reach, cx + cells.reach, cells.ncx, seg);
+    int s_home = 0;                                // the segment that holds p's own cell (the one without an image shift)
+    for (int s = 1; s < nseg; ++s) if (seg[s].k == 0) s_home = s;
+    int uy = cy - cells.reach, s = -1;             // current span
+    const int uy_end = cy + cells.reach;
+    int q = 0, qe = 0, fwd_from = 0;               // fwd_from: first q of the span that comes after p in the visiting order
+    double cpx = 0.0, cpy = 0.0;
+    unsigned code = 0u;
+    for (;;) {
+        if (q >= qe) {                             // next span (an empty one costs one turn)
+            if (++s == nseg) { s = 0; ++uy; }
+            if (uy > uy_end) break;
+            int ky = 0, row = uy;
+            if (uy < 0) { ky = +1; row = uy + cells.ncy; }
+            else if (uy >= cells.ncy) { ky = -1; row = uy - cells.ncy; }
+            const Seg sg = s == 0 ? seg[0] : (s == 1 ? seg[1] : seg[2]);   // selects, not a local-memory array
+            cpy = yi + ky * box.L[1];
+            cpx = xi + sg.k * box.L[0];
+            const int rbase = row * cells.ncx;
+            q = __ldg(fr.cell_start + rbase + sg.c0);
+            qe = __ldg(fr.cell_start + rbase + sg.c1 + 1);
+            code = (unsigned)(sg.k + 1) | ((unsigned)(ky + 1) << 2);
+            const int dir = uy != cy ? (uy > cy ? 1 : -1) : (s != s_home ? (s > s_home ? 1 : -1) : 0);
+            fwd_from = dir > 0 ? q : (dir < 0 ? qe : p + 1);
+            continue;
         }
-        ++n;
-    });
+        const double2 r = __ldg(fr.sxy + q);
+        const double dx = r.x - cpx, dy = r.y - cpy;
+        const double rsq = dx * dx + dy * dy;
+        // the particle itself is skipped (IrvingKirkwood.h:97), tested on hits only
+        if (!(rsq > rc2) && q != p) {
+            const double dj = __ldg(fr.sd + q);
+            if (pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) {
+                if (n < PGT_NB_SLOTS) {
+                    nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
+                    if (q >= fwd_from) pm |= 1u << n;
+                }
+                ++n;
+            }
+        }
+        ++q;
+    }
     counts[p] = n;
     prim_mask[p] = (unsigned short)pm;
     if (n > PGT_NB_SLOTS) atomicOr(eflags, PGT_EFLAG_BOND_OVERFLOW);
