@@ -300,7 +300,12 @@ void export_calculators(py::module_& m)
         .def("gettostring", &FieldObservable::gettostring)
         .def("save", &FieldObservable::save)
         .def("clear", &FieldObservable::clear_point)
-        .def("values", &FieldObservable::values);
+        .def("values", &FieldObservable::values)
+        // additive extension: load values computed elsewhere (re-formatting a saved binary dump; the formatter's tests)
+        .def("set_values", [](FieldObservable& f, py::array_t<double, py::array::c_style | py::array::forcecast> a) {
+            if ((std::size_t)a.size() != f.npoints * (std::size_t)f.ncomp) throw std::invalid_argument("[ERROR] set_values: expected npoints x ncomp values");
+            f.val.assign(a.data(), a.data() + a.size());
+        });
     export_field_obs<FieldKind::Virial, 2>(m, "VirialStressField2D");
     export_field_obs<FieldKind::Virial, 3>(m, "VirialStressField3D");
     export_field_obs<FieldKind::ElasticVirial, 2>(m, "ElasticVirialStressField2D");

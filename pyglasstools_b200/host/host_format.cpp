@@ -1,12 +1,18 @@
 // host_format.cpp -- text formatting of field dumps (io.fieldlogger.save_perrank, io.py:112-128) done in
-// one C++ pass per frame instead of 3 G Python->C++ calls: byte-identical lines
+// one multithreaded C++ pass per frame instead of 3 G Python->C++ calls: byte-identical lines
 //   "1 {x} {y} [{z} ]" + for each requested component  ostream<<value<<" "  + "\n"
 // where {x} is Python's str(float) (shortest round-trip repr) and the values use the C++ ostream default
 // (%g with 6 significant digits), exactly as CoarseGrainedField.h:160-183 prints them.
 #include <charconv>
 #include <cmath>
 #include <cstdio>
+#include <chrono>
+#include <cstdint>
+#include <cstdlib>
 #include <cstring>
+#include <thread>
+#include <vector>
+#include <algorithm>
 
 #include "host_common.h"
 
@@ -17,6 +23,14 @@ std::string ostream_double(double v)
     char buf[40];
     const int n = std::snprintf(buf, sizeof buf, "%g", v);
     return std::string(buf, (std::size_t)n);
+}
+
+static inline char* put_g_chars(char* p, char* end, double v);
+// the bulk formatter's route for one value (tests compare it with ostream_double)
+std::string ostream_double_fast(double v)
+{
+    char buf[48];
+    return std::string(buf, (std::size_t)(put_g_chars(buf, buf + sizeof buf, v) - buf));
 }
 
 // Python's float.__repr__: shortest digits that round-trip; scientific when the decimal exponent is < -4 or >= 16.
@@ -40,46 +54,180 @@ std::string repr_double(double v)
     return f;
 }
 
-// Appends the frame's lines for points [0, G) to a single string.
-static std::string format_field_frame(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
-                                      const std::vector<int>& comps)
+// printf("%g") characters of one value.  Fast path: six significant digits from ONE multiplication by an exactly
+// representable power of ten and a round-to-nearest, taken only when the scaled value is not within 1e-6 of a rounding
+// tie (there the exact decimal expansion decides: std::to_chars(general, 6), specified to produce printf's "%.6g").
+static inline char* put_g_chars(char* p, char* end, double v)
+{
+    static const double P10[23] = { 1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13, 1e14, 1e15, 1e16,
+                                    1e17, 1e18, 1e19, 1e20, 1e21, 1e22 };
+    const double a = std::fabs(v);
+    if (a >= 1e-15 && a < 1e20) {
+        int e2;
+        std::frexp(a, &e2);
+        int e10 = (int)std::floor((e2 - 1) * 0.30102999566398120);           // floor(log10 a) or one less
+        for (int tries = 0; tries < 2; ++tries) {
+            const int sh = 5 - e10;                                           // a * 10^sh in [1e5, 1e6)
+            if (sh < -22 || sh > 22) break;
+            const double scaled = sh >= 0 ? a * P10[sh] : a / P10[-sh];
+            if (scaled >= 999999.4999) { if (scaled < 999999.5001) break; ++e10; continue; }   // at the tie: exact route
+            if (scaled < 99999.5) { if (scaled < 99999.4999) { --e10; continue; } break; }
+            const double fl = std::floor(scaled), frac = scaled - fl;
+            if (std::fabs(frac - 0.5) < 1e-6) break;                          // near a tie: the slow, exact route
+            long long m = (long long)fl + (frac > 0.5 ? 1 : 0);              // 100000 .. 1000000
+            if (m >= 1000000) { m = 100000; ++e10; }
+            char d[6];
+            for (int k = 5; k >= 0; --k) { d[k] = (char)('0' + m % 10); m /= 10; }
+            int nd = 6;
+            while (nd > 1 && d[nd - 1] == '0') --nd;                          // %g drops trailing zeros
+            if (std::signbit(v)) *p++ = '-';
+            if (e10 < -4 || e10 >= 6) {                                       // d[.ddddd]e+XX
+                *p++ = d[0];
+                if (nd > 1) { *p++ = '.'; for (int k = 1; k < nd; ++k) *p++ = d[k]; }
+                *p++ = 'e';
+                int x = e10;
+                if (x < 0) { *p++ = '-'; x = -x; } else *p++ = '+';
+                if (x >= 100) { *p++ = (char)('0' + x / 100); x %= 100; }
+                *p++ = (char)('0' + x / 10);
+                *p++ = (char)('0' + x % 10);
+            } else if (e10 >= 0) {                                            // ddd[.ddd]
+                for (int k = 0; k <= e10; ++k) *p++ = k < nd ? d[k] : '0';
+                if (nd > e10 + 1) { *p++ = '.'; for (int k = e10 + 1; k < nd; ++k) *p++ = d[k]; }
+            } else {                                                          // 0.000ddd
+                *p++ = '0'; *p++ = '.';
+                for (int k = -1; k > e10; --k) *p++ = '0';
+                for (int k = 0; k < nd; ++k) *p++ = d[k];
+            }
+            return p;
+        }
+    }
+    return std::to_chars(p, end, v, std::chars_format::general, 6).ptr;
+}
+
+static inline char* put_g(char* p, char* end, double v)
+{
+    p = put_g_chars(p, end, v);
+    *p = ' ';
+    return p + 1;
+}
+
+// The lines of grid points [g0, g1).
+static void format_range(const double* P, std::ptrdiff_t pstride, int ncoord, const std::vector<const double*>& cols,
+                         const std::vector<int>& ncomp, const std::vector<int>& comps, std::size_t g0, std::size_t g1, std::string& out)
+{
+    out.clear();
+    out.reserve((g1 - g0) * (6 + 2 * 20 + 14 * cols.size()));
+    // coordinates repeat heavily on Cartesian grids (every x ny times in a row, every y once per row): a small
+    // direct-mapped cache of their strings, keyed on the bit pattern
+    struct Slot { std::uint64_t bits; unsigned char len; char txt[30]; };
+    constexpr std::size_t NSLOT = 4096;
+    std::vector<Slot> cache(NSLOT, Slot{ ~std::uint64_t(0), 0, { 0 } });     // all-ones is a NaN pattern: formatted uncached
+    char buf[64];
+    for (std::size_t g = g0; g < g1; ++g) {
+        out += "1 ";
+        for (int k = 0; k < ncoord; ++k) {
+            const double c = P[g * pstride + k];
+            std::uint64_t bits;
+            std::memcpy(&bits, &c, 8);
+            Slot& sl = cache[(std::size_t)((bits * 0x9E3779B97F4A7C15ull) >> 52)];
+            if (sl.bits != bits || bits == ~std::uint64_t(0)) {
+                const std::string r = repr_double(c);
+                if (r.size() + 1 <= sizeof sl.txt) {
+                    sl.bits = bits;
+                    sl.len = (unsigned char)(r.size() + 1);
+                    std::memcpy(sl.txt, r.data(), r.size());
+                    sl.txt[r.size()] = ' ';
+                } else {
+                    out += r;
+                    out += ' ';
+                    continue;
+                }
+            }
+            out.append(sl.txt, sl.len);
+        }
+        char* p = buf;
+        for (std::size_t f = 0; f < cols.size(); ++f) {
+            p = put_g(p, buf + sizeof buf, cols[f][g * ncomp[f] + comps[f]]);
+            if (p > buf + 40) { out.append(buf, (std::size_t)(p - buf)); p = buf; }
+        }
+        *p++ = '\n';
+        out.append(buf, (std::size_t)(p - buf));
+    }
+}
+
+// The frame's lines for points [0, G) as one string: the grid is cut into contiguous chunks, one per host thread, and the
+// chunks are concatenated in order -- the same bytes as the reference's per-point loop (io.py:112-128).
+static py::bytes format_field_frame_impl(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                                         const std::vector<int>& comps, int nthreads)
 {
     if (points.ndim() != 2 || points.shape(1) < 3) throw std::invalid_argument("[ERROR] points must be (G,3)");
     if (fields.size() != comps.size()) throw std::invalid_argument("[ERROR] one component index per field expected");
     const std::size_t G = (std::size_t)points.shape(0);
+    std::vector<const double*> cols;
+    std::vector<int> ncomp;
     for (std::size_t f = 0; f < fields.size(); ++f) {
         if (!fields[f] || fields[f]->npoints != G) throw std::invalid_argument("[ERROR] field size does not match the grid");
         if (comps[f] < 0 || comps[f] >= fields[f]->ncomp) throw std::invalid_argument("[ERROR] component index out of range");
+        cols.push_back(fields[f]->val.data());
+        ncomp.push_back(fields[f]->ncomp);
     }
-    auto P = points.unchecked<2>();
+    py::array_t<double, py::array::c_style | py::array::forcecast> pts(points);
+    const double* P = pts.data();
+    const std::ptrdiff_t pstride = pts.shape(1);
+    const int ncoord = dim == 3 ? 3 : 2;
+    int nt = nthreads > 0 ? nthreads : (int)std::thread::hardware_concurrency();
+    nt = std::max(1, std::min<int>({ nt, 64, (int)(G / 16384) + 1 }));
+    std::vector<std::string> parts((std::size_t)nt);
+    const bool dbg = std::getenv("PGT_FMT_DEBUG") != nullptr;
+    auto T0 = std::chrono::steady_clock::now();
+    {
+        py::gil_scoped_release nogil;
+        std::vector<std::thread> th;
+        for (int t = 1; t < nt; ++t)
+            th.emplace_back([&, t] { format_range(P, pstride, ncoord, cols, ncomp, comps, G * t / nt, G * (t + 1) / nt, parts[(std::size_t)t]); });
+        format_range(P, pstride, ncoord, cols, ncomp, comps, 0, G / nt, parts[0]);
+        for (auto& x : th) x.join();
+    }
+    auto T1 = std::chrono::steady_clock::now();
+    std::size_t total = 0;
+    for (auto& s : parts) total += s.size();
     std::string out;
-    out.reserve(G * (24 + 2 * 20 + 14 * fields.size()));
-    // coordinates repeat heavily on Cartesian grids: memoise the last strings per axis
-    double last[3] = { NAN, NAN, NAN };
-    std::string lasts[3];
-    char buf[40];
-    for (std::size_t g = 0; g < G; ++g) {
-        out += "1 ";
-        for (int k = 0; k < (dim == 3 ? 3 : 2); ++k) {
-            const double c = P(g, k);
-            if (!(c == last[k]) || std::signbit(c) != std::signbit(last[k])) { last[k] = c; lasts[k] = repr_double(c); }
-            out += lasts[k];
-            out += ' ';
-        }
-        for (std::size_t f = 0; f < fields.size(); ++f) {
-            const int n = std::snprintf(buf, sizeof buf, "%g ", fields[f]->val[g * fields[f]->ncomp + comps[f]]);
-            out.append(buf, (std::size_t)n);
-        }
-        out += '\n';
-    }
-    return out;
+    out.reserve(total);
+    for (auto& s : parts) out += s;
+    auto T2 = std::chrono::steady_clock::now();
+    py::bytes res(out);
+    if (dbg) std::fprintf(stderr, "format: %d threads, ranges %.1f ms, concat %.1f ms, bytes %.1f ms\n", nt,
+                          std::chrono::duration<double, std::milli>(T1 - T0).count(), std::chrono::duration<double, std::milli>(T2 - T1).count(),
+                          std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - T2).count());
+    return res;
+}
+
+static std::string format_field_frame(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                                      const std::vector<int>& comps)
+{
+    return std::string(format_field_frame_impl(points, dim, fields, comps, 0));
 }
 
 void export_format(py::module_& m)
 {
     m.def("repr_double", &repr_double);
     m.def("ostream_double", &ostream_double);
+    m.def("ostream_double_fast", &ostream_double_fast);
+    m.def("ostream_double_fast_check", [](py::array_t<double, py::array::c_style | py::array::forcecast> a) {
+        // number of values whose fast formatting differs from snprintf("%g") (tests: must be 0)
+        long long bad = 0;
+        char b1[48], b2[48];
+        for (py::ssize_t i = 0; i < a.size(); ++i) {
+            const int n1 = std::snprintf(b1, sizeof b1, "%g", a.data()[i]);
+            const int n2 = (int)(put_g_chars(b2, b2 + sizeof b2, a.data()[i]) - b2);
+            if (n1 != n2 || std::memcmp(b1, b2, (std::size_t)n1)) ++bad;
+        }
+        return bad;
+    });
     m.def("format_field_frame", &format_field_frame, py::arg("points"), py::arg("dim"), py::arg("fields"), py::arg("components"));
+    // same lines as bytes, with an explicit thread count (0: all host threads; 1: the serial reference for the tests)
+    m.def("format_field_frame_bytes", &format_field_frame_impl, py::arg("points"), py::arg("dim"), py::arg("fields"), py::arg("components"),
+          py::arg("nthreads") = 0);
 }
 
 }  // namespace pgt_host

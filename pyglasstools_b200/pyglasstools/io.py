@@ -70,11 +70,16 @@ class logfile(object):
 
 class fieldlogger(object):
 
-    def __init__(self, keyword, names, solver):
+    def __init__(self, keyword, names, solver, binary=False):
+        """``binary=True`` (additive extension, off by default): besides the reference's text file, every frame's
+        requested columns are saved at full precision as ``<keyword>.frame<N>[.rank<r>].npy`` (rows = this rank's grid
+        points, columns = x, y[, z], then the requested components in the order of ``names``)."""
         self.__obs_names = names
         _require(solver is not None, "User must specify solver object!")
         _require(names is not None, "User must specify list of observables to save!")
         self.solver = solver
+        self.keyword = keyword
+        self.binary = bool(binary)
         loggers_list.append(self)
         self.field_obs = irvingkirkwood.initialize_field(self.__obs_names, pyglasstools.get_sysdata().pysimbox.dim,
                                                          self.solver.gridpoints)
@@ -93,6 +98,12 @@ class fieldlogger(object):
         dim = pyglasstools.get_sysdata().pysimbox.dim
         fields, comps = self._columns(dim)
         self.file.write_shared(_pyglasstools.format_field_frame(self.solver.gridpoints, dim, fields, comps))
+        if self.binary:
+            import numpy as np
+            pts = np.asarray(self.solver.gridpoints, dtype=np.float64)[:, :(3 if dim == 3 else 2)]
+            cols = [f.values()[:, c] for f, c in zip(fields, comps)]
+            suffix = "" if size == 1 else ".rank{}".format(rank)
+            np.save("{}.frame{}{}.npy".format(self.keyword, frame_num, suffix), np.column_stack([pts] + cols))
 
     def save_perrank_polar(self, frame_num):
         dim = pyglasstools.get_sysdata().pysimbox.dim

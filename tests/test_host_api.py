@@ -284,6 +284,25 @@ def test_text_formats_match_python_and_iostream():
         assert _pyglasstools.ostream_double(float(v)) == "%g" % v
 
 
+def test_fast_g_formatting_equals_printf_including_ties():
+    """The bulk formatter's six-significant-digit route equals printf("%g") -- the C++ ostream default the reference prints
+    with (CoarseGrainedField.h:160-183) -- on random values over 40 decades, on every 6-digit rounding tie and its
+    neighbours, on decade boundaries and on the special values."""
+    from pyglasstools import _pgt_host as h
+    rng = np.random.default_rng(0)
+    a = rng.normal(size=1_000_000) * 10.0 ** rng.integers(-18, 22, 1_000_000)
+    assert h.ostream_double_fast_check(a) == 0
+    k = np.arange(100000, 1000000, 7, dtype=np.float64)
+    ties = np.concatenate([(k + 0.5) * 10.0 ** e for e in range(-12, 12)] + [k * 10.0 ** e for e in (-9, -5, -4, 0, 1, 5, 6, 9)] +
+                          [np.nextafter((k + 0.5) * 1e-3, 0), np.nextafter((k + 0.5) * 1e-3, 1e9)])
+    assert h.ostream_double_fast_check(ties) == 0
+    edge = np.array([0.0, -0.0, 1.0, -1.0, 999999.5, 999999.4999999, 0.0001, 0.00009999995, 1e-5, 123456.5, 1e15, 1e-15, 5e-324,
+                     1e300, np.inf, -np.inf, 99999.95, 9.999995, 0.9999995, 99.99995, 1e20, 9.9999949e19])
+    assert h.ostream_double_fast_check(edge) == 0
+    for v in edge:
+        assert h.ostream_double_fast(float(v)) == "%g" % v
+
+
 def test_field_frame_formatter_equals_reference_loop():
     pts = reference_grid(8.0, 1.0)
     field = _irvingkirkwood.VirialStressField2D("virialstress", "2-TENSOR", False, len(pts))
@@ -296,3 +315,33 @@ def test_field_frame_formatter_equals_reference_loop():
             line += field.gettostring(comp, index)
         want += line + "\n"
     assert got == want
+
+
+def test_multithreaded_formatter_same_bytes_and_binary_dump(tmp_path):
+    """The field text of a frame (io.py:112-128 + CoarseGrainedField.h:160-183) formatted by all host threads is the
+    serial formatter's bytes, which are the reference loop's bytes; values exercise every %g branch."""
+    import time
+    n = 300
+    ax = np.linspace(-150.0, 150.0, n)
+    pts = np.zeros((n * n, 3))
+    pts[:, 0] = np.repeat(ax, n)
+    pts[:, 1] = np.tile(ax, n)
+    rng = np.random.default_rng(9)
+    vals = rng.normal(size=(n * n, 4)) * 10.0 ** rng.integers(-9, 9, (n * n, 4))
+    vals[:7, 0] = [0.0, -0.0, 1.0, 100000.0, 999999.5, 1e-5, 0.0001]
+    field = _irvingkirkwood.VirialStressField2D("virialstress", "2-TENSOR", False, len(pts))
+    field.addGridpoints(pts)
+    field.set_values(vals)
+    t0 = time.perf_counter()
+    serial = _pyglasstools.format_field_frame_bytes(pts, 2, [field, field, field], [0, 3, 2], 1)
+    t1 = time.perf_counter()
+    threaded = _pyglasstools.format_field_frame_bytes(pts, 2, [field, field, field], [0, 3, 2], 0)
+    t2 = time.perf_counter()
+    assert serial == threaded
+    assert _pyglasstools.format_field_frame(pts, 2, [field, field, field], [0, 3, 2]).encode() == serial
+    lines = serial.decode().split("\n")
+    for index in (0, 1, 2, 3, 4, 5, 6, 777, n * n - 1):            # the reference's own per-point route
+        want = "1 {} {} ".format(pts[index][0], pts[index][1]) + "".join(field.gettostring(c, index) for c in (0, 3, 2))
+        assert lines[index] == want
+        assert lines[index].split()[3] == "%g" % vals[index, 0]
+    print("formatter: %d points, serial %.1f ms, threaded %.1f ms" % (n * n, (t1 - t0) * 1e3, (t2 - t1) * 1e3))
