@@ -662,7 +662,7 @@ def main():
     grid_shard = None
     if world > 1 and not grid_mode and not args.no_grid_shard:
         gsteps = max(10, args.steps // 2)
-        for c, _ in lanes[1:]:
+        for c in {id(c): c for c, _ in lanes if c is not ctx}.values():
             c.close()
         # every rank works on rank 0's frames now
         frames0 = make_frames(wl, 0, pool)

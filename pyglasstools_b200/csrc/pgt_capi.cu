@@ -754,12 +754,11 @@ int pgt_build_cells(pgt_ctx* ctx)
     stage_begin(ctx, PGT_STAGE_CELLS);
     ENSURE(ctx->cell_of, sizeof(int) * (size_t)std::max<long long>(N, 1));
     ENSURE(ctx->cell_count, sizeof(int) * ((size_t)ncells + 1));
-    ENSURE(ctx->cell_fill, sizeof(int) * (size_t)ncells);
+    ENSURE(ctx->cell_fill, sizeof(int) * (size_t)std::max<long long>(N, 1));   // per particle: arrival rank in its cell
     ENSURE(ctx->sorted_orig, sizeof(int) * (size_t)std::max<long long>(N, 1));
     ENSURE(ctx->scan_scratch, sizeof(int) * (size_t)pgt_scan_scratch_ints(std::max<long long>(ncells, N) + 1));
     ENSURE(ctx->eflags, sizeof(int) * 4);
     CK(cudaMemsetAsync(ctx->cell_count.p, 0, sizeof(int) * ((size_t)ncells + 1), ctx->stream));
-    CK(cudaMemsetAsync(ctx->cell_fill.p, 0, sizeof(int) * (size_t)ncells, ctx->stream));
     if (!ctx->eflags_init) { CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream)); ctx->eflags_init = true; }
     CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 2, ctx->stream));      // [0] stage flags; [2] is the sticky word
 
@@ -767,13 +766,12 @@ int pgt_build_cells(pgt_ctx* ctx)
     ctx->culled = shard_slab(ctx, c, &slab_lo, &slab_hi);
     ctx->slab_lo = slab_lo;
     ctx->slab_hi = slab_hi;
-    pgt_launch_wrap_count(ctx->src_pos, ctx->is_f32, N, ctx->box, c, ctx->cell_of.as<int>(), ctx->cell_count.as<int>(),
+    pgt_launch_wrap_count(ctx->src_pos, ctx->is_f32, N, ctx->box, c, ctx->cell_of.as<int>(), ctx->cell_fill.as<int>(), ctx->cell_count.as<int>(),
                           ctx->eflags.as<int>(), ctx->culled ? 1 : 0, slab_lo, slab_hi, ctx->stream, &ctx->launches);
     pgt_launch_scan_exclusive(ctx->cell_count.as<int>(), ctx->cell_count.as<int>(), (long long)ncells + 1,
                               ctx->scan_scratch.as<int>(), ctx->stream, &ctx->launches);
-    pgt_launch_scatter_ids(ctx->cell_of.as<int>(), N, ctx->cell_count.as<int>(), ctx->cell_fill.as<int>(),
+    pgt_launch_scatter_ids(ctx->cell_of.as<int>(), ctx->cell_fill.as<int>(), N, ctx->cell_count.as<int>(),
                            ctx->sorted_orig.as<int>(), ctx->stream, &ctx->launches);
-    pgt_launch_cell_sort(ctx->sorted_orig.as<int>(), ctx->cell_count.as<int>(), ncells, ctx->stream, &ctx->launches);
 
     // live count and error flags to the host (mapped memory).  A frame of the same shape as the last one counted does not
     // wait for them: its arrays are sized from that frame's count with a margin, the kernels read the live count on the
@@ -809,10 +807,10 @@ int pgt_build_cells(pgt_ctx* ctx)
         ENSURE(ctx->skxy, sizeof(double) * nl);
         ENSURE(ctx->skyy, sizeof(double) * nl);
     }
-    pgt_launch_gather_sorted(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box,
-                             ctx->sorted_orig.as<int>(), ctx->n_live, ctx->cell_count.as<int>() + ncells, ctx->sx.as<double>(), ctx->sy.as<double>(),
-                             ctx->sxy.as<double2>(), ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr, kin ? ctx->skxy.as<double>() : nullptr,
-                             kin ? ctx->skyy.as<double>() : nullptr, ctx->stream, &ctx->launches);
+    pgt_launch_cell_sort_gather(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box,
+                                ctx->sorted_orig.as<int>(), ctx->cell_count.as<int>(), ncells, ctx->n_live, ctx->sx.as<double>(), ctx->sy.as<double>(),
+                                ctx->sxy.as<double2>(), ctx->sd.as<double>(), kin ? ctx->skxx.as<double>() : nullptr,
+                                kin ? ctx->skxy.as<double>() : nullptr, kin ? ctx->skyy.as<double>() : nullptr, ctx->stream, &ctx->launches);
     CK(cudaGetLastError());
     if (ctx->raw_cur >= 0) {                                 // stage 1 was the last reader of the raw frame
         CK(cudaEventRecord(ctx->ev_raw_free[ctx->raw_cur], ctx->stream));

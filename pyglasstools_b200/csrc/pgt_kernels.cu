@@ -70,8 +70,8 @@ __device__ __forceinline__ bool load_wrapped(const void* pos, long long i, const
 // the shard.  The slab already includes everything the shard's tiles can reach (pgt_build_cells).
 template <bool F32>
 __global__ void __launch_bounds__(256) k_wrap_count(const void* __restrict__ pos, long long N, PgtBox box, PgtCells cells,
-                                                    int* __restrict__ cell_of, int* __restrict__ cell_count, int* eflags,
-                                                    int slab_on, double slab_lo, double slab_hi)
+                                                    int* __restrict__ cell_of, int* __restrict__ cell_slot, int* __restrict__ cell_count,
+                                                    int* eflags, int slab_on, double slab_lo, double slab_hi)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
@@ -87,20 +87,22 @@ __global__ void __launch_bounds__(256) k_wrap_count(const void* __restrict__ pos
             const int cx = cell_coord(x, box.lo[0], cells.inv_cwx, cells.ncx);
             const int cy = cell_coord(y, box.lo[1], cells.inv_cwy, cells.ncy);
             c = cy * cells.ncx + cx;
-            atomicAdd(&cell_count[c], 1);
+            // the histogram's atomic also hands out this particle's arrival rank in its cell: the scatter after the scan
+            // needs no second atomic pass
+            cell_slot[i] = atomicAdd(&cell_count[c], 1);
         }
     }
     cell_of[i] = c;
 }
 
-void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
+void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of, int* cell_slot,
                            int* cell_count, int* eflags, int slab_on, double slab_lo, double slab_hi, cudaStream_t st,
                            PgtLaunchCounter* lc)
 {
     if (N <= 0) return;
     const int blocks = (int)((N + 255) / 256);
-    if (is_f32) k_wrap_count<true><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags, slab_on, slab_lo, slab_hi);
-    else k_wrap_count<false><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_count, eflags, slab_on, slab_lo, slab_hi);
+    if (is_f32) k_wrap_count<true><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_slot, cell_count, eflags, slab_on, slab_lo, slab_hi);
+    else k_wrap_count<false><<<blocks, 256, 0, st>>>(pos, N, box, cells, cell_of, cell_slot, cell_count, eflags, slab_on, slab_lo, slab_hi);
     lc->n++;
 }
 
@@ -322,33 +324,42 @@ void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* tile_s
 
 // ------------------------------------------------------------------------------------------
 // Stage 1b: counting-sort scatter of particle ids, per-cell ordering, gather into sorted SoA
-__global__ void __launch_bounds__(256) k_scatter_ids(const int* __restrict__ cell_of, long long N, const int* __restrict__ cell_start,
-                                                     int* __restrict__ cell_fill, int* __restrict__ sorted_orig)
+__global__ void __launch_bounds__(256) k_scatter_ids(const int* __restrict__ cell_of, const int* __restrict__ cell_slot, long long N,
+                                                     const int* __restrict__ cell_start, int* __restrict__ sorted_orig)
 {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= N) return;
     const int c = cell_of[i];
     if (c < 0) return;
-    const int slot = cell_start[c] + atomicAdd(&cell_fill[c], 1);
-    sorted_orig[slot] = (int)i;
+    sorted_orig[__ldg(cell_start + c) + cell_slot[i]] = (int)i;      // arrival rank taken at count time (k_wrap_count)
 }
 
-void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_start, int* cell_fill, int* sorted_orig,
+void pgt_launch_scatter_ids(const int* cell_of, const int* cell_slot, long long N, const int* cell_start, int* sorted_orig,
                             cudaStream_t st, PgtLaunchCounter* lc)
 {
     if (N <= 0) return;
-    k_scatter_ids<<<(int)((N + 255) / 256), 256, 0, st>>>(cell_of, N, cell_start, cell_fill, sorted_orig);
+    k_scatter_ids<<<(int)((N + 255) / 256), 256, 0, st>>>(cell_of, cell_slot, N, cell_start, sorted_orig);
     lc->n++;
 }
 
-// The atomic scatter leaves each cell's members in arrival order; sorting them by original index
-// makes the layout (and therefore every summation order downstream) reproducible run to run.
-__global__ void __launch_bounds__(256) k_cell_sort(int* __restrict__ sorted_orig, const int* __restrict__ cell_start, int ncells)
+// The scatter leaves each cell's members in arrival order; sorting them by original index makes the layout (and
+// therefore every summation order downstream) reproducible run to run.  One thread per cell sorts its (usually one or
+// two) members and, in the same pass, gathers them into the sorted structure of arrays: the ids are read once, the
+// sorted arrays are written by consecutive threads in (nearly) consecutive places.
+template <bool F32>
+__global__ void __launch_bounds__(256) k_cell_sort_gather(const void* __restrict__ pos, const void* __restrict__ diam,
+                                                          const void* __restrict__ mass, const void* __restrict__ vel, PgtBox box,
+                                                          int* __restrict__ sorted_orig, const int* __restrict__ cell_start, int ncells,
+                                                          int n_cap, double* __restrict__ sx, double* __restrict__ sy, double2* __restrict__ sxy,
+                                                          double* __restrict__ sd, double* __restrict__ skxx, double* __restrict__ skxy,
+                                                          double* __restrict__ skyy)
 {
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncells) return;
-    const int b = cell_start[c], e = cell_start[c + 1];
-    for (int i = b + 1; i < e; ++i) {
+    // n_cap: particles the sorted arrays hold (the live count, or last frame's plus a margin when the host did not wait
+    // for this frame's: an overflow is reported through the sticky error word, never written past the arrays)
+    const int b = cell_start[c], e = min(cell_start[c + 1], n_cap);
+    for (int i = b + 1; i < e; ++i) {                        // insertion sort: cells hold a handful of particles
         const int key = sorted_orig[i];
         int j = i - 1;
         while (j >= b && sorted_orig[j] > key) {
@@ -357,52 +368,34 @@ __global__ void __launch_bounds__(256) k_cell_sort(int* __restrict__ sorted_orig
         }
         sorted_orig[j + 1] = key;
     }
-}
-
-void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc)
-{
-    k_cell_sort<<<(ncells + 255) / 256, 256, 0, st>>>(sorted_orig, cell_start, ncells);
-    lc->n++;
-}
-
-template <bool F32>
-__global__ void __launch_bounds__(256) k_gather_sorted(const void* __restrict__ pos, const void* __restrict__ diam,
-                                                       const void* __restrict__ mass, const void* __restrict__ vel, PgtBox box,
-                                                       const int* __restrict__ sorted_orig, int n_live, const int* __restrict__ n_live_dev,
-                                                       double* __restrict__ sx,
-                                                       double* __restrict__ sy, double2* __restrict__ sxy, double* __restrict__ sd,
-                                                       double* __restrict__ skxx, double* __restrict__ skxy, double* __restrict__ skyy)
-{
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    // n_live is the host's bound (exact, or last frame's count with a margin when the host did not wait for this frame's
-    // count); the live count itself sits in device memory
-    if (p >= n_live || p >= __ldg(n_live_dev)) return;
-    const long long i = sorted_orig[p];
-    double x, y;
-    load_wrapped<F32>(pos, i, box, x, y, nullptr);
-    sx[p] = x;
-    sy[p] = y;
-    sxy[p] = make_double2(x, y);                 // 16-byte rows: what the quad gather's bulk copies move
-    sd[p] = ld_real<F32>(diam, i);
-    if (skxx) {
-        const double m = mass ? ld_real<F32>(mass, i) : 1.0;
-        double vx = 0.0, vy = 0.0;
-        if (vel) { vx = ld_real<F32>(vel, 3 * i); vy = ld_real<F32>(vel, 3 * i + 1); }
-        // KineticStress::compute (ListofCommonObservables.h:131-142): m * v[a] * v[b]
-        skxx[p] = m * vx * vx;
-        skxy[p] = m * vx * vy;
-        skyy[p] = m * vy * vy;
+    for (int p = b; p < e; ++p) {
+        const long long i = sorted_orig[p];
+        double x, y;
+        load_wrapped<F32>(pos, i, box, x, y, nullptr);
+        sx[p] = x;
+        sy[p] = y;
+        sxy[p] = make_double2(x, y);                         // 16-byte rows: what the quad gather's bulk copies move
+        sd[p] = ld_real<F32>(diam, i);
+        if (skxx) {
+            const double m = mass ? ld_real<F32>(mass, i) : 1.0;
+            double vx = 0.0, vy = 0.0;
+            if (vel) { vx = ld_real<F32>(vel, 3 * i); vy = ld_real<F32>(vel, 3 * i + 1); }
+            // KineticStress::compute (ListofCommonObservables.h:131-142): m * v[a] * v[b]
+            skxx[p] = m * vx * vx;
+            skxy[p] = m * vx * vy;
+            skyy[p] = m * vy * vy;
+        }
     }
 }
 
-void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, const int* n_live_dev, double* sx, double* sy, double2* sxy, double* sd,
-                              double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
+void pgt_launch_cell_sort_gather(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
+                                 int* sorted_orig, const int* cell_start, int ncells, int n_cap, double* sx, double* sy, double2* sxy,
+                                 double* sd, double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc)
 {
-    if (n_live <= 0) return;
-    const int blocks = (n_live + 255) / 256;
-    if (is_f32) k_gather_sorted<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, n_live_dev, sx, sy, sxy, sd, skxx, skxy, skyy);
-    else k_gather_sorted<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, n_live, n_live_dev, sx, sy, sxy, sd, skxx, skxy, skyy);
+    if (ncells <= 0 || n_cap <= 0) return;
+    const int blocks = (ncells + 255) / 256;
+    if (is_f32) k_cell_sort_gather<true><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, cell_start, ncells, n_cap, sx, sy, sxy, sd, skxx, skxy, skyy);
+    else k_cell_sort_gather<false><<<blocks, 256, 0, st>>>(pos, diam, mass, vel, box, sorted_orig, cell_start, ncells, n_cap, sx, sy, sxy, sd, skxx, skxy, skyy);
     lc->n++;
 }
 

@@ -1,7 +1,7 @@
 // pgt_kernels.cuh -- hand-written sm_100a kernels for the IK / thermo pair-sum path.
 //
 // Stage map (BASELINE.json north_star):
-//   0/1  k_wrap_count, scan, k_scatter_ids, k_cell_sort, k_gather_sorted   (cell list, counting sort)
+//   0/1  k_wrap_count (histogram + arrival rank), scan, k_scatter_ids, k_cell_sort_gather   (cell list, counting sort)
 //   2/3  k_bonds_find<MODEL> + scan + k_bonds_fill_flat<MODEL>             (pair force + compacted half-bonds)
 //   4/5  k_ik_quad (Cartesian grids, virial field), k_ik_gather2 (any point list, local fields), k_ik_adaptive, k_ik_elastic
 //   6    k_thermo_pairs<MODEL>, k_thermo_final                             (global virial / energy / Born / kinetic)
@@ -102,17 +102,17 @@ struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 
 struct PgtLaunchCounter { long long n; };
 
 // slab_on: drop particles whose wrapped x lies outside [slab_lo, slab_hi] under every periodic image (grid-point sharding)
-void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of,
+void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of, int* cell_slot,
                            int* cell_count, int* eflags, int slab_on, double slab_lo, double slab_hi, cudaStream_t st,
                            PgtLaunchCounter* lc);
 void pgt_launch_scan_exclusive(const int* in, int* out, long long n, int* block_sums, cudaStream_t st, PgtLaunchCounter* lc);
 long long pgt_scan_scratch_ints(long long n);
-void pgt_launch_scatter_ids(const int* cell_of, long long N, const int* cell_start, int* cell_fill, int* sorted_orig,
+void pgt_launch_scatter_ids(const int* cell_of, const int* cell_slot, long long N, const int* cell_start, int* sorted_orig,
                             cudaStream_t st, PgtLaunchCounter* lc);
-void pgt_launch_cell_sort(int* sorted_orig, const int* cell_start, int ncells, cudaStream_t st, PgtLaunchCounter* lc);
-void pgt_launch_gather_sorted(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
-                              const int* sorted_orig, int n_live, const int* n_live_dev, double* sx, double* sy, double2* sxy, double* sd,
-                              double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
+// per cell: members ordered by original index, then gathered (promoted, wrapped) into the sorted structure of arrays
+void pgt_launch_cell_sort_gather(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box,
+                                 int* sorted_orig, const int* cell_start, int ncells, int n_cap, double* sx, double* sy, double2* sxy,
+                                 double* sd, double* skxx, double* skxy, double* skyy, cudaStream_t st, PgtLaunchCounter* lc);
 // mode 0: count force-carrying half-bonds per particle into counts[n+1]; mode 1: fill the CSR arrays;
 // mode 2/3: same for plain neighbours within max_rcut (export only);
 // mode 4: count AND keep the neighbours (nbr_j = [PGT_NB_SLOTS][n] scratch, out.j = error-flag word, out.b = the

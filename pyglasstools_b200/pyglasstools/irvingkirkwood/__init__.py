@@ -80,11 +80,12 @@ class ikcalculator(_ikbase):
             chunk[:, 0] = points[g // nmax]
             chunk[:, 1] = points[g % nmax]
         self.gridpoints = chunk
-        self._chunk_id = id(chunk)
+        self._chunk_copy = chunk.copy()          # the lattice as generated: an in-place edit of gridpoints is noticed
         self._finish(cgfunc)
 
     def run(self):
-        if id(self.gridpoints) == self._chunk_id:
+        gp = self.gridpoints
+        if isinstance(gp, np.ndarray) and gp.shape == self._chunk_copy.shape and np.array_equal(gp, self._chunk_copy):
             # same points, but the device generates them from the axis instead of reading G x 3 doubles
             self.calculator.compute_cartesian(self._axis, self._axis, self._g0, self._g1)
         else:
