@@ -650,6 +650,43 @@ def test_deferred_counts_same_bits_and_late_errors(orc, fixture_frames):
         assert np.array_equal(a, b)
 
 
+def test_two_contexts_on_one_device_keep_their_own_quadrature_rules(orc, fixture_frames):
+    """Gauss-Legendre tables are per context (kernel arguments / per-context device buffers), never per device: two contexts
+    with orders 5 and 7 -- and a third switched to the adaptive rule, which installs a 1-point table -- used in turn on
+    one GPU each integrate with their own rule."""
+    pos, diam, box = fixture_frames.position(150), fixture_frames.diameter, fixture_frames.box
+    P = orc.potential("poly12")
+    S = orc.System(box, pos, diam)
+    L = float(box[0])
+    axis = synth.linspace_axis(L, 40)
+    grid = np.zeros((1600, 3)); grid[:, 0] = np.repeat(axis, 40); grid[:, 1] = np.tile(axis, 40)
+    ctxs = {}
+    for order in (5, 7):
+        c = _capi.Context(0)
+        c.set_potential("poly12", P.scaled_rcut, orc.pot_params(P))
+        c.set_max_rcut(S.max_rcut(P))
+        c.set_cg("octic", 2.0, order)
+        c.set_grid_cartesian(axis, axis)
+        ctxs[order] = c
+    third = _capi.Context(0)
+    third.set_potential("poly12", P.scaled_rcut, orc.pot_params(P))
+    third.set_cg("octic", 2.0, 9)
+    want = {order: S.ik(P, orc.cgfunc("octic", 2.0, order), grid)["virial"] for order in (5, 7)}
+    for rep in range(2):
+        for order in (7, 5):
+            c = ctxs[order]
+            c.upload(pos, diam, box); c.build_cells(); c.build_bonds()
+            if rep == 1 and order == 7:
+                third.set_cg_adaptive("octic", 2.0, 1e-9, 1e-9, 50)      # uploads a 1-point rule into ITS context only
+            for variant in (0, 2):
+                c.set_option("ik_variant", variant)
+                c.ik_compute(_capi.OBS_VIRIAL)
+                assert_close(c.ik_download(), want[order])
+    assert np.abs(want[5] - want[7]).max() > 1e-9 * np.abs(want[5]).max()      # the two rules do differ
+    for c in list(ctxs.values()) + [third]:
+        c.close()
+
+
 def test_symmetric_packed_readback(gpu_ctx, orc, fixture_frames):
     """pgt_ik_download_sym_async: (xx, xy, yy) per grid point equals columns 0, 1, 3 of the full read-back, and the
     dropped column 2 (yx) is bit-identical to column 1 in the full field."""

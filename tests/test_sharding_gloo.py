@@ -39,6 +39,8 @@ def _worker(rank, world, port, outdir):
     import torch.distributed as dist
     from oracle import orc
     from pyglasstools_b200 import sharding
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import dist_helpers
     dist.init_process_group("gloo", rank=rank, world_size=world)
     z = np.load(os.path.join(ROOT, "tests", "golden", "polydisperse12_frames.npz"))
     pos = np.zeros((1024, 3), np.float32)
@@ -48,11 +50,11 @@ def _worker(rank, world, port, outdir):
     grid, _ = orc.cartesian_grid(float(z["box"][0]), 1.0)            # 31 x 31 = 961 points: ragged over 2 ranks
     g0, g1 = sharding.grid_shards(len(grid), world)[rank]
     local = S.ik(P, cg, grid[g0:g1])["virial"]
-    full = sharding.gather_field(dist, local, len(grid))
+    full = dist_helpers.gather_field(dist, local, len(grid))
     # throughput rule: all units over the slowest rank
-    value = sharding.job_throughput(dist, g1 - g0, 10.0 * (rank + 1))
+    value = dist_helpers.job_throughput(dist, g1 - g0, 10.0 * (rank + 1))
     frames = sharding.frame_shards(7, world, rank)
-    nfr = sharding.reduce_scalar(dist, len(frames), "sum")
+    nfr = dist_helpers.reduce_scalar(dist, len(frames), "sum")
     if rank == 0:
         np.savez(os.path.join(outdir, "out.npz"), full=full, value=value, nfr=nfr)
     dist.barrier()
