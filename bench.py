@@ -805,6 +805,12 @@ def main():
                     oc[key] = fn()
                 except Exception as e:                       # a side measurement must not lose the main line
                     oc[key] = {"error": repr(e)}
+            try:                                             # the Python surface, text output included (child process)
+                res = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "script_rate.py"), "1024"], capture_output=True,
+                                     text=True, timeout=300)
+                oc.update(json.loads(res.stdout.strip().splitlines()[-1]))
+            except Exception as e:
+                oc["script"] = {"error": repr(e)}
             out["other_configs"] = oc
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(wl, frames[0], args)

@@ -15,6 +15,7 @@
 #include <algorithm>
 
 #include "host_common.h"
+#include "host_io.h"
 
 namespace pgt_host {
 
@@ -157,8 +158,8 @@ static void format_range(const double* P, std::ptrdiff_t pstride, int ncoord, co
 
 // The frame's lines for points [0, G) as one string: the grid is cut into contiguous chunks, one per host thread, and the
 // chunks are concatenated in order -- the same bytes as the reference's per-point loop (io.py:112-128).
-static py::bytes format_field_frame_impl(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
-                                         const std::vector<int>& comps, int nthreads)
+static std::vector<std::string> format_field_parts(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                                                   const std::vector<int>& comps, int nthreads)
 {
     if (points.ndim() != 2 || points.shape(1) < 3) throw std::invalid_argument("[ERROR] points must be (G,3)");
     if (fields.size() != comps.size()) throw std::invalid_argument("[ERROR] one component index per field expected");
@@ -178,8 +179,6 @@ static py::bytes format_field_frame_impl(DArray points, int dim, const std::vect
     int nt = nthreads > 0 ? nthreads : (int)std::thread::hardware_concurrency();
     nt = std::max(1, std::min<int>({ nt, 64, (int)(G / 16384) + 1 }));
     std::vector<std::string> parts((std::size_t)nt);
-    const bool dbg = std::getenv("PGT_FMT_DEBUG") != nullptr;
-    auto T0 = std::chrono::steady_clock::now();
     {
         py::gil_scoped_release nogil;
         std::vector<std::thread> th;
@@ -188,18 +187,30 @@ static py::bytes format_field_frame_impl(DArray points, int dim, const std::vect
         format_range(P, pstride, ncoord, cols, ncomp, comps, 0, G / nt, parts[0]);
         for (auto& x : th) x.join();
     }
-    auto T1 = std::chrono::steady_clock::now();
+    return parts;
+}
+
+static py::bytes format_field_frame_impl(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                                         const std::vector<int>& comps, int nthreads)
+{
+    const std::vector<std::string> parts = format_field_parts(points, dim, fields, comps, nthreads);
     std::size_t total = 0;
     for (auto& s : parts) total += s.size();
     std::string out;
     out.reserve(total);
     for (auto& s : parts) out += s;
-    auto T2 = std::chrono::steady_clock::now();
-    py::bytes res(out);
-    if (dbg) std::fprintf(stderr, "format: %d threads, ranges %.1f ms, concat %.1f ms, bytes %.1f ms\n", nt,
-                          std::chrono::duration<double, std::milli>(T1 - T0).count(), std::chrono::duration<double, std::milli>(T2 - T1).count(),
-                          std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - T2).count());
-    return res;
+    return py::bytes(out);
+}
+
+// The same lines straight into the log file: the chunks are written in order as they are, without being joined or
+// handed through Python strings (at G = 1 M that round trip costs more than the formatting).
+static void write_field_frame(std::shared_ptr<LogFile> file, DArray points, int dim,
+                              const std::vector<std::shared_ptr<FieldObservable>>& fields, const std::vector<int>& comps)
+{
+    if (!file) throw std::invalid_argument("[ERROR] write_field_frame: no file");
+    const std::vector<std::string> parts = format_field_parts(points, dim, fields, comps, 0);
+    py::gil_scoped_release nogil;
+    for (auto& s : parts) file->write_shared(s);
 }
 
 static std::string format_field_frame(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
@@ -225,6 +236,7 @@ void export_format(py::module_& m)
         return bad;
     });
     m.def("format_field_frame", &format_field_frame, py::arg("points"), py::arg("dim"), py::arg("fields"), py::arg("components"));
+    m.def("write_field_frame", &write_field_frame, py::arg("file"), py::arg("points"), py::arg("dim"), py::arg("fields"), py::arg("components"));
     // same lines as bytes, with an explicit thread count (0: all host threads; 1: the serial reference for the tests)
     m.def("format_field_frame_bytes", &format_field_frame_impl, py::arg("points"), py::arg("dim"), py::arg("fields"), py::arg("components"),
           py::arg("nthreads") = 0);

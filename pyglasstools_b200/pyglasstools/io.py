@@ -97,7 +97,7 @@ class fieldlogger(object):
         """All lines of this rank's chunk, formatted in one C++ pass (same bytes as the reference's per-point loop)."""
         dim = pyglasstools.get_sysdata().pysimbox.dim
         fields, comps = self._columns(dim)
-        self.file.write_shared(_pyglasstools.format_field_frame(self.solver.gridpoints, dim, fields, comps))
+        _pyglasstools.write_field_frame(self.file, self.solver.gridpoints, dim, fields, comps)
         if self.binary:
             import numpy as np
             pts = np.asarray(self.solver.gridpoints, dtype=np.float64)[:, :(3 if dim == 3 else 2)]
