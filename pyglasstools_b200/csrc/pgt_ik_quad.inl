@@ -38,7 +38,6 @@
 #define IKQ_MAXRUNS (2 * IKQ_MAXROWS)
 #define IKQ_MAX_THREADS 256               // 2 CTAs of 256 threads per SM (shared memory bound): up to 128 registers each
 #define IKQ_SEC 0x8000u                   // list entry: kept from the bond's secondary end (weight 1/2, no far-end test)
-#define IKQ_UNSURE 0x4000u                // list entry, transient: the far-end test fell inside the guard band
 #define IKQ_MAX_NREC 0x1FFF               // a list entry / a particle's record range addresses 13 bits
 #define IKQ_STEP_ROOM 6                   // list slots one walk step may touch (4 primary + 2 secondary)
 
@@ -50,7 +49,9 @@ struct IKQCaps {
     int nrec_cap;                        // half-bond records of the rectangle
     int buf_cap;                         // entries of a thread's buffer: disc particles from the top down, list items from the bottom up
     int buf_stride;                      // 16-bit words between two threads' buffers (2 x odd: conflict-free columns)
+    int rank_bits;                       // bits of a list length
     double r2lo, r2hi;                   // |a + b|^2 <= r2lo: inside; > r2hi: outside; between: exact test
+    double r2keep;                       // phase 2 keeps a secondary item when |a + b|^2 > R^2 - band / 2
     double t1lo, t1hi;                   // the same band for t(1) = |a + b|^2 / R^2
     float r2lo32, r2hi32;                // the band of the single-precision disc test of phase 1 (tile-relative coordinates)
 };
@@ -214,10 +215,19 @@ __device__ __noinline__ void ikq_pass_exact(const PgtIKArgs& A, const IKQStatic&
         const double c0 = fma(pax, pax, pay * pay) * iR2;
         const double c1 = fma(pax, b.x, pay * b.y) * iR2x2;
         const double t1 = (c0 + cf.x) + c1;
-        bool half = (it & IKQ_SEC) != 0u || t1 > caps.t1hi;
-        if (!half && t1 > caps.t1lo) half = !(ikq_exact_far_ends(A, S, l, (int)kk, 1u, 0u, gxp, gyp, nruns) & 1u);
+        // far end clearly outside: one visit (1/2).  Otherwise a secondary item is always decided exactly (far end inside:
+        // the bond is integrated from its primary end, not here), a primary item inside the band too
+        const bool sec = (it & IKQ_SEC) != 0u;
+        double wh = 0.5;
+        if (!(t1 > caps.t1hi)) {
+            if (sec || t1 > caps.t1lo) {
+                const bool in = (ikq_exact_far_ends(A, S, l, (int)kk, 1u, 0u, gxp, gyp, nruns) & 1u) != 0u;
+                wh = sec ? (in ? 0.0 : 0.5) : (in ? 1.0 : 0.5);
+            } else {
+                wh = 1.0;
+            }
+        }
         const double wf = ik_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * cf.y;
-        const double wh = half ? 0.5 : 1.0;
         const double tx = (wf * wh) * b.x, ty = (wf * wh) * b.y;
         axx = fma(tx, b.x, axx);
         axy = fma(tx, b.y, axy);
@@ -478,7 +488,7 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
     // explicit 32-bit shared addresses in the hot loops: one register per table, immediate offsets for the slots
     const unsigned b_addr = ikq_smem(s_b), cf_addr = ikq_smem(s_cf), pos_addr = ikq_smem(s_pos), rng_addr = ikq_smem(s_rng);
     const unsigned own_addr = ikq_smem(s_own), buf_base = ikq_smem(s_buf);
-    const double r2lo = caps.r2lo, r2hi = caps.r2hi, t1lo = caps.t1lo, t1hi = caps.t1hi;
+    const double r2lo = caps.r2keep, t1lo = caps.t1lo, t1hi = caps.t1hi;
     unsigned hp = buf_top - 2u * (unsigned)nh;             // next disc particle to walk (the last one found comes first)
     int ks = 0, ns_rem = 0, kp = 0, np_rem = 0, lcur = 0;
     double ax = 0.0, ay = 0.0;
@@ -492,7 +502,6 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
         //      with a guard band).  Straight-line: slots are written unconditionally and the write pointer moves past
         //      the kept ones.  A vote per step: stop when some buffer is nearly full or every lane has finished
         unsigned wp = buf_addr;                                // my list's write pointer
-        unsigned nu2 = 0u;
         int state;
         do {
             if (ns_rem <= 0 && np_rem <= 0 && hp < buf_top) {
@@ -523,15 +532,13 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
                 const double2 b0 = ikq_lds_f64x2<0>(ba), b1 = ikq_lds_f64x2<16>(ba);
                 const double x0 = ax + b0.x, y0 = ay + b0.y, x1 = ax + b1.x, y1 = ay + b1.y;
                 const double d0 = fma(x0, x0, y0 * y0), d1 = fma(x1, x1, y1 * y1);
-                // kept when the primary end lies outside the disc; inside the guard band: kept for now and marked
-                // (bit 14), decided by the exact test after the loop
+                // kept when the primary end lies outside the disc, or inside the guard band of the test (phase 3 recomputes
+                // the same distance as t(1), notices the band there and has the exact test decide)
                 const unsigned keep = ((d0 > r2lo ? 1u : 0u) | (d1 > r2lo ? 2u : 0u)) & act;
-                const unsigned m0 = d0 <= r2hi ? IKQ_UNSURE : 0u, m1 = d1 <= r2hi ? IKQ_UNSURE : 0u;
-                ikq_sts_u16<0>(wp, (unsigned)ks | IKQ_SEC | m0);
+                ikq_sts_u16<0>(wp, (unsigned)ks | IKQ_SEC);
                 wp += (keep & 1u) << 1;
-                ikq_sts_u16<0>(wp, (unsigned)(ks + 1) | IKQ_SEC | m1);
+                ikq_sts_u16<0>(wp, (unsigned)(ks + 1) | IKQ_SEC);
                 wp += keep & 2u;
-                nu2 |= ((keep & 1u) ? m0 : 0u) | ((keep & 2u) ? m1 : 0u);
                 ks += 2;
                 ns_rem -= 2;
             }
@@ -539,19 +546,6 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
             state = (wp + 2u * IKQ_STEP_ROOM > hp) ? 2 : (idle ? 0 : 1);       // the next step's slots would reach my disc particles
             state = __reduce_max_sync(FULL_MASK, state);
         } while (state == 1);
-        if (nu2) {                                             // rare: exact far-end tests, the list is compacted in place
-            unsigned wq = buf_addr;
-            for (unsigned rp = buf_addr; rp < wp; rp += 2u) {
-                const unsigned e = ikq_lds_u16(rp);
-                bool keep = true;
-                if (e & IKQ_UNSURE) {
-                    const int k = (int)(e & (unsigned)IKQ_MAX_NREC);
-                    keep = !(ikq_exact_far_ends(A, S, (int)s_own[k], k, 1u, 0u, gx, gy, nruns) & 1u);
-                }
-                if (keep) { ikq_sts_u16<0>(wq, e & ~IKQ_UNSURE); wq += 2u; }
-            }
-            wp = wq;
-        }
         const int n = (int)((wp - buf_addr) >> 1);
         __syncwarp();
 
@@ -600,8 +594,11 @@ __global__ void __launch_bounds__(IKQ_MAX_THREADS, 2) k_ik_quad(const __grid_con
                     // far end is inside when t(1) = |a + b|^2 / R^2 <= 1 (inside the guard band the pass is redone with
                     // the exact test)
                     const double t1 = (c0 + cf.x) + c1;
-                    const bool half = (it & IKQ_SEC) != 0u || t1 > t1hi;
-                    unsure_any |= (!half && t1 > t1lo) ? 1u : 0u;
+                    const bool out = t1 > t1hi;
+                    const bool half = (it & IKQ_SEC) != 0u || out;
+                    // inside the band, primary or secondary item alike (phase 2 keeps a secondary item only when its
+                    // primary end is beyond R^2 - band / 2, i.e. beyond t1lo here, so none slips below the band)
+                    unsure_any |= (!out && t1 > t1lo) ? 1u : 0u;
                     const double wf = ik_quadrature<KERNEL, Q>(A, c0, c1, cf.x) * cf.y;
                     const double wh = __hiloint2double(half ? 0x3FE00000 : 0x3FF00000, 0);
                     const double tx = (wf * wh) * b.x, ty = (wf * wh) * b.y;
@@ -732,6 +729,7 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
                     caps->nrec_cap = (int)nrec;
                     caps->buf_cap = (int)lc;
                     caps->buf_stride = (int)stride;
+                    caps->rank_bits = lc < 64 ? 6 : 8;
                     *dyn_bytes = (size_t)(base + nrec * 34 + 15) & ~(size_t)15;
                 }
             }
@@ -743,6 +741,7 @@ static bool ikq_pick_caps(const PgtIKArgs& a, IKQCaps* caps, size_t* dyn_bytes)
     const double band = std::max(1e-9 * a.cg.rcutsq, 1e-11 * R * M);
     caps->r2lo = a.cg.rcutsq - band;
     caps->r2hi = a.cg.rcutsq + band;
+    caps->r2keep = a.cg.rcutsq - 0.5 * band;
     caps->t1lo = 1.0 - band * a.inv_rcutsq;
     caps->t1hi = 1.0 + band * a.inv_rcutsq;
     // guard band of phase 1's single-precision test: coordinates relative to the tile's corner are at most Mt in
