@@ -142,6 +142,18 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
  * then Dim^4 Born tensor (col-major flat); all already multiplied by 1/vol.  Entries whose
  * observable is not in obs_mask are 0.  out must hold 2*Dim^2 + 1 + Dim^4 doubles.              */
 int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, same kernels, same
+ * block partition and same `out` layout as pgt_thermo_compute, but the per-block partial sums and the reduced result
+ * live in one file-scope `static __device__` array of the library (PGT_THERMO_STATIC_MAX_BLOCKS * 25 + 32 doubles =
+ * 473 856 bytes, held by every GPU that loads the library until the process exits) instead of the context's device
+ * buffers: the call makes no cudaMalloc, cudaFree or other allocating call.  Frames with more than
+ * PGT_THERMO_STATIC_MAX_PARTICLES live particles are refused with PGT_ERR_ARG (use pgt_thermo_compute).  All contexts
+ * and all calls on a device share the array, which keeps the last call's contents (the call clears what it needs);
+ * calls that overlap on the GPU (two contexts = two streams on one device) race: serialise them.                    */
+#define PGT_THERMO_STATIC_MAX_BLOCKS 2368
+#define PGT_THERMO_STATIC_MAX_PARTICLES 2097152
+int pgt_thermo_compute_static(pgt_ctx* ctx, unsigned obs_mask, double* out);
 /* Particle-sharded thermo sums over GPUs: this ctx sums the pairs (id_i < id_j) visited from part `part` of `nparts`
  * equal shares of the sorted particles; the nparts partial results add up to pgt_thermo_compute's (sum them with
  * pgt_comm_allreduce_sum: the role of MPI reductions the reference never needed, ThermoCalculator being serial).

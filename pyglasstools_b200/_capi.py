@@ -27,7 +27,7 @@ EXPORTED = [
     "pgt_kernel_launches", "pgt_pair_eval", "pgt_cg_delta", "pgt_cg_bond", "pgt_fp64_peak_probe",
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
-    "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep",
+    "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep", "pgt_thermo_compute_static",
 ]
 
 _lib = None
@@ -101,6 +101,7 @@ def lib():
         L.pgt_ik_download.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
         L.pgt_ik_device_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pgt_thermo_compute.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
+        L.pgt_thermo_compute_static.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
         L.pgt_thermo_elastic.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.pgt_frame_set_displacement.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int64]
         L.pgt_export_bonds.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p,
@@ -277,6 +278,12 @@ class Context:
     def thermo(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
         out = np.zeros(25, np.float64)
         self._ck(lib().pgt_thermo_compute(self._h, int(obs_mask), _dp(out)))
+        return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy())
+
+    def thermo_static(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
+        """pgt_thermo_compute_static: the same sums with the library's static device scratch, no allocation in the call."""
+        out = np.zeros(25, np.float64)
+        self._ck(lib().pgt_thermo_compute_static(self._h, int(obs_mask), _dp(out)))
         return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy())
 
     def set_displacement(self, disp):

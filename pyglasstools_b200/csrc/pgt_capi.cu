@@ -3,6 +3,7 @@
 #include "pgt_kernels.cuh"
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <pthread.h>
 #include <algorithm>
 #include <cmath>
 #include <cstdarg>
@@ -1316,6 +1317,78 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
     CK(cudaStreamSynchronize(ctx->stream));
     const double* h = ctx->h_small;
     // device order: virial 4 | kinetic 4 | energy | born 16  ->  API order (same, documented in the header)
+    for (int k = 0; k < 25; ++k) out[k] = h[k];
+    return PGT_OK;
+}
+
+// ---- pgt_thermo_compute_static: the thermo pair sums with no allocation at all -------------------------------------
+// The per-block partial sums and the reduced result live in ONE file-scope device array instead of the context's
+// cudaMalloc'ed buffers.  Every device that loads this library holds the array until the process exits; every context
+// and every call on a device shares it (calls that overlap on the GPU race) and it keeps the last call's contents.
+#define PGT_STATIC_SCRATCH_DOUBLES (PGT_THERMO_STATIC_MAX_BLOCKS * 25 + 32)     /* partials | result slot (25 used)  */
+static __device__ __align__(256) double g_thermo_static_scratch[PGT_STATIC_SCRATCH_DOUBLES];
+
+// Device code of this file names the array directly: the result slot starts every call at zero.
+static __global__ void __launch_bounds__(32) k_thermo_static_clear()
+{
+    g_thermo_static_scratch[PGT_THERMO_STATIC_MAX_BLOCKS * 25 + threadIdx.x] = 0.0;
+}
+
+namespace {
+// In host code `g_thermo_static_scratch` is a host-side stand-in, not a device address: the address each device holds the
+// array at comes from cudaGetSymbolAddress, asked once per device with that device current.
+constexpr int STATIC_MAX_DEVICES = 64;
+double* g_static_ptr[STATIC_MAX_DEVICES] = {};
+pthread_mutex_t g_static_mu = PTHREAD_MUTEX_INITIALIZER;
+
+int static_scratch_ptr(pgt_ctx* ctx, double** out)
+{
+    if (ctx->device < 0 || ctx->device >= STATIC_MAX_DEVICES) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_static: device %d beyond %d", ctx->device, STATIC_MAX_DEVICES);
+    pthread_mutex_lock(&g_static_mu);
+    double* p = g_static_ptr[ctx->device];
+    cudaError_t e = cudaSuccess;
+    if (!p) {
+        e = cudaSetDevice(ctx->device);
+        if (e == cudaSuccess) e = cudaGetSymbolAddress((void**)&p, g_thermo_static_scratch);
+        if (e == cudaSuccess) g_static_ptr[ctx->device] = p;
+    }
+    pthread_mutex_unlock(&g_static_mu);
+    if (e != cudaSuccess || !p) return fail(ctx, PGT_ERR_CUDA, "cudaGetSymbolAddress(g_thermo_static_scratch) on device %d failed: %s", ctx->device, cudaGetErrorString(e));
+    *out = p;
+    return PGT_OK;
+}
+}  // namespace
+
+int pgt_thermo_compute_static(pgt_ctx* ctx, unsigned obs_mask, double* out)
+{
+    if (ctx) RESOLVE();
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_static: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: cells not built");
+    if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: no pair potential");
+    if (ctx->culled) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: the frame holds a grid shard's particles only (set the whole grid or option slab_cull = 0 and rebuild the cells)");
+    if (ctx->n_live > PGT_THERMO_STATIC_MAX_PARTICLES)
+        return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_static: the frame has %lld live particles, the static scratch serves at most %d (use pgt_thermo_compute)",
+                    (long long)ctx->n_live, PGT_THERMO_STATIC_MAX_PARTICLES);
+    const int blocks = pgt_thermo_blocks(ctx->n_live);
+    if (blocks > PGT_THERMO_STATIC_MAX_BLOCKS)
+        return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_static: %d blocks of partial sums, the static scratch holds %d", blocks, PGT_THERMO_STATIC_MAX_BLOCKS);
+    CK(cudaSetDevice(ctx->device));
+    double* scratch = nullptr;
+    int rc = static_scratch_ptr(ctx, &scratch);
+    if (rc != PGT_OK) return rc;
+    double* result = scratch + (size_t)PGT_THERMO_STATIC_MAX_BLOCKS * 25;
+    const int p_begin = (int)((long long)ctx->n_live * ctx->thermo_part / ctx->thermo_nparts);
+    const int p_end = (int)((long long)ctx->n_live * (ctx->thermo_part + 1) / ctx->thermo_nparts);
+    k_thermo_static_clear<<<1, 32, 0, ctx->stream>>>();
+    ctx->launches.n++;
+    // same kernels, same block partition as pgt_thermo_compute: every block writes all 25 of its partial sums, so the
+    // partials need no clearing
+    pgt_launch_thermo(ctx->pot, frame_view(ctx), ctx->box, ctx->cells, ctx->max_rcut, obs_mask, 1 / ctx->vol, scratch, blocks, result,
+                      p_begin, p_end, ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    pgt_launch_publish(result, 50, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
+    CK(cudaStreamSynchronize(ctx->stream));
+    const double* h = ctx->h_small;
     for (int k = 0; k < 25; ++k) out[k] = h[k];
     return PGT_OK;
 }
