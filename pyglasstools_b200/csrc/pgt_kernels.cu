@@ -508,7 +508,7 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
 // k_bonds_fill_list re-forms dx exactly as the search did (same operands, same operations -> same bits) and writes
 // the records.  Halves the neighbour searches of the count + fill pair above, which stays as the path for frames
 // where some particle has more than PGT_NB_SLOTS bonds.
-template <int MODEL>
+template <int MODEL, int UNR>
 __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
                                                     int* __restrict__ counts, unsigned* __restrict__ nb_list,
                                                     unsigned short* __restrict__ prim_mask, int* __restrict__ eflags)
@@ -555,21 +555,33 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
             fwd_from = dir > 0 ? q : (dir < 0 ? qe : p + 1);
             continue;
         }
-        const double2 r = __ldg(fr.sxy + q);
-        const double dx = r.x - cpx, dy = r.y - cpy;
-        const double rsq = dx * dx + dy * dy;
-        // the particle itself is skipped (IrvingKirkwood.h:97), tested on hits only
-        if (!(rsq > rc2) && q != p) {
-            const double dj = __ldg(fr.sd + q);
-            if (pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) {
-                if (n < PGT_NB_SLOTS) {
-                    nb_list[(size_t)n * fr.n + p] = (unsigned)q | (code << 28);
-                    if (q >= fwd_from) pm |= 1u << n;
+        // UNR candidates of the span per turn: their loads are issued together (the search is bound by the latency of
+        // these loads, not by their bytes); the tests and the hits keep the visiting order
+        const int m = min(qe - q, UNR);
+        double rsqv[UNR];
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const double2 r = __ldg(fr.sxy + (u < m ? q + u : q));
+            const double dx = r.x - cpx, dy = r.y - cpy;
+            rsqv[u] = dx * dx + dy * dy;
+        }
+#pragma unroll
+        for (int u = 0; u < UNR; ++u) {
+            const double rsq = rsqv[u];
+            const int qq = q + u;
+            // the particle itself is skipped (IrvingKirkwood.h:97), tested on hits only
+            if (u < m && !(rsq > rc2) && qq != p) {
+                const double dj = __ldg(fr.sd + qq);
+                if (pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) {
+                    if (n < PGT_NB_SLOTS) {
+                        nb_list[(size_t)n * fr.n + p] = (unsigned)qq | (code << 28);
+                        if (qq >= fwd_from) pm |= 1u << n;
+                    }
+                    ++n;
                 }
-                ++n;
             }
         }
-        ++q;
+        q += m;
     }
     counts[p] = n;
     prim_mask[p] = (unsigned short)pm;
@@ -647,8 +659,17 @@ static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, Pgt
 {
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
-    case 4: k_bonds_find<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, reinterpret_cast<unsigned*>(nbr_j),
-                                                        reinterpret_cast<unsigned short*>(out.b), out.j); break;
+    case 4: {
+        // candidates loaded per turn (developer knob; measured at cfg5: 1: 0.581, 2: 0.577, 3: 0.563, 4: 0.562, 6: 0.597 ms per bond stage)
+        static const int unr = getenv("PGT_FIND_UNROLL") ? atoi(getenv("PGT_FIND_UNROLL")) : 4;
+        unsigned* nb = reinterpret_cast<unsigned*>(nbr_j);
+        unsigned short* pmk = reinterpret_cast<unsigned short*>(out.b);
+        if (unr == 1) k_bonds_find<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, nb, pmk, out.j);
+        else if (unr == 2) k_bonds_find<MODEL, 2><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, nb, pmk, out.j);
+        else if (unr == 3) k_bonds_find<MODEL, 3><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, nb, pmk, out.j);
+        else k_bonds_find<MODEL, 4><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, nb, pmk, out.j);
+        break;
+    }
     case 5: k_bonds_fill_flat<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 6: k_bonds_fill_list<MODEL><<<blocks, 128, 0, st>>>(pot, fr, box, counts, reinterpret_cast<const unsigned*>(nbr_j), out, cscale); break;
     case 0: k_bonds<MODEL, 0><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, out, cscale, nbr_j); break;
