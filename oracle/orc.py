@@ -142,8 +142,9 @@ def refloops_lib():
     return _refloops
 
 
-def ref_ik(box, pos, diam, P, cg_kernel, cg_rcut, order, grid, vel=None, mass=None, obs_mask=1):
-    """IrvingKirkwood::compute (irvingkirkwood/IrvingKirkwood.h:74-110) of the reference itself on `grid` (G x 3)."""
+def ref_ik(box, pos, diam, P, cg_kernel, cg_rcut, order, grid, vel=None, mass=None, obs_mask=1, dim=2, disp=None):
+    """IrvingKirkwood::compute (irvingkirkwood/IrvingKirkwood.h:74-110) of the reference itself on `grid` (G x 3); dim = 3 uses
+    the reference's 3-D typedefs (G x 9 fields, box periodic on all axes); obs_mask bit3 with `disp`: the elastic virial field."""
     L = refloops_lib()
     box = np.ascontiguousarray(np.asarray(box, np.float64)[:3])
     pos = np.ascontiguousarray(pos, np.float64)
@@ -153,21 +154,25 @@ def ref_ik(box, pos, diam, P, cg_kernel, cg_rcut, order, grid, vel=None, mass=No
     grid = np.ascontiguousarray(grid, np.float64)
     prm = np.ascontiguousarray(pot_params(P), np.float64)
     G = len(grid)
-    vir = np.zeros((G, 4)) if obs_mask & 1 else None
-    kin = np.zeros((G, 4)) if obs_mask & 2 else None
+    D2 = dim * dim
+    disp = None if disp is None else np.ascontiguousarray(disp, np.float64)
+    vir = np.zeros((G, D2)) if obs_mask & 1 else None
+    kin = np.zeros((G, D2)) if obs_mask & 2 else None
+    ela = np.zeros((G, D2)) if (obs_mask & 8) and disp is not None else None
     mr, nl = C.c_double(0.0), C.c_int64(0)
     vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
     kid = {"octic": 0, "rect": 1, "mollifier": 2}[cg_kernel]
-    rc = L.ref_ik_compute(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), None, C.c_int(P.model),
-                          C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_int(kid), C.c_double(cg_rcut), C.c_int(order),
-                          C.c_int(0), C.c_double(0.0), C.c_double(0.0), C.c_int(0), C.c_int64(G), vp(grid), C.c_uint(obs_mask),
-                          vp(vir), vp(kin), None, C.byref(mr), C.byref(nl))
+    fn = L.ref_ik_compute if dim == 2 else L.ref_ik_compute3
+    rc = fn(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), vp(disp), C.c_int(P.model),
+            C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_int(kid), C.c_double(cg_rcut), C.c_int(order),
+            C.c_int(0), C.c_double(0.0), C.c_double(0.0), C.c_int(0), C.c_int64(G), vp(grid), C.c_uint(obs_mask),
+            vp(vir), vp(kin), vp(ela), C.byref(mr), C.byref(nl))
     if rc != 0:
         raise RuntimeError("ref_ik_compute failed (%d)" % rc)
-    return dict(virial=vir, kinetic=kin, max_rcut=mr.value, n_live=nl.value)
+    return dict(virial=vir, kinetic=kin, elastic=ela, max_rcut=mr.value, n_live=nl.value)
 
 
-def ref_thermo(box, pos, diam, P, vel=None, mass=None, obs_mask=1 | 4 | 8):
+def ref_thermo(box, pos, diam, P, vel=None, mass=None, obs_mask=1 | 4 | 8, dim=2, disp=None):
     """ThermoCalculator::compute (thermo/ThermoCalculator.h:68-90) of the reference itself; obs_mask bit0 virial,
     bit1 kinetic, bit2 energy, bit3 Born tensor."""
     L = refloops_lib()
@@ -177,14 +182,18 @@ def ref_thermo(box, pos, diam, P, vel=None, mass=None, obs_mask=1 | 4 | 8):
     vel = None if vel is None else np.ascontiguousarray(vel, np.float64)
     mass = None if mass is None else np.ascontiguousarray(mass, np.float64)
     prm = np.ascontiguousarray(pot_params(P), np.float64)
-    out = np.zeros(29)
+    D2, D4 = dim * dim, dim ** 4
+    out = np.zeros(2 * D2 + 1 + D4 + D2)
+    disp = None if disp is None else np.ascontiguousarray(disp, np.float64)
     mr = C.c_double(0.0)
     vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
-    rc = L.ref_thermo_compute(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), None, C.c_int(P.model),
-                              C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_uint(obs_mask), vp(out), C.byref(mr))
+    fn = L.ref_thermo_compute if dim == 2 else L.ref_thermo_compute3
+    rc = fn(vp(box), C.c_int64(len(diam)), vp(pos), vp(vel), vp(diam), vp(mass), vp(disp), C.c_int(P.model),
+            C.c_double(P.scaled_rcut), vp(prm), C.c_int(len(prm)), C.c_uint(obs_mask), vp(out), C.byref(mr))
     if rc != 0:
         raise RuntimeError("ref_thermo_compute failed (%d)" % rc)
-    return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy(), max_rcut=mr.value)
+    return dict(virial=out[0:D2].copy(), kinetic=out[D2:2 * D2].copy(), energy=float(out[2 * D2]),
+                born=out[2 * D2 + 1:2 * D2 + 1 + D4].copy(), elastic=out[2 * D2 + 1 + D4:].copy(), max_rcut=mr.value)
 
 
 # ---------------------------------------------------------------------------

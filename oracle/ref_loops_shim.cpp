@@ -82,6 +82,14 @@ typedef ForceProperty<2, 2, VirialStress> GlobalVirialStress2D;
 typedef ForceProperty<2, 2, ElasticVirialStress> GlobalElasticVirialStress2D;
 typedef LocalProperty<2, 2, KineticStress> GlobalKineticStress2D;
 typedef ForceProperty<4, 2, BornStiffnessTensor> GlobalBornTensor2D;
+typedef ForceField<2, 3, VirialStress> VirialStressField3D;
+typedef ForceField<2, 3, ElasticVirialStress> ElasticVirialStressField3D;
+typedef LocalField<2, 3, KineticStress> KineticStressField3D;
+typedef ForceScalarProperty<3, PotentialEnergy> GlobalPotentialEnergy3D;
+typedef ForceProperty<2, 3, VirialStress> GlobalVirialStress3D;
+typedef ForceProperty<2, 3, ElasticVirialStress> GlobalElasticVirialStress3D;
+typedef LocalProperty<2, 3, KineticStress> GlobalKineticStress3D;
+typedef ForceProperty<4, 3, BornStiffnessTensor> GlobalBornTensor3D;
 
 // ---- GSL stand-in, implemented on the oracle's tables / restatement (liborc.so)
 extern "C" int orc_gl_table(int n, double* x, double* w);
@@ -180,10 +188,10 @@ static std::shared_ptr<CoarseGrainFunction> make_cg(int kernel, double rcut, int
 
 // utils.py:9-22 (simbox: Lz = 1 in 2-D, origin 0) and utils.py:41-69 (ParticleSystem from the frame's arrays)
 static std::shared_ptr<ParticleSystem> make_system(const double* box, int64_t n, const double* pos, const double* vel,
-                                                   const double* diam, const double* mass, const double* disp)
+                                                   const double* diam, const double* mass, const double* disp, int dim = 2)
 {
-    Eigen::Vector3d L(box[0], box[1], 1.0), origin(0, 0, 0);
-    auto sb = std::make_shared<SimBox>(L, origin, 2);
+    Eigen::Vector3d L(box[0], box[1], dim == 2 ? 1.0 : box[2]), origin(0, 0, 0);
+    auto sb = std::make_shared<SimBox>(L, origin, dim);
     std::vector<double> d(diam, diam + n), m(n, 1.0);
     if (mass) m.assign(mass, mass + n);
     std::vector<std::vector<double>> r((size_t)n, std::vector<double>(3)), v((size_t)n, std::vector<double>(3, 0.0));
@@ -267,6 +275,68 @@ int ref_thermo_compute(const double* box, int64_t n, const double* pos, const do
     if (obs_mask & 4u) out29[8] = e->val;
     if (obs_mask & 8u) for (int q = 0; q < 16; ++q) out29[9 + q] = b->val.data()[q];
     if (obs_mask & 16u) for (int q = 0; q < 4; ++q) out29[25 + q] = el->val.data()[q];
+    return 0;
+}
+
+// The same two calculators with the reference's Dim = 3 typedefs (module-irvingkirkwood.cpp:9-13, module-thermo.cpp:8-20); the box is
+// periodic on all three axes (SimBox.cc:33, :41-44).  Field outputs: G x 9 (flat a + 3 b).
+int ref_ik_compute3(const double* box, int64_t n, const double* pos, const double* vel, const double* diam, const double* mass,
+                    const double* disp, int model, double scaled_rcut, const double* params, int nparams, int kernel, double cg_rcut,
+                    int order, int adaptive, double epsrel, double epsabs, int maxiter, int64_t G, const double* grid,
+                    unsigned obs_mask, double* virial, double* kinetic, double* elastic, double* max_rcut_out, int64_t* n_live)
+{
+    auto sys = make_system(box, n, pos, vel, diam, mass, disp, 3);
+    auto pot = make_pot(model, scaled_rcut, params, nparams);
+    auto cg = make_cg(kernel, cg_rcut, order, adaptive, epsrel, epsabs, maxiter);
+    if (!sys || !pot || !cg) return -1;
+    if (n_live) *n_live = (int64_t)sys->particles.size();
+    IrvingKirkwood calc(sys, pot, cg, std::make_shared<MPI::Communicator>());
+    if (max_rcut_out) *max_rcut_out = calc.max_rcut;
+    std::vector<Eigen::Vector3d> pts((size_t)G);
+    for (int64_t g = 0; g < G; ++g) pts[g] = Eigen::Vector3d(grid[3 * g], grid[3 * g + 1], grid[3 * g + 2]);
+    std::shared_ptr<VirialStressField3D> fv;
+    std::shared_ptr<KineticStressField3D> fk;
+    std::shared_ptr<ElasticVirialStressField3D> fe;
+    if (obs_mask & 1u) { fv = std::make_shared<VirialStressField3D>("virialstress", "2-TENSOR", false, (int)G); calc.addObservable(fv); }
+    if (obs_mask & 2u) { fk = std::make_shared<KineticStressField3D>("kineticstress", "2-TENSOR", true, (int)G); calc.addObservable(fk); }
+    if (obs_mask & 8u) { fe = std::make_shared<ElasticVirialStressField3D>("elasticvirialstress", "2-TENSOR", false, (int)G); calc.addObservable(fe); }
+    calc.compute(pts);
+    for (int64_t g = 0; g < G; ++g)
+        for (int q = 0; q < 9; ++q) {
+            if (fv && virial) virial[9 * g + q] = fv->val[g].data()[q];
+            if (fk && kinetic && fk->val[g].size() == 9) kinetic[9 * g + q] = fk->val[g].data()[q];
+            if (fe && elastic) elastic[9 * g + q] = fe->val[g].data()[q];
+        }
+    return 0;
+}
+
+// out: virial[9] | kinetic[9] | energy | born[81] | elastic[9]   (109 doubles)
+int ref_thermo_compute3(const double* box, int64_t n, const double* pos, const double* vel, const double* diam, const double* mass,
+                        const double* disp, int model, double scaled_rcut, const double* params, int nparams, unsigned obs_mask,
+                        double* out109, double* max_rcut_out)
+{
+    auto sys = make_system(box, n, pos, vel, diam, mass, disp, 3);
+    auto pot = make_pot(model, scaled_rcut, params, nparams);
+    if (!sys || !pot) return -1;
+    ThermoCalculator calc(sys, pot);
+    if (max_rcut_out) *max_rcut_out = calc.max_rcut;
+    auto v = std::make_shared<GlobalVirialStress3D>("virialstress", "2-TENSOR", false);
+    auto k = std::make_shared<GlobalKineticStress3D>("kineticstress", "2-TENSOR", true);
+    auto e = std::make_shared<GlobalPotentialEnergy3D>("potentialenergy", "SCALAR", false);
+    auto b = std::make_shared<GlobalBornTensor3D>("borntensor", "4-TENSOR", false);
+    auto el = std::make_shared<GlobalElasticVirialStress3D>("elasticvirialstress", "2-TENSOR", false);
+    if (obs_mask & 1u) calc.addObservable(v);
+    if (obs_mask & 2u) calc.addObservable(k);
+    if (obs_mask & 4u) calc.addObservable(e);
+    if (obs_mask & 8u) calc.addObservable(b);
+    if (obs_mask & 16u) calc.addObservable(el);
+    calc.compute();
+    for (int q = 0; q < 109; ++q) out109[q] = 0.0;
+    if (obs_mask & 1u) for (int q = 0; q < 9; ++q) out109[q] = v->val.data()[q];
+    if (obs_mask & 2u) for (int q = 0; q < 9; ++q) out109[9 + q] = k->val.data()[q];
+    if (obs_mask & 4u) out109[18] = e->val;
+    if (obs_mask & 8u) for (int q = 0; q < 81; ++q) out109[19 + q] = b->val.data()[q];
+    if (obs_mask & 16u) for (int q = 0; q < 9; ++q) out109[100 + q] = el->val.data()[q];
     return 0;
 }
 

@@ -193,6 +193,7 @@ class Context:
         b = (C.c_double * 3)(*[float(x) for x in box[:3]])
         vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
         self._ck(lib().pgt_frame_upload(self._h, vp(pos), vp(diam), vp(mass), vp(vel), int(f32), len(diam), b, dim))
+        self.dim = dim
 
     def upload_part(self, pos_part, diam_part, first, n_total, box, dim=2):
         """This rank's part of a frame (rows [first, first + len(diam_part)) of the N x 3 positions); assemble the frame
@@ -205,12 +206,14 @@ class Context:
         b = (C.c_double * 3)(*[float(x) for x in box[:3]])
         self._ck(lib().pgt_frame_upload_part(self._h, pos_part.ctypes.data_as(C.c_void_p), diam_part.ctypes.data_as(C.c_void_p),
                                              int(f32), int(first), len(diam_part), int(n_total), b, dim))
+        self.dim = dim
 
     def set_device_frame(self, d_pos, d_diam, n, box, is_f32=True, d_mass=None, d_vel=None, dim=2):
         b = (C.c_double * 3)(*[float(x) for x in box[:3]])
         self._ck(lib().pgt_frame_set_device(self._h, C.c_void_p(d_pos), C.c_void_p(d_diam),
                                             C.c_void_p(d_mass) if d_mass else None,
                                             C.c_void_p(d_vel) if d_vel else None, int(is_f32), int(n), b, dim))
+        self.dim = dim
 
     def build_cells(self):
         self._ck(lib().pgt_build_cells(self._h))
@@ -247,7 +250,7 @@ class Context:
 
     def ik_download(self, field=FIELD_VIRIAL, out=None):
         n = self.g1 - self.g0
-        shape = (n,) if field == FIELD_DENSITY else (n, 4)
+        shape = (n,) if field == FIELD_DENSITY else (n, getattr(self, "dim", 2) ** 2)
         if out is None:
             out = np.empty(shape, np.float64)
         self._ck(lib().pgt_ik_download(self._h, int(field), out.ctypes.data_as(C.c_void_p)))
@@ -276,9 +279,11 @@ class Context:
         return p.value, n.value
 
     def thermo(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
-        out = np.zeros(25, np.float64)
+        D = getattr(self, "dim", 2)
+        D2, D4 = D * D, D ** 4
+        out = np.zeros(2 * D2 + 1 + D4, np.float64)
         self._ck(lib().pgt_thermo_compute(self._h, int(obs_mask), _dp(out)))
-        return dict(virial=out[0:4].copy(), kinetic=out[4:8].copy(), energy=float(out[8]), born=out[9:25].copy())
+        return dict(virial=out[0:D2].copy(), kinetic=out[D2:2 * D2].copy(), energy=float(out[2 * D2]), born=out[2 * D2 + 1:].copy())
 
     def thermo_static(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
         """pgt_thermo_compute_static: the same sums with the library's static device scratch, no allocation in the call."""
@@ -292,7 +297,7 @@ class Context:
         self._ck(lib().pgt_frame_set_displacement(self._h, _dp(d), C.c_int64(len(d))))
 
     def thermo_elastic(self):
-        out = np.zeros(4, np.float64)
+        out = np.zeros(getattr(self, "dim", 2) ** 2, np.float64)
         self._ck(lib().pgt_thermo_elastic(self._h, _dp(out)))
         return out
 

@@ -153,6 +153,8 @@ struct pgt_ctx {
     long long n_hb = 0;
     DevBuf cell_of, cell_count, cell_fill, sorted_orig, scan_scratch, eflags;
     DevBuf sx, sy, sxy, sd, skxx, skxy, skyy;
+    DevBuf sz, sm3, svx3, svy3, svz3;   // Dim = 3: wrapped z, mass and velocity components of the sorted particles
+    Pgt3Cells cells3{};
     DevBuf hb_cnt, hb_b, hb_cf, hb_j, hb_pm, nb_list;
     bool hb_pm_valid = false;         // the primary masks cover every particle's records (single-search path, <= 16 bonds each)
     DevBuf gl_nodes, gl_weights;      // this context's quadrature rule (never shared between contexts)
@@ -343,9 +345,9 @@ PgtFrameView frame_view(const pgt_ctx* c)
 
 int set_box(pgt_ctx* ctx, const double box[3], int dim)
 {
-    if (dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "only dim == 2 is implemented on device (got %d)", dim);
+    if (dim != 2 && dim != 3) return fail(ctx, PGT_ERR_ARG, "dim must be 2 or 3 (got %d)", dim);
     ctx->dim = dim;
-    double L[3] = { box[0], box[1], 1.0 };   // utils.py:15-16 forces Lz = 1 in 2-D
+    double L[3] = { box[0], box[1], dim == 2 ? 1.0 : box[2] };   // utils.py:15-16 forces Lz = 1 in 2-D
     for (int d = 0; d < 3; ++d) {
         if (!(L[d] > 0) || !std::isfinite(L[d])) return fail(ctx, PGT_ERR_ARG, "box length %d is not positive", d);
         // SimBox::setBounds with origin 0 (SimBox.cc:48-52)
@@ -354,7 +356,7 @@ int set_box(pgt_ctx* ctx, const double box[3], int dim)
         ctx->box.L[d] = ctx->box.hi[d] - ctx->box.lo[d];   // Aboria: bmax - bmin
     }
     ctx->box.dim = dim;
-    ctx->vol = L[0] * L[1];
+    ctx->vol = dim == 2 ? L[0] * L[1] : L[0] * L[1] * L[2];    // SimBox.cc:36-44
     return PGT_OK;
 }
 
@@ -422,7 +424,7 @@ int pgt_ctx_destroy(pgt_ctx* ctx)
     if (ctx->comm && g_nccl.ok) g_nccl.CommDestroy(ctx->comm);
     DevBuf* bufs[] = { &ctx->raw_pos2[0], &ctx->raw_pos2[1], &ctx->raw_diam2[0], &ctx->raw_diam2[1], &ctx->raw_mass, &ctx->raw_vel, &ctx->cell_of, &ctx->cell_count, &ctx->cell_fill,
                        &ctx->sorted_orig, &ctx->scan_scratch, &ctx->eflags, &ctx->sx, &ctx->sy, &ctx->sxy, &ctx->sd, &ctx->skxx, &ctx->skxy,
-                       &ctx->skyy, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->hb_pm, &ctx->nb_list, &ctx->gl_nodes,
+                       &ctx->skyy, &ctx->sz, &ctx->sm3, &ctx->svx3, &ctx->svy3, &ctx->svz3, &ctx->hb_cnt, &ctx->hb_b, &ctx->hb_cf, &ctx->hb_j, &ctx->hb_pm, &ctx->nb_list, &ctx->gl_nodes,
                        &ctx->gl_weights, &ctx->gxs, &ctx->gys, &ctx->gpts,
                        &ctx->out_virial, &ctx->out_kinetic, &ctx->out_density, &ctx->out_elastic, &ctx->disp, &ctx->pack, &ctx->thermo_partials,
                        &ctx->thermo_out,
@@ -725,12 +727,193 @@ static bool shard_slab(const pgt_ctx* ctx, const PgtCells& c, double* lo, double
     return *hi - *lo < ctx->box.L[0];
 }
 
+// ---------------------------------------------------------------------------------- Dim = 3 (pgt_dim3.cu)
+// The reference's 3-D typedefs (module-irvingkirkwood.cpp:8-13, module-thermo.cpp:7-20): parity kernels, exact counts, no
+// deferral, no slab cull, no bond records (the gather runs the reference's nested search itself).
+static Pgt3Frame frame3(const pgt_ctx* c)
+{
+    Pgt3Frame f{};
+    f.n = c->n_live;
+    f.sx = c->sx.as<double>(); f.sy = c->sy.as<double>(); f.sz = c->sz.as<double>(); f.sd = c->sd.as<double>();
+    const bool kin = c->src_vel != nullptr;
+    f.sm = kin ? c->sm3.as<double>() : nullptr;
+    f.svx = kin ? c->svx3.as<double>() : nullptr;
+    f.svy = kin ? c->svy3.as<double>() : nullptr;
+    f.svz = kin ? c->svz3.as<double>() : nullptr;
+    f.sorig = c->sorted_orig.as<int>();
+    f.cell_start = c->cell_count.as<int>();
+    return f;
+}
+
+static int build_cells3(pgt_ctx* ctx)
+{
+    const long long N = ctx->N;
+    const double L[3] = { ctx->box.L[0], ctx->box.L[1], ctx->box.L[2] };
+    double side = ctx->cell_side_user > 0 ? ctx->cell_side_user : ctx->max_rcut;
+    side = std::max(side, std::cbrt(L[0] * L[1] * L[2] / (4.0 * (double)std::max<long long>(N, 1) + 64.0)));
+    Pgt3Cells& c = ctx->cells3;
+    for (;;) {
+        c.ncx = std::max(1, (int)std::floor(L[0] / side));
+        c.ncy = std::max(1, (int)std::floor(L[1] / side));
+        c.ncz = std::max(1, (int)std::floor(L[2] / side));
+        if ((long long)c.ncx * c.ncy * c.ncz <= (1LL << 27)) break;
+        side *= 1.26;
+    }
+    c.inv_cw[0] = 1.0 / (L[0] / c.ncx);
+    c.inv_cw[1] = 1.0 / (L[1] / c.ncy);
+    c.inv_cw[2] = 1.0 / (L[2] / c.ncz);
+    const int ncells = c.ncx * c.ncy * c.ncz;
+
+    wait_upload(ctx);
+    stage_begin(ctx, PGT_STAGE_CELLS);
+    ENSURE(ctx->cell_of, sizeof(int) * (size_t)std::max<long long>(N, 1));
+    ENSURE(ctx->cell_count, sizeof(int) * ((size_t)ncells + 1));
+    ENSURE(ctx->cell_fill, sizeof(int) * (size_t)std::max<long long>(N, 1));
+    ENSURE(ctx->sorted_orig, sizeof(int) * (size_t)std::max<long long>(N, 1));
+    ENSURE(ctx->scan_scratch, sizeof(int) * (size_t)pgt_scan_scratch_ints(std::max<long long>(ncells, N) + 1));
+    ENSURE(ctx->eflags, sizeof(int) * 4);
+    CK(cudaMemsetAsync(ctx->cell_count.p, 0, sizeof(int) * ((size_t)ncells + 1), ctx->stream));
+    CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int) * 4, ctx->stream));
+    ctx->eflags_init = true;
+    pgt3_launch_wrap_count(ctx->src_pos, ctx->is_f32, N, ctx->box, c, ctx->cell_of.as<int>(), ctx->cell_fill.as<int>(),
+                           ctx->cell_count.as<int>(), ctx->eflags.as<int>(), ctx->stream, &ctx->launches);
+    pgt_launch_scan_exclusive(ctx->cell_count.as<int>(), ctx->cell_count.as<int>(), (long long)ncells + 1, ctx->scan_scratch.as<int>(),
+                              ctx->stream, &ctx->launches);
+    pgt_launch_scatter_ids(ctx->cell_of.as<int>(), ctx->cell_fill.as<int>(), N, ctx->cell_count.as<int>(), ctx->sorted_orig.as<int>(),
+                           ctx->stream, &ctx->launches);
+    pgt_launch_publish(ctx->cell_count.as<int>() + ncells, 1, ctx->eflags.p, 1, ctx->d_small, ctx->stream, &ctx->launches);
+    CK(cudaStreamSynchronize(ctx->stream));
+    const int* h = reinterpret_cast<const int*>(ctx->h_small);
+    int rc = check_eflags(ctx, h[1]);
+    if (rc != PGT_OK) return rc;
+    ctx->n_live = h[0];
+    ctx->counts_pending = false;
+    ctx->cells_deferred = false;
+    ctx->known_nlive = -1;
+    ctx->known_nhb = -1;
+    ctx->culled = false;
+    const size_t nl = (size_t)std::max(ctx->n_live, 1);
+    ENSURE(ctx->sx, sizeof(double) * nl);
+    ENSURE(ctx->sy, sizeof(double) * nl);
+    ENSURE(ctx->sz, sizeof(double) * nl);
+    ENSURE(ctx->sd, sizeof(double) * nl);
+    const bool kin = ctx->src_vel != nullptr;
+    if (kin) {
+        ENSURE(ctx->sm3, sizeof(double) * nl);
+        ENSURE(ctx->svx3, sizeof(double) * nl);
+        ENSURE(ctx->svy3, sizeof(double) * nl);
+        ENSURE(ctx->svz3, sizeof(double) * nl);
+    }
+    Pgt3FrameOut o{ ctx->sx.as<double>(), ctx->sy.as<double>(), ctx->sz.as<double>(), ctx->sd.as<double>(),
+                    kin ? ctx->sm3.as<double>() : nullptr, kin ? ctx->svx3.as<double>() : nullptr,
+                    kin ? ctx->svy3.as<double>() : nullptr, kin ? ctx->svz3.as<double>() : nullptr };
+    pgt3_launch_sort_gather(ctx->src_pos, ctx->src_diam, ctx->src_mass, ctx->src_vel, ctx->is_f32, ctx->box, ctx->sorted_orig.as<int>(),
+                            ctx->cell_count.as<int>(), ncells, o, ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    if (ctx->raw_cur >= 0) {
+        CK(cudaEventRecord(ctx->ev_raw_free[ctx->raw_cur], ctx->stream));
+        ctx->raw_free_valid[ctx->raw_cur] = true;
+    }
+    stage_end(ctx, PGT_STAGE_CELLS);
+    ctx->cells_built = true;
+    ctx->bonds_built = false;
+    return PGT_OK;
+}
+
+static int ensure_disp(pgt_ctx* ctx);
+
+static int ik_compute3(pgt_ctx* ctx, unsigned obs_mask)
+{
+    for (int d = 0; d < 3; ++d)
+        if (ctx->cg.rcut >= ctx->box.L[d]) return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
+    if ((obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_ELASTIC)) && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no pair potential");
+    CK(cudaSetDevice(ctx->device));
+    const long long gl = ctx->g1 - ctx->g0;
+    ctx->field_g0 = ctx->g0;
+    ctx->field_g1 = ctx->g1;
+    const size_t n = (size_t)std::max<long long>(gl, 1);
+    if (obs_mask & PGT_OBS_VIRIAL) ENSURE(ctx->out_virial, sizeof(double) * 9 * n);
+    if (obs_mask & PGT_OBS_KINETIC) ENSURE(ctx->out_kinetic, sizeof(double) * 9 * n);
+    if (obs_mask & PGT_OBS_DENSITY) ENSURE(ctx->out_density, sizeof(double) * n);
+    if (obs_mask & PGT_OBS_ELASTIC) {
+        ENSURE(ctx->out_elastic, sizeof(double) * 9 * n);
+        const int rc = ensure_disp(ctx);
+        if (rc != PGT_OK) return rc;
+    }
+    if (ctx->dl_pending) CK(cudaStreamWaitEvent(ctx->stream, ctx->ev_dl_done, 0));
+    stage_begin(ctx, PGT_STAGE_IK);
+    Pgt3IKArgs a{};
+    a.fr = frame3(ctx);
+    a.grid.mode = ctx->grid_mode;
+    a.grid.nx = ctx->nx; a.grid.ny = ctx->ny;
+    a.grid.xs = ctx->gxs.as<double>(); a.grid.ys = ctx->gys.as<double>(); a.grid.pts = ctx->gpts.as<double>();
+    a.grid.g0 = ctx->g0; a.grid.g1 = ctx->g1;
+    a.box = ctx->box;
+    a.cells = ctx->cells3;
+    a.cg = ctx->cg;
+    a.nq = ctx->nq;
+    a.gl_nodes = ctx->gl_nodes.as<double>();
+    a.gl_weights = ctx->gl_weights.as<double>();
+    a.adaptive = ctx->quad_mode == PGT_QUAD_ADAPTIVE ? 1 : 0;
+    a.qag_epsabs = ctx->qag_epsabs; a.qag_epsrel = ctx->qag_epsrel; a.qag_limit = ctx->qag_limit;
+    a.max_rcut = ctx->max_rcut;
+    a.disp = (obs_mask & PGT_OBS_ELASTIC) ? ctx->disp.as<double>() : nullptr;
+    a.out_virial = ctx->out_virial.as<double>();
+    a.out_kinetic = ctx->out_kinetic.as<double>();
+    a.out_density = ctx->out_density.as<double>();
+    a.out_elastic = ctx->out_elastic.as<double>();
+    a.obs_mask = obs_mask;
+    if ((obs_mask & PGT_OBS_KINETIC) && !a.fr.sm && gl > 0) CK(cudaMemsetAsync(ctx->out_kinetic.p, 0, sizeof(double) * 9 * n, ctx->stream));
+    CK(cudaMemsetAsync(ctx->eflags.p, 0, sizeof(int), ctx->stream));
+    if (gl > 0) CK(pgt3_launch_ik(ctx->pot, a, ctx->eflags.as<int>(), ctx->stream, &ctx->launches));
+    stage_end(ctx, PGT_STAGE_IK);
+    if (a.adaptive) {
+        pgt_launch_publish(ctx->eflags.p, 1, nullptr, 0, ctx->d_small, ctx->stream, &ctx->launches);
+        CK(cudaStreamSynchronize(ctx->stream));
+        const int fl = reinterpret_cast<int*>(ctx->h_small)[0];
+        if (fl & PGT_EFLAG_QAG_CAPACITY)
+            return fail(ctx, PGT_ERR_UNSUPPORTED, "adaptive bond quadrature: a bond needs more than %d intervals on device", PGT_QAG_CAP);
+        if (fl & PGT_EFLAG_QAG_FAILED)
+            return fail(ctx, PGT_ERR_DATA, "adaptive bond quadrature did not reach the tolerance within maxiter = %d intervals "
+                        "(GSL's error handler aborts the reference here)", ctx->qag_limit);
+    }
+    ctx->last_ik_mask = obs_mask;
+    return PGT_OK;
+}
+
+// out: virial 9 | kinetic 9 | energy | born 81 (100 doubles), or the elastic virial's 9 when elastic_only
+static int thermo3(pgt_ctx* ctx, unsigned obs_mask, bool elastic_only, double* out)
+{
+    CK(cudaSetDevice(ctx->device));
+    if (elastic_only) {
+        const int rc = ensure_disp(ctx);
+        if (rc != PGT_OK) return rc;
+        obs_mask = PGT_OBS_ELASTIC;
+    } else obs_mask &= ~PGT_OBS_ELASTIC;
+    const int blocks = pgt3_thermo_blocks(ctx->n_live);
+    const int p_begin = (int)((long long)ctx->n_live * ctx->thermo_part / ctx->thermo_nparts);
+    const int p_end = (int)((long long)ctx->n_live * (ctx->thermo_part + 1) / ctx->thermo_nparts);
+    ENSURE(ctx->thermo_partials, sizeof(double) * pgt3_thermo_nv() * (size_t)blocks);
+    ENSURE(ctx->thermo_out, sizeof(double) * 128);
+    stage_begin(ctx, PGT_STAGE_THERMO);
+    CK(pgt3_launch_thermo(ctx->pot, frame3(ctx), ctx->box, ctx->cells3, ctx->max_rcut, obs_mask, elastic_only ? ctx->disp.as<double>() : nullptr,
+                          1 / ctx->vol, ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), p_begin, p_end, ctx->stream,
+                          &ctx->launches));
+    stage_end(ctx, PGT_STAGE_THERMO);
+    CK(cudaMemcpyAsync(ctx->h_small, ctx->thermo_out.p, sizeof(double) * 109, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (elastic_only) for (int k = 0; k < 9; ++k) out[k] = ctx->h_small[100 + k];
+    else for (int k = 0; k < 100; ++k) out[k] = ctx->h_small[k];
+    return PGT_OK;
+}
+
 int pgt_build_cells(pgt_ctx* ctx)
 {
     if (!ctx) return PGT_ERR_ARG;
     if (!ctx->have_frame) return fail(ctx, PGT_ERR_STATE, "pgt_build_cells: no frame");
     if (!(ctx->max_rcut > 0)) return fail(ctx, PGT_ERR_STATE, "pgt_build_cells: max_rcut not set");
     CK(cudaSetDevice(ctx->device));
+    if (ctx->dim == 3) return build_cells3(ctx);
     const long long N = ctx->N;
 
     // cell geometry: side ~ max_rcut/2, never more than ~8 cells per particle
@@ -829,6 +1012,11 @@ int pgt_build_bonds(pgt_ctx* ctx)
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_build_bonds: no pair potential");
     CK(cudaSetDevice(ctx->device));
+    if (ctx->dim == 3) {                                       // no records in 3-D: the gather searches the pairs itself
+        ctx->n_hb = 0;
+        ctx->bonds_built = true;
+        return PGT_OK;
+    }
     // deferred counts: the record arrays keep last frame's size plus a margin, the writer drops records beyond it and the
     // sticky word reports it; needs the single-search path and the warp-flattened writer (the one with the capacity guard)
     const bool defer = ctx->cells_deferred && ctx->counts_pending && ctx->known_nhb >= 0 && ctx->bond_single_search &&
@@ -906,7 +1094,7 @@ int pgt_frame_counts(pgt_ctx* ctx, int64_t* n_live, int64_t* n_halfbonds, int64_
     RESOLVE();
     if (n_live) *n_live = ctx->cells_built ? ctx->n_live : -1;
     if (n_halfbonds) *n_halfbonds = ctx->bonds_built ? ctx->n_hb : -1;
-    if (n_cells) *n_cells = ctx->cells_built ? (int64_t)ctx->cells.ncx * ctx->cells.ncy : -1;
+    if (n_cells) *n_cells = !ctx->cells_built ? -1 : (ctx->dim == 3 ? (int64_t)ctx->cells3.ncx * ctx->cells3.ncy * ctx->cells3.ncz : (int64_t)ctx->cells.ncx * ctx->cells.ncy);
     return PGT_OK;
 }
 
@@ -982,6 +1170,7 @@ int pgt_ik_compute(pgt_ctx* ctx, unsigned obs_mask)
     if (ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no grid");
     if (!(obs_mask & (PGT_OBS_VIRIAL | PGT_OBS_KINETIC | PGT_OBS_DENSITY | PGT_OBS_ELASTIC))) return fail(ctx, PGT_ERR_ARG, "pgt_ik_compute: empty observable mask");
     if ((obs_mask & PGT_OBS_ELASTIC) && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_ik_compute: no pair potential");
+    if (ctx->dim == 3) return ik_compute3(ctx, obs_mask);
     if (ctx->cg.rcut >= ctx->box.L[0] || ctx->cg.rcut >= ctx->box.L[1])
         return fail(ctx, PGT_ERR_DATA, "cg_rcut %g is not smaller than the box", ctx->cg.rcut);
     if (ctx->n_live >= (1 << 28))
@@ -1093,6 +1282,7 @@ int pgt_ik_count_work(pgt_ctx* ctx, int64_t* sum_unique_bonds, int64_t* sum_half
 {
     if (ctx) RESOLVE();
     if (!ctx) return PGT_ERR_ARG;
+    if (ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_ik_count_work: 2-D frames only");
     if (!ctx->bonds_built || !ctx->have_cg || ctx->grid_mode < 0) return fail(ctx, PGT_ERR_STATE, "pgt_ik_count_work: frame, bonds, cg and grid required");
     CK(cudaSetDevice(ctx->device));
     DevBuf out;
@@ -1179,10 +1369,10 @@ int pgt_set_option(pgt_ctx* ctx, const char* name, double value)
 static int field_info(pgt_ctx* ctx, int field_id, DevBuf** buf, int* ncomp)
 {
     switch (field_id) {
-    case PGT_FIELD_VIRIAL: *buf = &ctx->out_virial; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_VIRIAL) ? 0 : -1;
-    case PGT_FIELD_KINETIC: *buf = &ctx->out_kinetic; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_KINETIC) ? 0 : -1;
+    case PGT_FIELD_VIRIAL: *buf = &ctx->out_virial; *ncomp = ctx->dim * ctx->dim; return (ctx->last_ik_mask & PGT_OBS_VIRIAL) ? 0 : -1;
+    case PGT_FIELD_KINETIC: *buf = &ctx->out_kinetic; *ncomp = ctx->dim * ctx->dim; return (ctx->last_ik_mask & PGT_OBS_KINETIC) ? 0 : -1;
     case PGT_FIELD_DENSITY: *buf = &ctx->out_density; *ncomp = 1; return (ctx->last_ik_mask & PGT_OBS_DENSITY) ? 0 : -1;
-    case PGT_FIELD_ELASTIC: *buf = &ctx->out_elastic; *ncomp = 4; return (ctx->last_ik_mask & PGT_OBS_ELASTIC) ? 0 : -1;
+    case PGT_FIELD_ELASTIC: *buf = &ctx->out_elastic; *ncomp = ctx->dim * ctx->dim; return (ctx->last_ik_mask & PGT_OBS_ELASTIC) ? 0 : -1;
     }
     return -2;
 }
@@ -1223,6 +1413,7 @@ static int ik_download_impl(pgt_ctx* ctx, int field_id, double* out, bool wait)
 int pgt_ik_download_sym_async(pgt_ctx* ctx, int field_id, double* out)
 {
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_ik_download_sym_async: null argument");
+    if (ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_ik_download_sym_async: 2-D fields only (read a 3-D field with pgt_ik_download)");
     DevBuf* b;
     int nc;
     int rc = field_info(ctx, field_id, &b, &nc);
@@ -1302,6 +1493,7 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: no pair potential");
     if (ctx->culled) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute: the frame holds a grid shard's particles only (set the whole grid or option slab_cull = 0 and rebuild the cells)");
+    if (ctx->dim == 3) return thermo3(ctx, obs_mask, false, out);
     CK(cudaSetDevice(ctx->device));
     const int blocks = pgt_thermo_blocks(ctx->n_live);
     const int p_begin = (int)((long long)ctx->n_live * ctx->thermo_part / ctx->thermo_nparts);
@@ -1366,6 +1558,7 @@ int pgt_thermo_compute_static(pgt_ctx* ctx, unsigned obs_mask, double* out)
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: no pair potential");
     if (ctx->culled) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_static: the frame holds a grid shard's particles only (set the whole grid or option slab_cull = 0 and rebuild the cells)");
+    if (ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_thermo_compute_static: 2-D frames only");
     if (ctx->n_live > PGT_THERMO_STATIC_MAX_PARTICLES)
         return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_static: the frame has %lld live particles, the static scratch serves at most %d (use pgt_thermo_compute)",
                     (long long)ctx->n_live, PGT_THERMO_STATIC_MAX_PARTICLES);
@@ -1423,6 +1616,7 @@ int pgt_thermo_elastic(pgt_ctx* ctx, double* out)
     if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_elastic: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: cells not built");
     if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_elastic: no pair potential");
+    if (ctx->dim == 3) return thermo3(ctx, 0, true, out);
     CK(cudaSetDevice(ctx->device));
     int rc = ensure_disp(ctx);
     if (rc != PGT_OK) return rc;
@@ -1506,12 +1700,14 @@ static int export_pairs(pgt_ctx* ctx, bool bonds, int64_t cap, int64_t* n, int32
 
 int pgt_export_bonds(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j, double* rij_xy, double* fdivr)
 {
+    if (ctx && ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "export: 2-D frames only");
     return export_pairs(ctx, true, cap, n, i, j, rij_xy, fdivr);
 }
 
 int pgt_export_neighbors(pgt_ctx* ctx, int64_t cap, int64_t* n, int32_t* i, int32_t* j)
 {
     if (ctx && !ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "export: no pair potential");
+    if (ctx && ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "export: 2-D frames only");
     return export_pairs(ctx, false, cap, n, i, j, nullptr, nullptr);
 }
 
@@ -1519,6 +1715,7 @@ int pgt_export_wrapped(pgt_ctx* ctx, double* xy, uint8_t* alive)
 {
     if (!ctx || !xy) return fail(ctx, PGT_ERR_ARG, "pgt_export_wrapped: null argument");
     if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_export_wrapped: cells not built");
+    if (ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_export_wrapped: 2-D frames only");
     CK(cudaSetDevice(ctx->device));
     RESOLVE();
     const int np = ctx->n_live;

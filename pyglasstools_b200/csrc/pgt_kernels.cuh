@@ -101,6 +101,51 @@ struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 
 // ---- launch wrappers (defined in pgt_kernels.cu) ---------------------------------------------
 struct PgtLaunchCounter { long long n; };
 
+// ---- Dim = 3 (pgt_dim3.cu): the reference's 3-D typedefs, parity kernels
+struct Pgt3Cells {
+    int ncx, ncy, ncz;
+    double inv_cw[3];            // 1 / cell width per axis
+};
+struct Pgt3Frame {               // live particles sorted by cell ((cz ncy + cy) ncx + cx), ascending id inside a cell
+    int n;
+    const double *sx, *sy, *sz, *sd;
+    const double *sm, *svx, *svy, *svz;   // NULL when the frame has no velocities
+    const int* sorig;
+    const int* cell_start;       // ncx ncy ncz + 1
+};
+struct Pgt3FrameOut { double *sx, *sy, *sz, *sd, *sm, *svx, *svy, *svz; };
+struct Pgt3IKArgs {
+    Pgt3Frame fr;
+    PgtGridView grid;
+    PgtBox box;
+    Pgt3Cells cells;
+    PgtCG cg;
+    int nq;
+    const double* gl_nodes;
+    const double* gl_weights;
+    int adaptive;
+    double qag_epsabs, qag_epsrel;
+    int qag_limit;
+    double max_rcut;
+    const double* disp;          // N x 3, original particle order (elastic field), or NULL
+    double* out_virial;          // (g1 - g0) x 9, flat a + 3 b
+    double* out_kinetic;         // (g1 - g0) x 9
+    double* out_density;         // (g1 - g0)
+    double* out_elastic;         // (g1 - g0) x 9
+    unsigned obs_mask;
+};
+void pgt3_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, Pgt3Cells cells, int* cell_of, int* cell_slot,
+                            int* cell_count, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
+void pgt3_launch_sort_gather(const void* pos, const void* diam, const void* mass, const void* vel, int is_f32, PgtBox box, int* sorted_orig,
+                             const int* cell_start, int ncells, Pgt3FrameOut out, cudaStream_t st, PgtLaunchCounter* lc);
+cudaError_t pgt3_launch_ik(const PgtPot& pot, const Pgt3IKArgs& a, int* eflags, cudaStream_t st, PgtLaunchCounter* lc);
+int pgt3_thermo_blocks(int n);
+int pgt3_thermo_nv();
+cudaError_t pgt3_launch_thermo(const PgtPot& pot, Pgt3Frame fr, PgtBox box, Pgt3Cells cells, double max_rcut, unsigned obs_mask,
+                               const double* disp, double inv_vol, double* partials, int blocks, double* out_dev, int p_begin, int p_end,
+                               cudaStream_t st, PgtLaunchCounter* lc);
+
+
 // slab_on: drop particles whose wrapped x lies outside [slab_lo, slab_hi] under every periodic image (grid-point sharding)
 void pgt_launch_wrap_count(const void* pos, int is_f32, long long N, PgtBox box, PgtCells cells, int* cell_of, int* cell_slot,
                            int* cell_count, int* eflags, int slab_on, double slab_lo, double slab_hi, cudaStream_t st,
