@@ -81,7 +81,12 @@ int pgt_set_cell_size(pgt_ctx* ctx, double cell_side);
  * (ParticleSystem.cc:3-30; Aboria NeighbourSearchBase.h:208-237) and SimBox (SimBox.cc:25-52).
  * pos: N x 3 (float or double), diam: N, mass: N or NULL (=1), vel: N x 3 or NULL (=0).
  * box: Lx,Ly,Lz (Lz forced to 1 when dim==2 as utils.py:15-16 does).  Host pointers; the copy
- * is asynchronous on the ctx stream from the caller's (ideally pinned) memory.               */
+ * is asynchronous on the ctx stream from the caller's (ideally pinned) memory.
+ * dim == 3 selects the reference's Dim = 3 typedefs (module-irvingkirkwood.cpp:9-13, module-thermo.cpp:8-20): the box is
+ * periodic on all three axes (SimBox.cc:33), fields are Dim*Dim = 9 doubles per grid point, pgt_thermo_compute returns
+ * 9 + 9 + 1 + 81 doubles, pgt_thermo_elastic 9.  The 3-D stages are parity kernels (the reference's nested searches, no
+ * bond records: pgt_build_bonds is a no-op); the parity exports, pgt_ik_count_work, pgt_ik_download_sym_async and
+ * pgt_thermo_compute_static serve 2-D frames only (PGT_ERR_UNSUPPORTED otherwise).                                  */
 int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel,
                      int is_f32, int64_t N, const double box[3], int dim);
 /* One rank's PART of a frame (grid-point sharding over GPUs: every GPU needs the whole frame, but each rank pushes

@@ -103,8 +103,9 @@ void Calculator::prepare_device(bool need_bonds)
     pgt_ctx* ctx = S.ctx();
     const ParticleSystem& ps = *m_sysdata;
     const SimBox& box = *ps.simbox;
-    if (box.dim != 2) throw std::domain_error("[ERROR] only 2-D systems are implemented on device");
-    if (box.origin[0] != 0.0 || box.origin[1] != 0.0) throw std::domain_error("[ERROR] a shifted box origin is not implemented on device");
+    if (box.dim != 2 && box.dim != 3) throw std::domain_error("[ERROR] the box dimension must be 2 or 3");
+    if (box.origin[0] != 0.0 || box.origin[1] != 0.0 || (box.dim == 3 && box.origin[2] != 0.0))
+        throw std::domain_error("[ERROR] a shifted box origin is not implemented on device");
     if (m_potential->model < 0) throw std::domain_error("[ERROR] the abstract PairPotential carries no force model");
 
     const std::string sig = m_potential->signature();
@@ -135,14 +136,16 @@ void ThermoCalculator::compute()
 {
     unsigned mask = 0;
     bool elastic = false;
+    const int D = m_sysdata->simbox->dim, D2 = D * D, D4 = D2 * D2;
     for (auto& kv : m_obs) {
-        if (kv.second->dim != 2) throw std::domain_error("[ERROR] only 2-D observables are implemented on device");
+        // the reference's templates would let a 2-D observable read a 3-D system (and the reverse); nothing in its Python layer does
+        if (kv.second->dim != D) throw std::domain_error("[ERROR] observable '" + kv.second->name + "' and the simulation box differ in dimension");
         if (kv.second->kind == ThermoKind::ElasticVirial) elastic = true;
         else mask |= kv.second->mask();
     }
     for (auto& kv : m_obs) kv.second->clear();
     if (mask == 0 && !elastic) return;
-    double out[32] = { 0 }, out_el[4] = { 0 };
+    double out[128] = { 0 }, out_el[9] = { 0 };
     {
         py::gil_scoped_release nogil;
         prepare_device(false);
@@ -154,15 +157,15 @@ void ThermoCalculator::compute()
             S.check(pgt_thermo_elastic(S.ctx(), out_el), "pgt_thermo_elastic");
         }
     }
-    // device layout: virial 4 | kinetic 4 | energy | born 16, already times 1/vol (ThermoCalculator.h:58-64)
+    // device layout: virial D^2 | kinetic D^2 | energy | born D^4, already times 1/vol (ThermoCalculator.h:58-64)
     for (auto& kv : m_obs) {
         ThermoObservable& o = *kv.second;
         switch (o.kind) {
-        case ThermoKind::Virial: std::copy(out, out + 4, o.val.begin()); break;
-        case ThermoKind::Kinetic: std::copy(out + 4, out + 8, o.val.begin()); break;
-        case ThermoKind::Energy: o.val[0] = out[8]; break;
-        case ThermoKind::Born: std::copy(out + 9, out + 25, o.val.begin()); break;
-        case ThermoKind::ElasticVirial: std::copy(out_el, out_el + 4, o.val.begin()); break;
+        case ThermoKind::Virial: std::copy(out, out + D2, o.val.begin()); break;
+        case ThermoKind::Kinetic: std::copy(out + D2, out + 2 * D2, o.val.begin()); break;
+        case ThermoKind::Energy: o.val[0] = out[2 * D2]; break;
+        case ThermoKind::Born: std::copy(out + 2 * D2 + 1, out + 2 * D2 + 1 + D4, o.val.begin()); break;
+        case ThermoKind::ElasticVirial: std::copy(out_el, out_el + D2, o.val.begin()); break;
         default: break;
         }
     }
@@ -181,7 +184,7 @@ void IrvingKirkwood::run(long long npoints)
     unsigned mask = 0;
     for (auto& kv : m_obs) {
         FieldObservable& o = *kv.second;
-        if (o.dim != 2) throw std::domain_error("[ERROR] only 2-D fields are implemented on device");
+        if (o.dim != m_sysdata->simbox->dim) throw std::domain_error("[ERROR] field '" + o.name + "' and the simulation box differ in dimension");
         if ((long long)o.npoints != npoints)
             throw std::invalid_argument("[ERROR] field '" + o.name + "' was sized for " + std::to_string(o.npoints) + " grid points, compute() got " +
                                         std::to_string(npoints));

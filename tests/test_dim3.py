@@ -168,3 +168,68 @@ def test_gpu_dim3_larger_frame_f32_cartesian_grid_shards_and_adaptive(orc):
             ctx.export_bonds()
     finally:
         ctx.close()
+
+
+@pytest.mark.gpu
+def test_gpu_dim3_through_the_python_surface(orc, tmp_path, monkeypatch):
+    """The example scripts' statements on a 3-D trajectory (utils.read_gsd(..., ndim=3)): ikcalculator + fieldlogger with
+    3 x 3 component names and the x y z coordinate columns (io.py:112-128), thermo.calculator + logfile with a Born entry."""
+    monkeypatch.chdir(tmp_path)
+    import pyglasstools as pglass
+    pglass.reset()
+    try:
+        import pyglasstools.io as io
+        import pyglasstools.utils as utils
+        import pyglasstools.potential as pot
+        import pyglasstools.thermo as thermo
+        import pyglasstools.irvingkirkwood as ik
+        import pyglasstools.irvingkirkwood.cgfunc as cgfunc
+        from pyglasstools import gsdio
+
+        rng = np.random.default_rng(9)
+        n, L = 8, 8.0
+        frames = []
+        for f in range(2):
+            ii, jj, kk = np.meshgrid(np.arange(n), np.arange(n), np.arange(n), indexing="ij")
+            pos = (np.stack([ii.ravel(), jj.ravel(), kk.ravel()], 1) + 0.5 - n / 2 + rng.uniform(-0.3, 0.3, (n**3, 3))).astype(np.float32)
+            diam = rng.uniform(0.8, 1.25, n**3).astype(np.float32)
+            frames.append(dict(box=np.array([L, L, L, 0, 0, 0], np.float32), position=pos, diameter=diam, dimensions=3))
+        gsdio.write_trajectory("traj3.gsd", frames)
+        poly12 = pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)                                # noqa: F841
+        mycgfunc = cgfunc.octic(rcut=1.5, mode="fixedpoint", order=5)
+        mysystem = utils.read_gsd(filename="traj3.gsd", checkpointfile="restart.log", ndim=3)  # noqa: F841
+        assert pglass.get_sysdata().pysimbox.dim == 3
+        calc = ik.ikcalculator(cgfunc=mycgfunc, dx=1.0)
+        names = ['virialstress_00', 'virialstress_22', 'virialstress_12']
+        flog = io.fieldlogger(keyword="dump3", names=names, solver=calc)
+        tcalc = thermo.calculator()
+        tlog = io.logfile(filename="thermo3.log", names=['virialstress_22', 'virialstress_02', 'potentialenergy', 'borntensor_0122'], solver=tcalc)
+        pglass.analyze(frame_list=range(2))
+        flog.file.flush()
+        del tlog
+
+        P, cg = orc.potential("poly12"), orc.cgfunc("octic", 1.5, 5)
+        grid = np.asarray(calc.gridpoints)
+        assert grid.shape == (64, 3) and not grid[:, 2].any()
+        S0 = orc.System(frames[0]["box"][:3], frames[0]["position"], frames[0]["diameter"], dim=3)
+        mr = S0.max_rcut(P)                                      # frozen at the calculator's construction (Calculator.h:37-46)
+        S = orc.System(frames[1]["box"][:3], frames[1]["position"], frames[1]["diameter"], dim=3)
+        want = S.ik(P, cg, grid, max_rcut=mr)["virial"]
+        got = flog.field_obs['virialstress'].values()
+        assert got.shape == (64, 9)
+        close(got, want, np.abs(want).max())
+        lines = open("dump3.xyz").read().split("\n")
+        assert lines[0] == "64 " and lines[1].startswith("#Frame 0")
+        last = lines[66 + 2:66 + 2 + 64]                          # second frame's rows
+        for g in (0, 17, 63):
+            cols = last[g].split()
+            assert len(cols) == 1 + 3 + 3                         # "1 x y z" + three components
+            np.testing.assert_allclose([float(c) for c in cols[1:4]], grid[g], rtol=1e-5, atol=1e-12)
+            np.testing.assert_allclose([float(c) for c in cols[4:]], [want[g][0], want[g][8], want[g][1 + 3 * 2]], rtol=2e-5, atol=1e-9)
+        th = np.loadtxt("thermo3.log", skiprows=1)
+        assert th.shape == (2, 5)
+        w = S.thermo(P, max_rcut=mr)
+        born_0122 = w["born"][2 + 3 * (2 + 3 * (1 + 3 * 0))]      # io.py: 'abcd' -> d + dim (c + dim (b + dim a))
+        np.testing.assert_allclose(th[1, 1:], [w["virial"][8], w["virial"][0 + 3 * 2], w["energy"], born_0122], rtol=0, atol=1e-6)
+    finally:
+        pglass.reset()
