@@ -386,6 +386,7 @@ def main():
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
     ap.add_argument("--e2e-lanes", type=int, default=1, choices=(1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over; 1 (default): one context pipelines upload / stages / read-back on its own three streams")
     ap.add_argument("--e2e-buffers", type=int, default=3, choices=(2, 3, 4), help="host field buffers the single-context loop reads back into in turn")
+    ap.add_argument("--e2e-pos", default="xyz", choices=("xy", "xyz"), help="host position rows of the end-to-end loop: xyz = N x 3 float32 through pgt_frame_upload (the GSD layout, 16 B per particle cross the link), xy = N x 2 through pgt_frame_upload_xy (12 B)")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
     ap.add_argument("--pool", type=int, default=3, help="distinct frames cycled per rank")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -457,9 +458,13 @@ def main():
         g_local = G
     pin_pos = [_capi.PinnedArray((N, 3), np.float32) for _ in range(pool)]
     pin_diam = [_capi.PinnedArray((N,), np.float32) for _ in range(pool)]
+    pin_xy = [_capi.PinnedArray((N, 2), np.float32) for _ in range(pool)]
+    pos_xy = [args.e2e_pos == "xy"]              # the end-to-end loops upload N x 2 rows (the synthetic frames have z = 0)
     dev_pos, dev_diam = [], []
     for k, f in enumerate(frames):
         pin_pos[k].array[...] = f["position"]
+        pin_xy[k].array[...] = f["position"][:, :2]
+        assert not f["position"][:, 2].any()
         pin_diam[k].array[...] = f["diameter"]
         dev_pos.append(torch.from_numpy(f["position"]).cuda())
         dev_diam.append(torch.from_numpy(f["diameter"]).cuda())
@@ -501,6 +506,8 @@ def main():
             # this rank's 1/world of the frame over PCIe, the rest over NVLink
             c.upload_part(pin_pos[k].array[p_first:p_last], pin_diam[k].array[p_first:p_last], p_first, N, box)
             c.comm_allgather_frame()
+        elif pos_xy[0]:
+            c.upload_xy(pin_xy[k].array, pin_diam[k].array, box)
         else:
             c.upload(pin_pos[k].array, pin_diam[k].array, box)
         c.build_cells()
@@ -544,6 +551,8 @@ def main():
             k = s % pool
             if parts:
                 c.upload_part(pin_pos[k].array[p_first:p_last], pin_diam[k].array[p_first:p_last], p_first, N, box)
+            elif pos_xy[0]:
+                c.upload_xy(pin_xy[k].array, pin_diam[k].array, box)
             else:
                 c.upload(pin_pos[k].array, pin_diam[k].array, box)
         up(0)
@@ -647,6 +656,13 @@ def main():
     ctx.set_option("async_counts", 1)
     e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
     assert np.isfinite(e2e_check) and e2e_check > 0
+    # for comparison, the same loop with N x 2 position rows (pgt_frame_upload_xy: 12 instead of 16 bytes per particle up)
+    e2e_xy = None
+    if not pos_xy[0] and args.e2e_lanes == 1 and not grid_mode and world == 1:
+        pos_xy[0] = True
+        ms_xy, _ = time_e2e([lanes[0]], args.steps, args.warmup, False, 1)
+        pos_xy[0] = False
+        e2e_xy = ms_xy / args.steps
     # for comparison, the round-1 arrangement: three contexts, one host thread each, every stage waiting for its count
     e2e_alt = None
     if len(lanes) == 1 + (args.e2e_buffers - 1) and args.e2e_lanes == 1 and not grid_mode and world == 1:
@@ -752,7 +768,7 @@ def main():
                     traffic, traffic_src = float(line.split()[-1]), prof
     except Exception:
         pass
-    h2d = N * 3 * 4 + N * 4 if not grid_mode else (p_last - p_first) * 16
+    h2d = N * (2 if pos_xy[0] else 3) * 4 + N * 4 if not grid_mode else (p_last - p_first) * 16
     d2h = g_local * ncomp_out * 8
     sb = stage_bytes(N, ncells, float(np.mean(hb_per_frame)))
     cells_ms, bonds_ms = float(np.mean(stage_ms["cells"])), float(np.mean(stage_ms["bonds"]))
@@ -770,11 +786,14 @@ def main():
             "config": config_dict(args, wl, world, pool),
             "clocks": sampler.summary([win_a, win_b]),
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": "C-ABI pgt_frame_upload .. %s, pinned host buffers; %s" % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", "one context (upload, compute and read-back streams), one host thread, counts deferred" if args.e2e_lanes == 1 else "frames spread over %d contexts, %s" % (args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread"))},
+                    "ms_per_step": ms_e2e / args.steps, "host_binding": numa, "api": ("C-ABI %s .. %%s, pinned host buffers; %%s" % ("pgt_frame_upload_xy (N x 2 float32 rows: a 2-D frame has no z column)" if pos_xy[0] else "pgt_frame_upload")) % ("pgt_ik_download_sym_async (xx,xy,yy)" if args.e2e_field == "sym" else "pgt_ik_download_async", "one context (upload, compute and read-back streams), one host thread, counts deferred" if args.e2e_lanes == 1 else "frames spread over %d contexts, %s" % (args.e2e_lanes, "one host thread per context" if args.e2e_threads == 2 else "one host thread"))},
+            "e2e_xy_upload": None if e2e_xy is None else {
+                "value": G / (e2e_xy * 1e-3), "unit": UNIT, "ms_per_step": e2e_xy, "h2d_bytes_per_step": N * 12,
+                "api": "the same loop through pgt_frame_upload_xy (N x 2 float32 position rows: a 2-D frame needs no z column), for comparison"},
             "e2e_three_contexts": None if e2e_alt is None else {
                 "value": G / (e2e_alt * 1e-3), "unit": UNIT, "ms_per_step": e2e_alt,
                 "api": "round-1 arrangement for comparison: three contexts, one host thread each, every stage waits for its count"},
-            "e2e_link": "both end-to-end figures are bound by the host link: %.0f MB per frame cross PCIe (H2D %.0f + D2H %.0f); alone the directions run at ~55 / ~57 GB/s (tools/copy_rates.py), with both busy this VM sustains ~65-70 GB/s in total" % ((h2d + d2h) / 1e6, h2d / 1e6, d2h / 1e6),
+            "e2e_link": "%.0f MB per frame cross PCIe (H2D %.0f + D2H %.0f); the link itself moves that in ~2.0-2.1 ms with both directions busy (tools/link_probe.py: 55 / 56 GB/s alone, ~84 GB/s together), less than the stages take; what the end-to-end loop loses against the resident one is the slowdown of the memory-bound stages while the read-back's DMA runs beside them (tools/pipe_probe.py: cells 0.22 -> 0.32 ms, bonds 0.53 -> 0.65 ms, gather +0.02 ms)" % ((h2d + d2h) / 1e6, h2d / 1e6, d2h / 1e6),
             "gpu_launches": launches_total,
             "stage_ms": {"cells": cells_ms, "bonds": bonds_ms, "ik": ik_avg_ms},
             "roofline": {"kernel": "k_ik_quad", "bound": "fp64", "achieved": achieved, "peak": fp64_peak, "unit": "TFLOP/s",

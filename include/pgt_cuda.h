@@ -89,6 +89,11 @@ int pgt_set_cell_size(pgt_ctx* ctx, double cell_side);
  * pgt_thermo_compute_static serve 2-D frames only (PGT_ERR_UNSUPPORTED otherwise).                                  */
 int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel,
                      int is_f32, int64_t N, const double box[3], int dim);
+/* The same for a 2-D frame whose positions the caller holds as N x 2 rows (x, y): z = 0 for every particle, 12 instead of
+ * 16 bytes per float32 particle cross the host link (25 % of the upload).  What ParticleSystem's ctor would receive with
+ * a zero third column (ParticleSystem.cc:3-30); same stages, same bits as pgt_frame_upload of the N x 3 array.           */
+int pgt_frame_upload_xy(pgt_ctx* ctx, const void* pos_xy, const void* diam, const void* mass, const void* vel,
+                        int is_f32, int64_t N, const double box[3]);
 /* One rank's PART of a frame (grid-point sharding over GPUs: every GPU needs the whole frame, but each rank pushes
  * only 1/nranks of it over PCIe and pgt_comm_allgather_frame assembles it on every GPU over NVLink).  Parts are
  * ceil(N / nranks) particles each, rank r's starting at particle r * ceil(N / nranks) (the last may be short):

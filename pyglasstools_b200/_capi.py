@@ -28,6 +28,7 @@ EXPORTED = [
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
     "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep", "pgt_thermo_compute_static",
+    "pgt_frame_upload_xy",
 ]
 
 _lib = None
@@ -91,6 +92,8 @@ def lib():
         L.pgt_frame_upload.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64,
                                        C.POINTER(C.c_double), C.c_int]
         L.pgt_frame_set_device.argtypes = L.pgt_frame_upload.argtypes
+        L.pgt_frame_upload_xy.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int64,
+                                          C.POINTER(C.c_double)]
         L.pgt_build_cells.argtypes = [C.c_void_p]
         L.pgt_build_bonds.argtypes = [C.c_void_p]
         L.pgt_frame_counts.argtypes = [C.c_void_p, C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int64)]
@@ -194,6 +197,21 @@ class Context:
         vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
         self._ck(lib().pgt_frame_upload(self._h, vp(pos), vp(diam), vp(mass), vp(vel), int(f32), len(diam), b, dim))
         self.dim = dim
+
+    def upload_xy(self, pos_xy, diam, box, mass=None, vel=None):
+        """pgt_frame_upload_xy: a 2-D frame from N x 2 position rows (z = 0)."""
+        f32 = pos_xy.dtype == np.float32
+        dt = np.float32 if f32 else np.float64
+        pos_xy = np.ascontiguousarray(pos_xy, dt)
+        assert pos_xy.ndim == 2 and pos_xy.shape[1] == 2
+        diam = np.ascontiguousarray(diam, dt)
+        mass = None if mass is None else np.ascontiguousarray(mass, dt)
+        vel = None if vel is None else np.ascontiguousarray(vel, dt)
+        self._keep["frame"] = (pos_xy, diam, mass, vel)   # the copy is asynchronous
+        b = (C.c_double * 3)(*[float(x) for x in box[:3]])
+        vp = lambda a: None if a is None else a.ctypes.data_as(C.c_void_p)
+        self._ck(lib().pgt_frame_upload_xy(self._h, vp(pos_xy), vp(diam), vp(mass), vp(vel), int(f32), len(diam), b))
+        self.dim = 2
 
     def upload_part(self, pos_part, diam_part, first, n_total, box, dim=2):
         """This rank's part of a frame (rows [first, first + len(diam_part)) of the N x 3 positions); assemble the frame

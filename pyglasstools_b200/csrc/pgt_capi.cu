@@ -356,6 +356,7 @@ int set_box(pgt_ctx* ctx, const double box[3], int dim)
         ctx->box.L[d] = ctx->box.hi[d] - ctx->box.lo[d];   // Aboria: bmax - bmin
     }
     ctx->box.dim = dim;
+    ctx->box.pstride = 3;
     ctx->vol = dim == 2 ? L[0] * L[1] : L[0] * L[1] * L[2];    // SimBox.cc:36-44
     return PGT_OK;
 }
@@ -629,18 +630,19 @@ static void wait_upload(pgt_ctx* ctx)
     }
 }
 
-int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel, int is_f32,
-                     int64_t N, const double box[3], int dim)
+static int frame_upload_impl(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel, int is_f32,
+                             int64_t N, const double box[3], int dim, int pstride)
 {
     if (!ctx || !pos || !diam || !box) return fail(ctx, PGT_ERR_ARG, "pgt_frame_upload: null argument");
     CK(cudaSetDevice(ctx->device));
     int rc = set_frame_common(ctx, is_f32, N, box, dim);
     if (rc != PGT_OK) return rc;
+    ctx->box.pstride = pstride;
     const size_t es = is_f32 ? 4 : 8;
-    const int k = upload_slot(ctx, (size_t)N * 3 * es, (size_t)N * es);
+    const int k = upload_slot(ctx, (size_t)N * pstride * es, (size_t)N * es);
     if (k < 0) return PGT_ERR_CUDA;
     cudaEventRecord(ctx->ev0[PGT_STAGE_UPLOAD], ctx->ul_stream);
-    CK(cudaMemcpyAsync(ctx->raw_pos2[k].p, pos, (size_t)N * 3 * es, cudaMemcpyHostToDevice, ctx->ul_stream));
+    CK(cudaMemcpyAsync(ctx->raw_pos2[k].p, pos, (size_t)N * pstride * es, cudaMemcpyHostToDevice, ctx->ul_stream));
     CK(cudaMemcpyAsync(ctx->raw_diam2[k].p, diam, (size_t)N * es, cudaMemcpyHostToDevice, ctx->ul_stream));
     cudaEventRecord(ctx->ev1[PGT_STAGE_UPLOAD], ctx->ul_stream);
     ctx->ev_valid[PGT_STAGE_UPLOAD] = true;
@@ -660,6 +662,18 @@ int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void
     }
     ctx->part_chunk = 0;
     return PGT_OK;
+}
+
+int pgt_frame_upload(pgt_ctx* ctx, const void* pos, const void* diam, const void* mass, const void* vel, int is_f32,
+                     int64_t N, const double box[3], int dim)
+{
+    return frame_upload_impl(ctx, pos, diam, mass, vel, is_f32, N, box, dim, 3);
+}
+
+int pgt_frame_upload_xy(pgt_ctx* ctx, const void* pos_xy, const void* diam, const void* mass, const void* vel, int is_f32,
+                        int64_t N, const double box[3])
+{
+    return frame_upload_impl(ctx, pos_xy, diam, mass, vel, is_f32, N, box, 2, 2);
 }
 
 int pgt_frame_upload_part(pgt_ctx* ctx, const void* pos_part, const void* diam_part, int is_f32, int64_t first, int64_t count,

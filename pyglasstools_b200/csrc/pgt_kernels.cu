@@ -52,9 +52,10 @@ __device__ __forceinline__ int cell_coord(double v, double lo, double inv_cw, in
 template <bool F32>
 __device__ __forceinline__ bool load_wrapped(const void* pos, long long i, const PgtBox& box, double& x, double& y, int* eflags)
 {
-    x = ld_real<F32>(pos, 3 * i);
-    y = ld_real<F32>(pos, 3 * i + 1);
-    double z = ld_real<F32>(pos, 3 * i + 2);
+    const long long row = (long long)box.pstride * i;
+    x = ld_real<F32>(pos, row);
+    y = ld_real<F32>(pos, row + 1);
+    const double z = box.pstride == 3 ? ld_real<F32>(pos, row + 2) : 0.0;
     bool alive = wrap_axis(x, box.lo[0], box.hi[0], eflags);
     alive = wrap_axis(y, box.lo[1], box.hi[1], eflags) && alive;
     // third axis is non-periodic in 2-D: out of [lo,hi) or non-finite => deleted
@@ -558,10 +559,12 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
         // UNR candidates of the span per turn: their loads are issued together (the search is bound by the latency of
         // these loads, not by their bytes); the tests and the hits keep the visiting order
         const int m = min(qe - q, UNR);
-        double rsqv[UNR];
+        double rsqv[UNR], djv[UNR];
 #pragma unroll
         for (int u = 0; u < UNR; ++u) {
-            const double2 r = __ldg(fr.sxy + (u < m ? q + u : q));
+            const int qq = u < m ? q + u : q;
+            const double2 r = __ldg(fr.sxy + qq);
+            djv[u] = __ldg(fr.sd + qq);                 // with the position: a hit does not wait for a second load
             const double dx = r.x - cpx, dy = r.y - cpy;
             rsqv[u] = dx * dx + dy * dy;
         }
@@ -571,7 +574,7 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
             const int qq = q + u;
             // the particle itself is skipped (IrvingKirkwood.h:97), tested on hits only
             if (u < m && !(rsq > rc2) && qq != p) {
-                const double dj = __ldg(fr.sd + qq);
+                const double dj = djv[u];
                 if (pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) {
                     if (n < PGT_NB_SLOTS) {
                         nb_list[(size_t)n * fr.n + p] = (unsigned)qq | (code << 28);
@@ -660,8 +663,8 @@ static void launch_bonds_model(int mode, const PgtPot& pot, PgtFrameView fr, Pgt
     const int blocks = (fr.n + 127) / 128;
     switch (mode) {
     case 4: {
-        // candidates loaded per turn (developer knob; measured at cfg5: 1: 0.581, 2: 0.577, 3: 0.563, 4: 0.562, 6: 0.597 ms per bond stage)
-        static const int unr = getenv("PGT_FIND_UNROLL") ? atoi(getenv("PGT_FIND_UNROLL")) : 4;
+        // candidates loaded per turn (developer knob; measured at cfg5 with the diameters loaded alongside: 2: 0.544, 3: 0.536, 4: 0.569 ms per bond stage; 1 without: 0.581)
+        static const int unr = getenv("PGT_FIND_UNROLL") ? atoi(getenv("PGT_FIND_UNROLL")) : 3;
         unsigned* nb = reinterpret_cast<unsigned*>(nbr_j);
         unsigned short* pmk = reinterpret_cast<unsigned short*>(out.b);
         if (unr == 1) k_bonds_find<MODEL, 1><<<blocks, 128, 0, st>>>(pot, fr, box, cells, rc2, counts, nb, pmk, out.j);

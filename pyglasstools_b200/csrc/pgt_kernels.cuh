@@ -22,6 +22,7 @@ enum { PGT_EFLAG_Z_NONZERO = 1, PGT_EFLAG_WRAP_RUNAWAY = 2, PGT_EFLAG_BOND_OVERF
 struct PgtBox {
     double lo[3], hi[3], L[3];
     int dim;
+    int pstride;                 // components per row of the raw position array: 3 (x y z), or 2 (x y; pgt_frame_upload_xy)
 };
 
 struct PgtCells {

@@ -704,3 +704,39 @@ def test_symmetric_packed_readback(gpu_ctx, orc, fixture_frames):
     gpu_ctx.ik_download_wait()
     assert np.array_equal(out.array, full[:, [0, 1, 3]])
     assert np.array_equal(full[:, 1], full[:, 2])
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_upload_xy_rows_give_the_same_bits_as_xyz_rows(gpu_ctx, dtype):
+    """pgt_frame_upload_xy (N x 2 position rows of a 2-D frame) against pgt_frame_upload of the same frame with a zero z
+    column: same live particles, same records, same field, bit for bit."""
+    fr = synth.synth_frame(96, 2024, velocities=True)
+    pos = fr["position"].astype(dtype)
+    pos[7, 0] += dtype(fr["box"][0])                       # one particle outside the box: wrapped
+    diam, vel = fr["diameter"].astype(dtype), fr["velocity"].astype(dtype)
+    rc = 1.25
+    gpu_ctx.set_potential("poly12", rc, [1.0, 0.2, -28.0 / rc**12, 48.0 / rc**14, -21.0 / rc**16])
+    gpu_ctx.set_max_rcut(rc * float(diam.max()))
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    axis = synth.linspace_axis(float(fr["box"][0]), 80)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+    got = []
+    for xy in (False, True):
+        if xy:
+            gpu_ctx.upload_xy(np.ascontiguousarray(pos[:, :2]), diam, fr["box"], vel=vel)
+        else:
+            gpu_ctx.upload(pos, diam, fr["box"], vel=vel)
+        gpu_ctx.build_cells()
+        gpu_ctx.build_bonds()
+        gpu_ctx.ik_compute(_capi.OBS_VIRIAL | _capi.OBS_KINETIC)
+        got.append((gpu_ctx.counts(), gpu_ctx.export_bonds(), gpu_ctx.ik_download(_capi.FIELD_VIRIAL).copy(),
+                    gpu_ctx.ik_download(_capi.FIELD_KINETIC).copy(), gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY | _capi.OBS_KINETIC)))
+    a, b = got
+    assert a[0] == b[0] and a[0]["n_live"] == len(diam)
+    for u, v in zip(a[1], b[1]):
+        assert np.array_equal(u, v)
+    assert np.array_equal(a[2], b[2]) and np.abs(a[2]).max() > 0
+    assert np.array_equal(a[3], b[3]) and np.abs(a[3]).max() > 0
+    for k in ("virial", "kinetic"):
+        assert np.array_equal(a[4][k], b[4][k])
+    assert a[4]["energy"] == b[4]["energy"]
