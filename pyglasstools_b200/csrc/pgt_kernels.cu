@@ -509,19 +509,12 @@ __global__ void __launch_bounds__(128) k_bonds(PgtPot pot, PgtFrameView fr, PgtB
 // k_bonds_fill_list re-forms dx exactly as the search did (same operands, same operations -> same bits) and writes
 // the records.  Halves the neighbour searches of the count + fill pair above, which stays as the path for frames
 // where some particle has more than PGT_NB_SLOTS bonds.
-template <int MODEL, int UNR>
-__global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
-                                                    int* __restrict__ counts, unsigned* __restrict__ nb_list,
-                                                    unsigned short* __restrict__ prim_mask, int* __restrict__ eflags)
+// The search of one particle: keep(slot, entry) receives the force-carrying neighbours in visiting order (entry = sorted
+// index | image code << 28); returns their number, pm = the primary mask of the first PGT_NB_SLOTS of them.
+template <int MODEL, int UNR, class KEEP>
+__device__ __forceinline__ int bonds_search(const PgtPot& pot, const PgtFrameView& fr, const PgtBox& box, const PgtCells& cells, double rc2,
+                                            int p, double xi, double yi, double di, unsigned& pm_out, KEEP&& keep)
 {
-    const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= fr.n) return;
-    if (fr.n_dev && p >= __ldg(fr.n_dev)) {        // fr.n is only a bound (the host did not wait for the live count)
-        counts[p] = 0;
-        prim_mask[p] = 0;
-        return;
-    }
-    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
     int n = 0;
     unsigned pm = 0u;                              // bit k: record k of this particle is the bond's primary end (q visited after p)
     // The neighbour enumeration of for_each_neighbor_img (same cells, same order, same operations on the same operands),
@@ -577,7 +570,7 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
                 const double dj = djv[u];
                 if (pgt_pair_has_force<MODEL>(pot, rsq, di, dj)) {
                     if (n < PGT_NB_SLOTS) {
-                        nb_list[(size_t)n * fr.n + p] = (unsigned)qq | (code << 28);
+                        keep(n, (unsigned)qq | (code << 28));
                         if (qq >= fwd_from) pm |= 1u << n;
                     }
                     ++n;
@@ -586,6 +579,27 @@ __global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr,
         }
         q += m;
     }
+    pm_out = pm;
+    return n;
+}
+
+template <int MODEL, int UNR>
+__global__ void __launch_bounds__(128) k_bonds_find(PgtPot pot, PgtFrameView fr, PgtBox box, PgtCells cells, double rc2,
+                                                    int* __restrict__ counts, unsigned* __restrict__ nb_list,
+                                                    unsigned short* __restrict__ prim_mask, int* __restrict__ eflags)
+{
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= fr.n) return;
+    if (fr.n_dev && p >= __ldg(fr.n_dev)) {        // fr.n is only a bound (the host did not wait for the live count)
+        counts[p] = 0;
+        prim_mask[p] = 0;
+        return;
+    }
+    const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
+    unsigned pm;
+    const size_t stride = (size_t)fr.n;
+    const int n = bonds_search<MODEL, UNR>(pot, fr, box, cells, rc2, p, xi, yi, di, pm,
+                                           [&](int slot, unsigned e) { nb_list[(size_t)slot * stride + p] = e; });
     counts[p] = n;
     prim_mask[p] = (unsigned short)pm;
     if (n > PGT_NB_SLOTS) atomicOr(eflags, PGT_EFLAG_BOND_OVERFLOW);
