@@ -84,11 +84,15 @@ __global__ void __launch_bounds__(256) k3_sort_gather(const void* __restrict__ p
     const int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= ncells) return;
     const int b = cell_start[c], e = cell_start[c + 1];
-    for (int k = b + 1; k < e; ++k) {
-        const int v = sorted_orig[k];
-        int j = k - 1;
-        while (j >= b && sorted_orig[j] > v) { sorted_orig[j + 1] = sorted_orig[j]; --j; }
-        sorted_orig[j + 1] = v;
+    if (e - b <= 24) {
+        for (int k = b + 1; k < e; ++k) {
+            const int v = sorted_orig[k];
+            int j = k - 1;
+            while (j >= b && sorted_orig[j] > v) { sorted_orig[j + 1] = sorted_orig[j]; --j; }
+            sorted_orig[j + 1] = v;
+        }
+    } else {
+        pgt_heapsort_ids(sorted_orig + b, e - b);
     }
     for (int p = b; p < e; ++p) {
         const long long i = sorted_orig[p];

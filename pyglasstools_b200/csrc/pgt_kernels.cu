@@ -258,9 +258,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_scan_chained(const int* in, in
                 const int idx = look - lane;
                 unsigned long long st = SCAN_PREFIX;                           // before tile 0: prefix 0
                 if (idx >= 0) st = *reinterpret_cast<volatile unsigned long long*>(state + idx);
-                if (__any_sync(FULL_MASK, (st >> 62) == 0)) continue;          // a predecessor has not published yet
                 const unsigned pref = __ballot_sync(FULL_MASK, (st >> 62) == 2);
                 const int stop = pref ? __ffs(pref) - 1 : 31;                  // nearest predecessor holding a prefix
+                // only the predecessors between this tile and that one have to have published; farther ones do not matter
+                const unsigned need = stop >= 31 ? FULL_MASK : ((2u << stop) - 1u);
+                if (__ballot_sync(FULL_MASK, (st >> 62) == 0) & need) continue;
                 int x = lane <= stop ? (int)(unsigned)(st & SCAN_VALUE) : 0;
 #pragma unroll
                 for (int d = 16; d >= 1; d >>= 1) x += __shfl_xor_sync(FULL_MASK, x, d);
@@ -360,14 +362,18 @@ __global__ void __launch_bounds__(256) k_cell_sort_gather(const void* __restrict
     // n_cap: particles the sorted arrays hold (the live count, or last frame's plus a margin when the host did not wait
     // for this frame's: an overflow is reported through the sticky error word, never written past the arrays)
     const int b = cell_start[c], e = min(cell_start[c + 1], n_cap);
-    for (int i = b + 1; i < e; ++i) {                        // insertion sort: cells hold a handful of particles
-        const int key = sorted_orig[i];
-        int j = i - 1;
-        while (j >= b && sorted_orig[j] > key) {
-            sorted_orig[j + 1] = sorted_orig[j];
-            --j;
+    if (e - b <= 24) {
+        for (int i = b + 1; i < e; ++i) {                    // insertion sort: cells hold a handful of particles
+            const int key = sorted_orig[i];
+            int j = i - 1;
+            while (j >= b && sorted_orig[j] > key) {
+                sorted_orig[j + 1] = sorted_orig[j];
+                --j;
+            }
+            sorted_orig[j + 1] = key;
         }
-        sorted_orig[j + 1] = key;
+    } else {
+        pgt_heapsort_ids(sorted_orig + b, e - b);            // a clustered frame or a large cell side: O(k log k), not O(k^2)
     }
     for (int p = b; p < e; ++p) {
         const long long i = sorted_orig[p];

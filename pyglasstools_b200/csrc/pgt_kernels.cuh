@@ -102,6 +102,28 @@ struct PgtThermoOut { double v[32]; };   // virial 4, kinetic 4, energy 1, born 
 // ---- launch wrappers (defined in pgt_kernels.cu) ---------------------------------------------
 struct PgtLaunchCounter { long long n; };
 
+// In-place heapsort of a cell's particle ids (ascending): the path for cells with many members.
+__device__ inline void pgt_heapsort_ids(int* a, int n)
+{
+    auto sift = [&](int root, int end) {
+        const int v = a[root];
+        for (;;) {
+            int child = 2 * root + 1;
+            if (child >= end) break;
+            if (child + 1 < end && a[child + 1] > a[child]) ++child;
+            if (a[child] <= v) break;
+            a[root] = a[child];
+            root = child;
+        }
+        a[root] = v;
+    };
+    for (int i = n / 2 - 1; i >= 0; --i) sift(i, n);
+    for (int end = n - 1; end > 0; --end) {
+        const int t = a[0]; a[0] = a[end]; a[end] = t;
+        sift(0, end);
+    }
+}
+
 // ---- Dim = 3 (pgt_dim3.cu): the reference's 3-D typedefs, parity kernels
 struct Pgt3Cells {
     int ncx, ncy, ncz;

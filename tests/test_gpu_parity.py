@@ -740,3 +740,40 @@ def test_upload_xy_rows_give_the_same_bits_as_xyz_rows(gpu_ctx, dtype):
     for k in ("virial", "kinetic"):
         assert np.array_equal(a[4][k], b[4][k])
     assert a[4]["energy"] == b[4]["energy"]
+
+
+def test_crowded_cell_sorts_in_n_log_n_and_matches_the_oracle(gpu_ctx, orc):
+    """A clustered frame: 1 024 particles inside one unit patch (a handful of cells hold hundreds of members each, the per-cell
+    sort takes its heapsort path, every particle has far more than 16 bonds so the bond list takes its two-search path);
+    live count, neighbour and bond counts, thermo sums and the field on a few grid points against the oracle."""
+    rng = np.random.default_rng(31)
+    L = 24.0
+    bg = synth.synth_frame(24, 5)
+    ii, jj = np.meshgrid(np.arange(32), np.arange(32), indexing="ij")
+    patch = np.zeros((1024, 3), np.float32)
+    patch[:, 0] = (3.0 + (ii.ravel() + 0.5) / 32 + rng.uniform(-0.004, 0.004, 1024)).astype(np.float32)
+    patch[:, 1] = (-2.0 + (jj.ravel() + 0.5) / 32 + rng.uniform(-0.004, 0.004, 1024)).astype(np.float32)
+    pos = np.concatenate([bg["position"], patch])
+    order = rng.permutation(len(pos))                       # ids of the patch are scattered over the frame
+    pos = pos[order]
+    diam = np.concatenate([bg["diameter"], np.full(1024, 1.0, np.float32)])[order]
+    box = np.array([L, L, 1.0])
+    P = orc.potential("poly12")
+    S = setup_ctx(gpu_ctx, orc, P, "poly12", pos, diam, box)
+    gpu_ctx.build_bonds()
+    cnt = gpu_ctx.counts()
+    assert cnt["n_live"] == len(diam)
+    oi, oj, _, ofl = S.neighbor_pairs(P)
+    gi, gj = gpu_ctx.export_neighbors()
+    assert len(gi) == len(oi) and pairs_key(gi, gj) == pairs_key(oi, oj)
+    assert cnt["n_halfbonds"] == int(ofl.sum()) and cnt["n_halfbonds"] > 200 * 1024
+    t = gpu_ctx.thermo(_capi.OBS_VIRIAL | _capi.OBS_ENERGY)
+    w = S.thermo(P, born=False)
+    assert_close(t["virial"], w["virial"], atol=1e-12 * np.abs(w["virial"]).max())
+    assert_close(t["energy"], w["energy"])
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    grid = np.array([[3.5, -1.5, 0.0], [2.0, -3.0, 0.0], [-8.0, 7.0, 0.0], [5.2, -1.0, 0.0]])
+    gpu_ctx.set_grid_points(grid)
+    gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+    want = S.ik(P, orc.cgfunc("octic", 2.0, 5), grid)["virial"]
+    assert_close(gpu_ctx.ik_download(_capi.FIELD_VIRIAL), want, atol=1e-12 * np.abs(want).max())
