@@ -384,7 +384,7 @@ def main():
     ap.add_argument("--e2e-field", default="sym", choices=("auto", "full", "sym"),
                     help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy); auto: full on one GPU, sym on several (the host's PCIe / memory path is shared)")
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
-    ap.add_argument("--e2e-lanes", type=int, default=1, choices=(1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over; 1 (default): one context pipelines upload / stages / read-back on its own three streams")
+    ap.add_argument("--e2e-lanes", type=int, default=2, choices=(1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over (default 2, one host thread each: measured fastest, 2.38 ms per frame at cfg5); 1: one context and one host thread pipeline upload / stages / read-back on the context's three streams (2.54 ms; timed beside the default as e2e_one_context)")
     ap.add_argument("--e2e-buffers", type=int, default=3, choices=(2, 3, 4), help="host field buffers the single-context loop reads back into in turn")
     ap.add_argument("--e2e-pos", default="xy", choices=("xy", "xyz"), help="host position rows of the end-to-end loop: xy = N x 2 float32 through pgt_frame_upload_xy (a 2-D frame has no z column: 12 B per particle cross the link; default), xyz = N x 3 through pgt_frame_upload (the GSD layout, 16 B)")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
@@ -659,22 +659,29 @@ def main():
     # for comparison, the same loop with the other layout of the position rows (N x 3 through pgt_frame_upload: 16 bytes per
     # particle up; N x 2 through pgt_frame_upload_xy: 12).  At one GPU the link is not the bound and the two agree; with 4-8
     # ranks sharing one host the bytes count
-    e2e_other = None
-    if args.e2e_lanes == 1 and not grid_mode and world == 1:
+    e2e_other, e2e_alt = None, None
+    if not grid_mode and world == 1:
+        main_lanes = [(c, o) for c, o in lanes[:args.e2e_lanes]] if args.e2e_lanes > 1 else [lanes[0]]
+        if args.e2e_lanes > 1:
+            ctx.set_option("async_counts", 0)
         pos_xy[0] = not pos_xy[0]
-        ms_o, _ = time_e2e([lanes[0]], args.steps, args.warmup, False, 1)
+        ms_o, _ = time_e2e(list(main_lanes), args.steps, args.warmup, False, args.e2e_threads)
         pos_xy[0] = not pos_xy[0]
-        e2e_other = ms_o / args.steps
-    # for comparison, the round-1 arrangement: three contexts, one host thread each, every stage waiting for its count
-    e2e_alt = None
-    if len(lanes) == 1 + (args.e2e_buffers - 1) and args.e2e_lanes == 1 and not grid_mode and world == 1:
-        alt = make_lanes(ctx, 3, my_shard)
-        ctx.set_option("async_counts", 0)
-        ms_alt, _ = time_e2e(alt, args.steps, args.warmup, False, 2)
         ctx.set_option("async_counts", 1)
+        e2e_other = ms_o / args.steps
+        # for comparison, the other arrangement: ONE context and one host thread pipelining upload / stages / read-back on
+        # the context's three streams with deferred counts (when the default is several contexts), or three contexts with a
+        # host thread each (when one context was asked for)
+        if args.e2e_lanes > 1:
+            ms_alt, _ = time_e2e([lanes[0]], args.steps, args.warmup, False, 1)
+        else:
+            alt = make_lanes(ctx, 3, my_shard)
+            ctx.set_option("async_counts", 0)
+            ms_alt, _ = time_e2e(alt, args.steps, args.warmup, False, 2)
+            ctx.set_option("async_counts", 1)
+            for c, _ in alt[1:]:
+                c.close()
         e2e_alt = ms_alt / args.steps
-        for c, _ in alt[1:]:
-            c.close()
 
     # ---- N > 1: one frame split over the ranks by grid points (the reference's MPI decomposition), strong scaling
     grid_shard = None
@@ -792,9 +799,9 @@ def main():
             ("e2e_xyz_upload" if pos_xy[0] else "e2e_xy_upload"): None if e2e_other is None else {
                 "value": G / (e2e_other * 1e-3), "unit": UNIT, "ms_per_step": e2e_other, "h2d_bytes_per_step": N * (16 if pos_xy[0] else 12),
                 "api": "the same loop through %s, for comparison" % ("pgt_frame_upload with N x 3 float32 position rows (the GSD layout)" if pos_xy[0] else "pgt_frame_upload_xy (N x 2 float32 position rows)")},
-            "e2e_three_contexts": None if e2e_alt is None else {
+            ("e2e_one_context" if args.e2e_lanes > 1 else "e2e_three_contexts"): None if e2e_alt is None else {
                 "value": G / (e2e_alt * 1e-3), "unit": UNIT, "ms_per_step": e2e_alt,
-                "api": "round-1 arrangement for comparison: three contexts, one host thread each, every stage waits for its count"},
+                "api": ("for comparison: ONE context and one host thread, upload / stages / read-back pipelined on the context's three streams, counts deferred (no host synchronisation between stages)" if args.e2e_lanes > 1 else "for comparison: three contexts, one host thread each, every stage waits for its count")},
             "e2e_link": "%.0f MB per frame cross PCIe (H2D %.0f + D2H %.0f); the link itself moves that in ~2.0-2.1 ms with both directions busy (tools/link_probe.py: 55 / 56 GB/s alone, ~84 GB/s together), less than the stages take; what the end-to-end loop loses against the resident one is the slowdown of the memory-bound stages while the read-back's DMA runs beside them (tools/pipe_probe.py: cells 0.22 -> 0.32 ms, bonds 0.53 -> 0.65 ms, gather +0.02 ms)" % ((h2d + d2h) / 1e6, h2d / 1e6, d2h / 1e6),
             "gpu_launches": launches_total,
             "stage_ms": {"cells": cells_ms, "bonds": bonds_ms, "ik": ik_avg_ms},
