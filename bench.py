@@ -264,6 +264,9 @@ def setup_ctx(_capi, synth, device, wl, dmax, L):
     return ctx
 
 
+LANE_ASYNC = int(os.environ.get("PGT_BENCH_LANE_ASYNC", "0"))   # developer knob: deferred counts inside multi-context e2e lanes
+
+
 def stage_bytes(N, ncells, n_hb):
     """Algorithmic HBM bytes per frame of the two memory-bound stages:
     cells  60 B / particle (16 raw float32 read + 4 key + 4 slot + 4 sorted id + 32 sorted x, y, (x,y), d written)
@@ -493,7 +496,7 @@ def main():
             cb.set_shard(*shard)
             # several contexts: each stage waits for its count, which keeps the kernels of different frames from
             # co-running on the device (measured: 2.46 against 2.58 ms per frame at cfg5 with deferred counts)
-            cb.set_option("async_counts", 0)
+            cb.set_option("async_counts", LANE_ASYNC)
             lanes.append((cb, _capi.PinnedArray((shard[1] - shard[0], ncomp_out), np.float64)))
         return lanes
 
@@ -651,7 +654,7 @@ def main():
     if grid_mode:
         comm_init_all([c for c, _ in lanes])
     if len(lanes) > 1:
-        ctx.set_option("async_counts", 0)
+        ctx.set_option("async_counts", LANE_ASYNC)
     ms_e2e, win_b = time_e2e(lanes, args.steps, args.warmup, grid_mode, args.e2e_threads)
     ctx.set_option("async_counts", 1)
     e2e_check = float(sum(np.abs(o.array).sum() for _, o in lanes))   # the read-backs are real
