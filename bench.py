@@ -359,20 +359,46 @@ def thermo_workload(_capi, synth, device, nframes=1000):
     dmax = max(float(fr["diameter"].max()) for fr in pool)
     ctx.set_max_rcut(max(rc * dmax, dmax))
     mask = _capi.OBS_VIRIAL | _capi.OBS_ENERGY
+    # page-locked frames and results; pgt_thermo_compute_async + deferred counts: the loop never waits for the device, the
+    # host collects the results of 32 frames at a time
+    N = len(pool[0]["diameter"])
+    pin_pos = [_capi.PinnedArray((N, 3), np.float32) for _ in pool]
+    pin_diam = [_capi.PinnedArray((N,), np.float32) for _ in pool]
+    for k, fr in enumerate(pool):
+        pin_pos[k].array[...] = fr["position"]
+        pin_diam[k].array[...] = fr["diameter"]
+    ring = [_capi.PinnedArray((25,), np.float64) for _ in range(32)]
+    box = pool[0]["box"]
+    check = []
     for f in range(16):
-        fr = pool[f % len(pool)]
-        ctx.upload(fr["position"], fr["diameter"], fr["box"])
+        k = f % len(pool)
+        ctx.upload(pin_pos[k].array, pin_diam[k].array, box)
         ctx.build_cells()
-        ctx.thermo(mask)
+        t = ctx.thermo(mask)
+        if f < len(pool):
+            check.append(np.concatenate([t["virial"], t["kinetic"], [t["energy"]], t["born"]]))
     t0 = time.perf_counter()
     for f in range(nframes):
-        fr = pool[f % len(pool)]
-        ctx.upload(fr["position"], fr["diameter"], fr["box"])
+        k = f % len(pool)
+        ctx.upload(pin_pos[k].array, pin_diam[k].array, box)
+        ctx.build_cells()
+        ctx.thermo_async(mask, ring[f % len(ring)].array)
+        if f % len(ring) == len(ring) - 1:
+            ctx.sync()                                   # the 32 results are consumed here
+    ctx.sync()
+    dt = time.perf_counter() - t0
+    last = (nframes - 1) % len(pool)
+    assert np.array_equal(ring[(nframes - 1) % len(ring)].array, check[last]), "asynchronous thermo sums differ from the synchronous ones"
+    t1 = time.perf_counter()
+    for f in range(min(nframes, 200)):
+        k = f % len(pool)
+        ctx.upload(pin_pos[k].array, pin_diam[k].array, box)
         ctx.build_cells()
         ctx.thermo(mask)
-    dt = time.perf_counter() - t0
-    out = {"description": "BASELINE configs[1]: thermo virial + energy, synthetic N=65536, %d frames through the C-ABI (upload, cells, pair sums, read-back per frame)" % nframes,
-           "value": nframes / dt, "unit": "frames/s", "device_ms": {"cells": ctx.stage_ms("cells"), "thermo": ctx.stage_ms("thermo")}}
+    dt_sync = (time.perf_counter() - t1) / min(nframes, 200)
+    out = {"description": "BASELINE configs[1]: thermo virial + energy, synthetic N=65536, %d frames through the C-ABI from page-locked host buffers (pgt_frame_upload, pgt_build_cells, pgt_thermo_compute_async; the host collects 32 frames' results at a time)" % nframes,
+           "value": nframes / dt, "unit": "frames/s", "synchronous_frames_per_s": 1.0 / dt_sync,
+           "device_ms": {"cells": ctx.stage_ms("cells"), "thermo": ctx.stage_ms("thermo")}}
     ctx.close()
     return out
 

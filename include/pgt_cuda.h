@@ -152,6 +152,11 @@ int pgt_ik_device_ptr(pgt_ctx* ctx, int field_id, void** d_ptr, int64_t* n_doubl
  * then Dim^4 Born tensor (col-major flat); all already multiplied by 1/vol.  Entries whose
  * observable is not in obs_mask are 0.  out must hold 2*Dim^2 + 1 + Dim^4 doubles.              */
 int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out);
+/* The same without a host synchronisation: `out` (25 doubles, page-locked for a truly asynchronous copy) is valid after
+ * pgt_synchronize.  With the option "async_counts" a trajectory loop of pgt_frame_upload / pgt_build_cells /
+ * pgt_thermo_compute_async never waits for the device (the reference's loop, thermo/ThermoCalculator.h:68-90, is
+ * synchronous: this is the thermo counterpart of pgt_ik_download_async).  2-D frames.                              */
+int pgt_thermo_compute_async(pgt_ctx* ctx, unsigned obs_mask, double* out);
 /* No counterpart in the reference: added for callers that cannot call cudaMalloc
  * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same inputs, same kernels, same
  * block partition and same `out` layout as pgt_thermo_compute, but the per-block partial sums and the reduced result

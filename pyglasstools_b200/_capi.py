@@ -28,7 +28,7 @@ EXPORTED = [
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
     "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep", "pgt_thermo_compute_static",
-    "pgt_frame_upload_xy",
+    "pgt_frame_upload_xy", "pgt_thermo_compute_async",
 ]
 
 _lib = None
@@ -105,6 +105,7 @@ def lib():
         L.pgt_ik_device_ptr.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_void_p), C.POINTER(C.c_int64)]
         L.pgt_thermo_compute.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
         L.pgt_thermo_compute_static.argtypes = [C.c_void_p, C.c_uint, C.POINTER(C.c_double)]
+        L.pgt_thermo_compute_async.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
         L.pgt_thermo_elastic.argtypes = [C.c_void_p, C.POINTER(C.c_double)]
         L.pgt_frame_set_displacement.argtypes = [C.c_void_p, C.POINTER(C.c_double), C.c_int64]
         L.pgt_export_bonds.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.c_void_p, C.c_void_p, C.c_void_p,
@@ -302,6 +303,11 @@ class Context:
         out = np.zeros(2 * D2 + 1 + D4, np.float64)
         self._ck(lib().pgt_thermo_compute(self._h, int(obs_mask), _dp(out)))
         return dict(virial=out[0:D2].copy(), kinetic=out[D2:2 * D2].copy(), energy=float(out[2 * D2]), born=out[2 * D2 + 1:].copy())
+
+    def thermo_async(self, obs_mask, out):
+        """pgt_thermo_compute_async: the 25 doubles (virial 4 | kinetic 4 | energy | born 16) land in `out` (a page-locked
+        float64 array of at least 25 entries) once the context has been synchronised."""
+        self._ck(lib().pgt_thermo_compute_async(self._h, int(obs_mask), out.ctypes.data_as(C.c_void_p)))
 
     def thermo_static(self, obs_mask=OBS_VIRIAL | OBS_ENERGY):
         """pgt_thermo_compute_static: the same sums with the library's static device scratch, no allocation in the call."""

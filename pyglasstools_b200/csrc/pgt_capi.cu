@@ -1527,6 +1527,32 @@ int pgt_thermo_compute(pgt_ctx* ctx, unsigned obs_mask, double* out)
     return PGT_OK;
 }
 
+// The same sums without a host synchronisation: the 25 doubles are copied into `out` (page-locked memory for a copy that
+// really is asynchronous) behind the kernels on the context's stream, valid after pgt_synchronize.  With deferred counts
+// (option async_counts) a trajectory loop of upload / cells / thermo never waits for the device.
+int pgt_thermo_compute_async(pgt_ctx* ctx, unsigned obs_mask, double* out)
+{
+    if (!ctx || !out) return fail(ctx, PGT_ERR_ARG, "pgt_thermo_compute_async: null argument");
+    if (!ctx->cells_built) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_async: cells not built");
+    if (!ctx->have_pot) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_async: no pair potential");
+    if (ctx->culled) return fail(ctx, PGT_ERR_STATE, "pgt_thermo_compute_async: the frame holds a grid shard's particles only");
+    if (ctx->dim != 2) return fail(ctx, PGT_ERR_UNSUPPORTED, "pgt_thermo_compute_async: 2-D frames only");
+    if (ctx->thermo_nparts > 1) RESOLVE();                     // the particle shares are cut from the exact live count
+    CK(cudaSetDevice(ctx->device));
+    const int blocks = pgt_thermo_blocks(ctx->n_live);
+    const int p_begin = (int)((long long)ctx->n_live * ctx->thermo_part / ctx->thermo_nparts);
+    const int p_end = (int)((long long)ctx->n_live * (ctx->thermo_part + 1) / ctx->thermo_nparts);
+    ENSURE(ctx->thermo_partials, sizeof(double) * 25 * (size_t)blocks);
+    ENSURE(ctx->thermo_out, sizeof(double) * 32);
+    stage_begin(ctx, PGT_STAGE_THERMO);
+    pgt_launch_thermo(ctx->pot, frame_view(ctx), ctx->box, ctx->cells, ctx->max_rcut, obs_mask, 1 / ctx->vol,
+                      ctx->thermo_partials.as<double>(), blocks, ctx->thermo_out.as<double>(), p_begin, p_end, ctx->stream, &ctx->launches);
+    CK(cudaGetLastError());
+    stage_end(ctx, PGT_STAGE_THERMO);
+    CK(cudaMemcpyAsync(out, ctx->thermo_out.p, sizeof(double) * 25, cudaMemcpyDeviceToHost, ctx->stream));
+    return PGT_OK;
+}
+
 // ---- pgt_thermo_compute_static: the thermo pair sums with no allocation at all -------------------------------------
 // The per-block partial sums and the reduced result live in ONE file-scope device array instead of the context's
 // cudaMalloc'ed buffers.  Every device that loads this library holds the array until the process exits; every context

@@ -751,7 +751,9 @@ __global__ void __launch_bounds__(THERMO_THREADS) k_thermo_pairs(PgtPot pot, Pgt
 #pragma unroll
     for (int k = 0; k < THERMO_NVAL; ++k) acc[k] = 0.0;
 
-    // [p_begin, p_end): this rank's share of the sorted particles (pgt_thermo_set_shard; the whole frame by default)
+    // [p_begin, p_end): this rank's share of the sorted particles (pgt_thermo_set_shard; the whole frame by default); when the
+    // host did not wait for the live count (pgt_thermo_compute_async) p_end is only a bound and the count is read here
+    if (fr.n_dev) p_end = min(p_end, __ldg(fr.n_dev));
     for (int p = p_begin + blockIdx.x * blockDim.x + threadIdx.x; p < p_end; p += gridDim.x * blockDim.x) {
         const double xi = fr.sx[p], yi = fr.sy[p], di = fr.sd[p];
         const int oi = fr.sorig[p];

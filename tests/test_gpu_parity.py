@@ -777,3 +777,39 @@ def test_crowded_cell_sorts_in_n_log_n_and_matches_the_oracle(gpu_ctx, orc):
     gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
     want = S.ik(P, orc.cgfunc("octic", 2.0, 5), grid)["virial"]
     assert_close(gpu_ctx.ik_download(_capi.FIELD_VIRIAL), want, atol=1e-12 * np.abs(want).max())
+
+
+def test_thermo_async_over_a_trajectory_equals_the_synchronous_sums(orc):
+    """pgt_thermo_compute_async in a loop that never waits (deferred counts): every frame's 25 doubles equal
+    pgt_thermo_compute's bit for bit, and the first frame's equal the oracle's."""
+    ctx = _capi.Context(0)
+    try:
+        frames = [synth.synth_frame(96, 300 + f, velocities=True) for f in range(6)]
+        P = orc.potential("poly12")
+        ctx.set_potential("poly12", P.scaled_rcut, orc.pot_params(P))
+        dmax = max(float(f["diameter"].max()) for f in frames)
+        ctx.set_max_rcut(max(P.scaled_rcut * dmax, dmax))
+        mask = _capi.OBS_VIRIAL | _capi.OBS_ENERGY | _capi.OBS_KINETIC | _capi.OBS_BORN
+        want = []
+        for fr in frames:
+            ctx.upload(fr["position"], fr["diameter"], fr["box"], vel=fr["velocity"])
+            ctx.build_cells()
+            t = ctx.thermo(mask)
+            want.append(np.concatenate([t["virial"], t["kinetic"], [t["energy"]], t["born"]]))
+        outs = [_capi.PinnedArray((25,), np.float64) for _ in frames]
+        for o in outs:
+            o.array[...] = -1.0
+        for rep in range(2):                                # the second pass runs with the counts deferred
+            for fr, o in zip(frames, outs):
+                ctx.upload(fr["position"], fr["diameter"], fr["box"], vel=fr["velocity"])
+                ctx.build_cells()
+                ctx.thermo_async(mask, o.array)
+            ctx.sync()
+            for o, w in zip(outs, want):
+                assert np.array_equal(o.array, w)
+        S = orc.System(frames[0]["box"], frames[0]["position"], frames[0]["diameter"], vel=frames[0]["velocity"])
+        w0 = S.thermo(P)
+        assert_close(want[0][0:4], w0["virial"])
+        assert_close(want[0][8], w0["energy"])
+    finally:
+        ctx.close()
