@@ -71,8 +71,8 @@ private:
 
 class ParticleSystem {
 public:
-    ParticleSystem(std::shared_ptr<SimBox> box, unsigned int n, DArray diameter, DArray mass, DArray position, DArray velocity);
-    void assign(unsigned int n, DArray diameter, DArray mass, DArray position, DArray velocity);
+    ParticleSystem(std::shared_ptr<SimBox> box, unsigned int n, py::array diameter, py::array mass, py::array position, py::array velocity);
+    void assign(unsigned int n, py::array diameter, py::array mass, py::array position, py::array velocity);
 
     std::size_t size() const { return m_diam.size(); }
     std::shared_ptr<SimBox> simbox;

@@ -1,4 +1,5 @@
 // host_core.cpp -- device session, SimBox, ParticleSystem, Manager, Communicator / LogFile shims.
+#include <algorithm>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -6,6 +7,7 @@
 #include <cstring>
 #include <iostream>
 #include <sstream>
+#include <thread>
 
 #include "host_common.h"
 #include "host_io.h"
@@ -106,23 +108,124 @@ static void copy_vec(const DArray& a, std::size_t n, std::vector<double>& out, c
     out.assign(a.data(), a.data() + n);
 }
 
-ParticleSystem::ParticleSystem(std::shared_ptr<SimBox> box, unsigned int n, DArray diameter, DArray mass, DArray position,
-                               DArray velocity)
+ParticleSystem::ParticleSystem(std::shared_ptr<SimBox> box, unsigned int n, py::array diameter, py::array mass, py::array position,
+                               py::array velocity)
     : simbox(std::move(box)), m_uid(g_next_uid++)
 {
     if (!simbox) throw std::invalid_argument("[ERROR]: ParticleSystem needs a SimBox");
     assign(n, std::move(diameter), std::move(mass), std::move(position), std::move(velocity));
 }
 
-void ParticleSystem::assign(unsigned int n, DArray diameter, DArray mass, DArray position, DArray velocity)
+namespace {
+// A frame array as the copy loop reads it: float32 or float64 rows in C order, read in place (GSD chunks are float32: no
+// float64 temporary of the whole frame); anything else goes through numpy's cast once.
+struct FrameArray {
+    py::array keep;
+    const float* f = nullptr;
+    const double* d = nullptr;
+    std::size_t row = 1;                                        // elements per row
+    double at(std::size_t i) const { return f ? (double)f[i] : d[i]; }
+};
+
+FrameArray frame_array(py::array a, std::size_t n, int ndim, const char* what)
 {
-    copy_vec(diameter, n, m_diam, "diameter");
-    copy_vec(mass, n, m_mass, "mass");
-    copy_rows3(position, n, m_pos, "position");
-    copy_rows3(velocity, n, m_vel, "velocity");
-    m_disp.assign(3 * (std::size_t)n, 0.0);
-    enforce_domain();
-    refresh_flags();
+    if (a.ndim() != ndim || (std::size_t)a.shape(0) != n || (ndim == 2 && a.shape(1) < 3))
+        throw std::invalid_argument(std::string("[ERROR]: Size of ") + what + " array mismatch with # of particles!");
+    FrameArray r;
+    const bool c_order = (a.flags() & py::array::c_style) != 0;
+    if (c_order && py::isinstance<py::array_t<float>>(a)) {
+        r.keep = a;
+        r.f = static_cast<const float*>(a.data());
+    } else {
+        r.keep = DArray(a);                                     // forcecast: one float64 copy
+        r.d = static_cast<const double*>(r.keep.data());
+    }
+    r.row = ndim == 2 ? (std::size_t)r.keep.shape(1) : 1;
+    return r;
+}
+
+template <class F>
+void parallel_chunks(std::size_t n, F&& f)
+{
+    const unsigned hw = std::thread::hardware_concurrency();
+    const int nt = (int)std::max<std::size_t>(1, std::min<std::size_t>({ hw ? hw : 1, 16, n / 65536 + 1 }));
+    if (nt <= 1) { f((std::size_t)0, n, 0); return; }
+    std::vector<std::thread> th;
+    for (int t = 1; t < nt; ++t) th.emplace_back([&f, n, nt, t] { f(n * t / nt, n * (t + 1) / nt, t); });
+    f((std::size_t)0, n / nt, 0);
+    for (auto& x : th) x.join();
+}
+}  // namespace
+
+// One pass over the frame, on several host threads for large frames: promote to FP64, Aboria's enforce_domain
+// (NeighbourSearchBase.h:208-237: periodic axes wrapped into [low, high) by repeated +-(high - low); a particle with a
+// non-finite coordinate or outside a non-periodic axis is deleted), velocity / mass flags, zero displacements.
+void ParticleSystem::assign(unsigned int n_, py::array diameter, py::array mass, py::array position, py::array velocity)
+{
+    const std::size_t n = n_;
+    const FrameArray D = frame_array(std::move(diameter), n, 1, "diameter"), M = frame_array(std::move(mass), n, 1, "mass");
+    const FrameArray P = frame_array(std::move(position), n, 2, "position"), V = frame_array(std::move(velocity), n, 2, "velocity");
+    m_diam.resize(n); m_mass.resize(n);
+    m_pos.resize(3 * n); m_vel.resize(3 * n); m_disp.resize(3 * n);
+    const SimBox& b = *simbox;
+    std::vector<unsigned char> dead_any(64, 0), vel_any(64, 0), mass_any(64, 0);
+    std::vector<unsigned char> alive(n, 1);
+    {
+        py::gil_scoped_release nogil;
+        parallel_chunks(n, [&](std::size_t i0, std::size_t i1, int t) {
+            bool anyv = false, anym = false, anydead = false;
+            for (std::size_t i = i0; i < i1; ++i) {
+                bool ok = true;
+                double r[3];
+                for (int k = 0; k < 3; ++k) {
+                    r[k] = P.at(P.row * i + k);
+                    const double lo = b.lowerbound[k], hi = b.upperbound[k], L = hi - lo;
+                    if (!std::isfinite(r[k])) { ok = false; continue; }
+                    if (b.periodic[k]) {
+                        int guard = 0;
+                        while (r[k] < lo && ++guard < (1 << 20)) r[k] += L;
+                        while (r[k] >= hi && ++guard < (1 << 20)) r[k] -= L;
+                    } else if (r[k] < lo || r[k] >= hi) ok = false;
+                }
+                for (int k = 0; k < 3; ++k) {
+                    const double v = V.at(V.row * i + k);
+                    m_pos[3 * i + k] = r[k];
+                    m_vel[3 * i + k] = v;
+                    m_disp[3 * i + k] = 0.0;
+                    anyv |= v != 0.0;
+                }
+                const double m = M.at(i);
+                m_diam[i] = D.at(i);
+                m_mass[i] = m;
+                anym |= m != 1.0;
+                if (!ok) { alive[i] = 0; anydead = true; }
+            }
+            dead_any[(std::size_t)t] = anydead; vel_any[(std::size_t)t] = anyv; mass_any[(std::size_t)t] = anym;
+        });
+    }
+    bool some_dead = false;
+    for (unsigned char c : dead_any) some_dead |= c != 0;
+    if (some_dead) {                                            // rare: compact in place, order kept
+        std::size_t w = 0;
+        for (std::size_t i = 0; i < n; ++i) {
+            if (!alive[i]) continue;
+            for (int k = 0; k < 3; ++k) {
+                m_pos[3 * w + k] = m_pos[3 * i + k];
+                m_vel[3 * w + k] = m_vel[3 * i + k];
+            }
+            m_diam[w] = m_diam[i];
+            m_mass[w] = m_mass[i];
+            ++w;
+        }
+        m_pos.resize(3 * w); m_vel.resize(3 * w); m_disp.resize(3 * w);
+        m_diam.resize(w); m_mass.resize(w);
+        refresh_flags();                                        // the deleted particles' velocities and masses do not count
+    } else {
+        has_velocity = false;
+        unit_mass = true;
+        for (unsigned char c : vel_any) has_velocity |= c != 0;
+        for (unsigned char c : mass_any) unit_mass &= c == 0;
+    }
     touch();
 }
 
@@ -359,7 +462,12 @@ void export_core(py::module_& m)
         .def_readwrite("vol", &SimBox::vol);
 
     py::class_<ParticleSystem, std::shared_ptr<ParticleSystem>>(m, "ParticleSystem")
-        .def(py::init<std::shared_ptr<SimBox>, unsigned int, DArray, DArray, DArray, DArray>())
+        // numpy arrays are read in place (float32 GSD chunks without a float64 temporary); lists and other sequences go
+        // through numpy's conversion, as the reference's std::vector arguments accept them (ParticleSystem.cc:191-205)
+        .def(py::init<std::shared_ptr<SimBox>, unsigned int, py::array, py::array, py::array, py::array>())
+        .def(py::init([](std::shared_ptr<SimBox> box, unsigned int n, DArray d, DArray m, DArray p, DArray v) {
+            return std::make_shared<ParticleSystem>(std::move(box), n, py::array(d), py::array(m), py::array(p), py::array(v));
+        }))
         .def("getMass", &ParticleSystem::getMass)
         .def("setMass", &ParticleSystem::setMass)
         .def("getDiameter", &ParticleSystem::getDiameter)
@@ -375,6 +483,9 @@ void export_core(py::module_& m)
         .def("getNeighbors", &ParticleSystem::getNeighbors)
         .def("getNeighborsDistance", &ParticleSystem::getNeighborsDistance)
         .def("update", &ParticleSystem::assign)
+        .def("update", [](ParticleSystem& ps, unsigned int n, DArray d, DArray m, DArray p, DArray v) {
+            ps.assign(n, py::array(d), py::array(m), py::array(p), py::array(v));
+        })
         .def("__len__", &ParticleSystem::size);
 
     py::class_<Observable, std::shared_ptr<Observable>>(m, "Observable")

@@ -101,6 +101,17 @@ class HOOMDTrajectory(object):
             return self.file.read_chunk(0, name)
         return default() if callable(default) else default
 
+    def _default(self, kind, n):
+        """Schema defaults for chunks a file does not hold (velocity 0, mass 1, ...): one read-only array per (kind, N),
+        shared by the frames instead of being allocated and touched anew for each."""
+        cache = self.__dict__.setdefault("_defaults", {})
+        a = cache.get((kind, n))
+        if a is None:
+            a = np.zeros((n, 3), np.float32) if kind == "zeros3" else np.ones(n, np.float32)
+            a.setflags(write=False)
+            cache[(kind, n)] = a
+        return a
+
     def read_frame(self, frame):
         frame = int(frame)
         if frame < 0:
@@ -114,10 +125,10 @@ class HOOMDTrajectory(object):
         c.box = np.asarray(self._get(frame, "configuration/box", np.array([1, 1, 1, 0, 0, 0], np.float32)), np.float32)
         p.N = int(self._get(frame, "particles/N", np.zeros(1, np.uint32))[0])
         n = p.N
-        p.position = self._get(frame, "particles/position", lambda: np.zeros((n, 3), np.float32))
-        p.velocity = self._get(frame, "particles/velocity", lambda: np.zeros((n, 3), np.float32))
-        p.diameter = self._get(frame, "particles/diameter", lambda: np.ones(n, np.float32))
-        p.mass = self._get(frame, "particles/mass", lambda: np.ones(n, np.float32))
+        p.position = self._get(frame, "particles/position", lambda: self._default("zeros3", n))
+        p.velocity = self._get(frame, "particles/velocity", lambda: self._default("zeros3", n))
+        p.diameter = self._get(frame, "particles/diameter", lambda: self._default("ones", n))
+        p.mass = self._get(frame, "particles/mass", lambda: self._default("ones", n))
         for key, shape in (("position", (n, 3)), ("velocity", (n, 3)), ("diameter", (n,)), ("mass", (n,))):
             if getattr(p, key).shape != shape:
                 raise RuntimeError("{}: particles/{} of frame {} has shape {}, expected {}".format(
