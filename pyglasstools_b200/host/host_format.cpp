@@ -6,10 +6,12 @@
 #include <charconv>
 #include <cmath>
 #include <cstdio>
+#include <atomic>
 #include <chrono>
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <thread>
 #include <vector>
 #include <algorithm>
@@ -116,8 +118,8 @@ static inline char* put_g(char* p, char* end, double v)
 static void format_range(const double* P, std::ptrdiff_t pstride, int ncoord, const std::vector<const double*>& cols,
                          const std::vector<int>& ncomp, const std::vector<int>& comps, std::size_t g0, std::size_t g1, std::string& out)
 {
-    out.clear();
-    out.reserve((g1 - g0) * (6 + 2 * 20 + 14 * cols.size()));
+    out.clear();                                             // pooled: keeps the capacity the last frame needed
+    if (out.capacity() == 0) out.reserve((g1 - g0) * (6 + 2 * 12 + 12 * cols.size()));
     // coordinates repeat heavily on Cartesian grids (every x ny times in a row, every y once per row): a small
     // direct-mapped cache of their strings, keyed on the bit pattern
     struct Slot { std::uint64_t bits; unsigned char len; char txt[30]; };
@@ -156,49 +158,93 @@ static void format_range(const double* P, std::ptrdiff_t pstride, int ncoord, co
     }
 }
 
-// The frame's lines for points [0, G) as one string: the grid is cut into contiguous chunks, one per host thread, and the
-// chunks are concatenated in order -- the same bytes as the reference's per-point loop (io.py:112-128).
-static std::vector<std::string> format_field_parts(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
-                                                   const std::vector<int>& comps, int nthreads)
+// The frame's lines for points [0, G): the grid is cut into contiguous chunks, one per host thread, and the chunks are
+// used in order -- the same bytes as the reference's per-point loop (io.py:112-128).  The chunk strings live in a
+// process-wide pool and keep their capacity from frame to frame: a fresh 70 MB of text buffers per frame costs more in
+// page faults than the formatting itself.  The pool's mutex is only ever waited for with the GIL released.
+namespace {
+struct FramePrep {
+    py::array_t<double, py::array::c_style | py::array::forcecast> pts;
+    const double* P = nullptr;
+    std::ptrdiff_t pstride = 3;
+    int ncoord = 2;
+    std::size_t G = 0;
+    std::vector<const double*> cols;
+    std::vector<int> ncomp, comps;
+    int nt = 1;
+};
+std::mutex g_parts_mu;
+std::vector<std::string> g_parts;
+}  // namespace
+
+static FramePrep prepare_frame(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                               const std::vector<int>& comps, int nthreads)
 {
     if (points.ndim() != 2 || points.shape(1) < 3) throw std::invalid_argument("[ERROR] points must be (G,3)");
     if (fields.size() != comps.size()) throw std::invalid_argument("[ERROR] one component index per field expected");
-    const std::size_t G = (std::size_t)points.shape(0);
-    std::vector<const double*> cols;
-    std::vector<int> ncomp;
-    for (std::size_t f = 0; f < fields.size(); ++f) {
-        if (!fields[f] || fields[f]->npoints != G) throw std::invalid_argument("[ERROR] field size does not match the grid");
-        if (comps[f] < 0 || comps[f] >= fields[f]->ncomp) throw std::invalid_argument("[ERROR] component index out of range");
-        cols.push_back(fields[f]->val.data());
-        ncomp.push_back(fields[f]->ncomp);
+    FramePrep f;
+    f.G = (std::size_t)points.shape(0);
+    for (std::size_t k = 0; k < fields.size(); ++k) {
+        if (!fields[k] || fields[k]->npoints != f.G) throw std::invalid_argument("[ERROR] field size does not match the grid");
+        if (comps[k] < 0 || comps[k] >= fields[k]->ncomp) throw std::invalid_argument("[ERROR] component index out of range");
+        f.cols.push_back(fields[k]->val.data());
+        f.ncomp.push_back(fields[k]->ncomp);
     }
-    py::array_t<double, py::array::c_style | py::array::forcecast> pts(points);
-    const double* P = pts.data();
-    const std::ptrdiff_t pstride = pts.shape(1);
-    const int ncoord = dim == 3 ? 3 : 2;
+    f.comps = comps;
+    f.pts = py::array_t<double, py::array::c_style | py::array::forcecast>(points);
+    f.P = f.pts.data();
+    f.pstride = f.pts.shape(1);
+    f.ncoord = dim == 3 ? 3 : 2;
     int nt = nthreads > 0 ? nthreads : (int)std::thread::hardware_concurrency();
-    nt = std::max(1, std::min<int>({ nt, 64, (int)(G / 16384) + 1 }));
-    std::vector<std::string> parts((std::size_t)nt);
-    {
-        py::gil_scoped_release nogil;
-        std::vector<std::thread> th;
-        for (int t = 1; t < nt; ++t)
-            th.emplace_back([&, t] { format_range(P, pstride, ncoord, cols, ncomp, comps, G * t / nt, G * (t + 1) / nt, parts[(std::size_t)t]); });
-        format_range(P, pstride, ncoord, cols, ncomp, comps, 0, G / nt, parts[0]);
-        for (auto& x : th) x.join();
+    f.nt = std::max(1, std::min<int>({ nt, 64, (int)(f.G / 16384) + 1 }));
+    return f;
+}
+
+// No GIL needed; the caller holds g_parts_mu.  The grid is cut into four chunks per thread; the threads take chunks in
+// order and the CALLING thread consumes each chunk (in order) as soon as it is complete, so that writing the text to the
+// file overlaps the formatting of the chunks behind it.
+template <class CONSUME>
+static void format_chunks(const FramePrep& f, CONSUME&& consume)
+{
+    const int nt = f.nt;
+    const std::size_t G = f.G;
+    const int C = nt == 1 ? 1 : 4 * nt;
+    if ((int)g_parts.size() < C) g_parts.resize((std::size_t)C);
+    if (nt == 1) {
+        format_range(f.P, f.pstride, f.ncoord, f.cols, f.ncomp, f.comps, 0, G, g_parts[0]);
+        consume(g_parts[0]);
+        return;
     }
-    return parts;
+    std::atomic<int> next{ 0 };
+    std::vector<std::atomic<int>> done((std::size_t)C);
+    for (auto& d : done) d.store(0, std::memory_order_relaxed);
+    std::vector<std::thread> th;
+    for (int t = 0; t < nt; ++t)
+        th.emplace_back([&] {
+            for (;;) {
+                const int c = next.fetch_add(1);
+                if (c >= C) break;
+                format_range(f.P, f.pstride, f.ncoord, f.cols, f.ncomp, f.comps, G * (std::size_t)c / C, G * (std::size_t)(c + 1) / C, g_parts[(std::size_t)c]);
+                done[(std::size_t)c].store(1, std::memory_order_release);
+            }
+        });
+    for (int c = 0; c < C; ++c) {
+        while (!done[(std::size_t)c].load(std::memory_order_acquire)) std::this_thread::yield();
+        consume(g_parts[(std::size_t)c]);
+    }
+    for (auto& x : th) x.join();
 }
 
 static py::bytes format_field_frame_impl(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
                                          const std::vector<int>& comps, int nthreads)
 {
-    const std::vector<std::string> parts = format_field_parts(points, dim, fields, comps, nthreads);
-    std::size_t total = 0;
-    for (auto& s : parts) total += s.size();
+    const FramePrep f = prepare_frame(points, dim, fields, comps, nthreads);
     std::string out;
-    out.reserve(total);
-    for (auto& s : parts) out += s;
+    {
+        py::gil_scoped_release nogil;
+        std::lock_guard<std::mutex> lk(g_parts_mu);
+        format_chunks(f, [&](const std::string& s) { out += s; });
+    }
     return py::bytes(out);
 }
 
@@ -208,9 +254,10 @@ static void write_field_frame(std::shared_ptr<LogFile> file, DArray points, int 
                               const std::vector<std::shared_ptr<FieldObservable>>& fields, const std::vector<int>& comps)
 {
     if (!file) throw std::invalid_argument("[ERROR] write_field_frame: no file");
-    const std::vector<std::string> parts = format_field_parts(points, dim, fields, comps, 0);
+    const FramePrep f = prepare_frame(points, dim, fields, comps, 0);
     py::gil_scoped_release nogil;
-    for (auto& s : parts) file->write_shared(s);
+    std::lock_guard<std::mutex> lk(g_parts_mu);
+    format_chunks(f, [&](const std::string& s) { file->write_shared(s); });
 }
 
 static std::string format_field_frame(DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
@@ -221,6 +268,16 @@ static std::string format_field_frame(DArray points, int dim, const std::vector<
 
 void export_format(py::module_& m)
 {
+    m.def("format_field_frame_ms", [](DArray points, int dim, const std::vector<std::shared_ptr<FieldObservable>>& fields,
+                                      const std::vector<int>& comps, int nthreads) {
+        // developer hook: milliseconds of the formatting pass alone (no join, no Python bytes, no file)
+        const FramePrep f = prepare_frame(points, dim, fields, comps, nthreads);
+        py::gil_scoped_release nogil;
+        std::lock_guard<std::mutex> lk(g_parts_mu);
+        const auto t0 = std::chrono::steady_clock::now();
+        format_chunks(f, [](const std::string&) {});
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    });
     m.def("repr_double", &repr_double);
     m.def("ostream_double", &ostream_double);
     m.def("ostream_double_fast", &ostream_double_fast);
