@@ -215,6 +215,11 @@ int pgt_event_elapsed_ms(pgt_ctx* ctx, int slot_begin, int slot_end, float* ms);
 /* Page-locked host memory for the caller's frame / field buffers (cudaHostAlloc / cudaFreeHost). */
 int pgt_host_alloc(void** ptr, uint64_t bytes);
 int pgt_host_free(void* ptr);
+/* Page-locks / releases an EXISTING host allocation (cudaHostRegister): copies from and to it then run at link speed and
+ * asynchronously.  No counterpart in the reference.  PGT_ERR_CUDA when the driver refuses: the buffer stays usable, pageable.
+ * Unregister before the memory is freed.                                                                              */
+int pgt_host_register(void* ptr, uint64_t bytes);
+int pgt_host_unregister(void* ptr);
 /* Tuning knobs: "ik_variant" (0 automatic, 2 two-phase gather, 7 quad gather where it applies);
  * "async_counts" (1 default: a frame of the same shape as the last one counted sizes its arrays from that frame's particle
  *   and half-bond counts plus a margin and does not wait for its own; counts and errors reach the host at the next

@@ -28,7 +28,7 @@ EXPORTED = [
     "pgt_ik_count_work", "pgt_event_record", "pgt_event_elapsed_ms", "pgt_host_alloc", "pgt_host_free",
     "pgt_set_option", "pgt_comm_unique_id", "pgt_comm_init", "pgt_comm_allgather_field", "pgt_comm_allreduce_sum", "pgt_comm_destroy",
     "pgt_frame_upload_part", "pgt_comm_allgather_frame", "pgt_thermo_set_shard", "pgt_ik_download_wait_keep", "pgt_thermo_compute_static",
-    "pgt_frame_upload_xy", "pgt_thermo_compute_async",
+    "pgt_frame_upload_xy", "pgt_thermo_compute_async", "pgt_host_register", "pgt_host_unregister",
 ]
 
 _lib = None
@@ -119,6 +119,8 @@ def lib():
         L.pgt_event_elapsed_ms.argtypes = [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]
         L.pgt_host_alloc.argtypes = [C.POINTER(C.c_void_p), C.c_uint64]
         L.pgt_host_free.argtypes = [C.c_void_p]
+        L.pgt_host_register.argtypes = [C.c_void_p, C.c_uint64]
+        L.pgt_host_unregister.argtypes = [C.c_void_p]
         L.pgt_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
         L.pgt_comm_unique_id.argtypes = [C.c_void_p]
         L.pgt_comm_init.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]

@@ -1340,6 +1340,21 @@ int pgt_host_alloc(void** ptr, uint64_t bytes)
     return PGT_OK;
 }
 
+int pgt_host_register(void* ptr, uint64_t bytes)
+{
+    if (!ptr || !bytes) return PGT_ERR_ARG;
+    const cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterDefault);
+    if (e != cudaSuccess) { cudaGetLastError(); return PGT_ERR_CUDA; }
+    return PGT_OK;
+}
+
+int pgt_host_unregister(void* ptr)
+{
+    if (!ptr) return PGT_ERR_ARG;
+    if (cudaHostUnregister(ptr) != cudaSuccess) { cudaGetLastError(); return PGT_ERR_CUDA; }
+    return PGT_OK;
+}
+
 int pgt_host_free(void* ptr)
 {
     if (ptr && cudaFreeHost(ptr) != cudaSuccess) return PGT_ERR_CUDA;

@@ -118,6 +118,11 @@ void Calculator::prepare_device(bool need_bonds)
     if (S.frame_token != ps.token() || S.frame_max_rcut != max_rcut) {
         S.check(pgt_set_max_rcut(ctx, max_rcut), "pgt_set_max_rcut");
         const double L[3] = { box.boxsize[0], box.boxsize[1], box.boxsize[2] };
+        // a ParticleSystem refilled frame after frame keeps its arrays where they are: page-locked in place, the upload
+        // runs at link speed (every compute path below ends with a synchronising read-back, so the arrays are not touched
+        // again before the copy has completed)
+        ps.pin_pos.ensure(ps.m_pos.data(), ps.m_pos.size() * sizeof(double));
+        ps.pin_diam.ensure(ps.m_diam.data(), ps.m_diam.size() * sizeof(double));
         S.check(pgt_frame_upload(ctx, ps.m_pos.data(), ps.m_diam.data(), ps.unit_mass ? nullptr : ps.m_mass.data(),
                                  ps.has_velocity ? ps.m_vel.data() : nullptr, 0, (int64_t)ps.size(), L, box.dim), "pgt_frame_upload");
         S.check(pgt_build_cells(ctx), "pgt_build_cells");
@@ -208,6 +213,7 @@ void IrvingKirkwood::run(long long npoints)
     for (auto& kv : m_obs) {
         FieldObservable& o = *kv.second;
         const int field = o.kind == FieldKind::Virial ? PGT_FIELD_VIRIAL : (o.kind == FieldKind::Kinetic ? PGT_FIELD_KINETIC : PGT_FIELD_ELASTIC);
+        o.pin_val.ensure(o.val.data(), o.val.size() * sizeof(double));
         S.check(pgt_ik_download(ctx, field, o.val.data()), "pgt_ik_download");
         if (ratio != 1.0)
             for (double& v : o.val) v *= ratio;

@@ -55,6 +55,31 @@ private:
     pgt_ctx* m_ctx = nullptr;
 };
 
+// A host allocation page-locked in place (pgt_host_register) for as long as it keeps its address and size: the frame
+// arrays of a ParticleSystem that is refilled frame after frame, the holders of the field observables.  Copies from and
+// to them then run at link speed instead of through the driver's pageable staging.  Registration failures are not
+// errors (the buffer stays pageable).
+struct PinnedView {
+    void* p = nullptr;
+    std::size_t bytes = 0;
+    void ensure(const void* ptr, std::size_t n)
+    {
+        if (ptr == p && n == bytes) return;
+        release();
+        if (ptr && n >= (std::size_t)1 << 20 && pgt_host_register(const_cast<void*>(ptr), n) == PGT_OK) { p = const_cast<void*>(ptr); bytes = n; }
+    }
+    void release()
+    {
+        if (p) pgt_host_unregister(p);
+        p = nullptr;
+        bytes = 0;
+    }
+    PinnedView() = default;
+    PinnedView(const PinnedView&) = delete;
+    PinnedView& operator=(const PinnedView&) = delete;
+    ~PinnedView() { release(); }
+};
+
 // ---------------------------------------------------------------------------------------------
 struct SimBox {
     SimBox(double L, const Vec3& origin, int dim);
@@ -81,6 +106,9 @@ public:
     std::vector<double> m_diam, m_mass;
     bool has_velocity = false;                    // any non-zero velocity component
     bool unit_mass = true;                        // all masses == 1
+
+    mutable PinnedView pin_pos, pin_diam;          // m_pos / m_diam page-locked in place while they keep their address
+    void unpin() const { pin_pos.release(); pin_diam.release(); }
 
     std::uint64_t token() const { return (m_uid << 20) ^ m_version; }
     void touch() { ++m_version; }
@@ -184,6 +212,7 @@ struct FieldObservable : Observable {
     int ncomp;
     std::size_t npoints;
     std::vector<double> val;                                       // npoints x ncomp, col-major per point
+    PinnedView pin_val;                                            // val page-locked in place (sized once, at construction)
     std::vector<double> points;                                    // npoints x 3
 };
 

@@ -85,7 +85,8 @@ class ikcalculator(_ikbase):
 
     def run(self):
         gp = self.gridpoints
-        if isinstance(gp, np.ndarray) and gp.shape == self._chunk_copy.shape and np.array_equal(gp, self._chunk_copy):
+        if (isinstance(gp, np.ndarray) and gp.dtype == np.float64 and gp.flags.c_contiguous and gp.shape == self._chunk_copy.shape
+                and _pyglasstools.array_equal_fast(gp, self._chunk_copy)):
             # same points, but the device generates them from the axis instead of reading G x 3 doubles
             self.calculator.compute_cartesian(self._axis, self._axis, self._g0, self._g1)
         else:

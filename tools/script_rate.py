@@ -68,7 +68,7 @@ def main():
         out["cfg1_script"] = {"description": "example_scripts/irvingkirkwood on the shipped trajectory, frames 180..199, dx = 0.25 (grid %d), text .xyz output included" % G,
                               "value": G * 20 / dt, "unit": "grid-point*frames/s", "ms_per_frame": dt / 20 * 1e3, "text_MB_per_frame": size / 20 / 1e6, "ms_split": run_script.split}
         os.remove("restart.log"); os.remove("dump.xyz")
-        nfr = 4
+        nfr = 10
         syn = [synth.synth_frame(n, 777 + k) for k in range(nfr)]
         gsdio.write_trajectory("synth.gsd", [dict(box=f["box"], position=f["position"], diameter=f["diameter"]) for f in syn])
         L = float(syn[0]["box"][0])
