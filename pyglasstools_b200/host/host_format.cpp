@@ -196,7 +196,7 @@ static FramePrep prepare_frame(DArray points, int dim, const std::vector<std::sh
     f.pstride = f.pts.shape(1);
     f.ncoord = dim == 3 ? 3 : 2;
     int nt = nthreads > 0 ? nthreads : (int)std::thread::hardware_concurrency();
-    f.nt = std::max(1, std::min<int>({ nt, 64, (int)(f.G / 16384) + 1 }));
+    f.nt = std::max(1, std::min<int>({ nt, 64, (int)(f.G / 4096) + 1 }));
     return f;
 }
 
