@@ -420,6 +420,15 @@ class Context:
         return a
 
 
+def host_register(arr):
+    """Page-locks a numpy array's memory in place (pgt_host_register); False when the driver refuses."""
+    return lib().pgt_host_register(arr.ctypes.data_as(C.c_void_p), C.c_uint64(arr.nbytes)) == 0
+
+
+def host_unregister(arr):
+    return lib().pgt_host_unregister(arr.ctypes.data_as(C.c_void_p)) == 0
+
+
 class PinnedArray:
     """A numpy view over page-locked host memory (cudaHostAlloc) owned by this object."""
 

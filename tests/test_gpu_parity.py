@@ -813,3 +813,32 @@ def test_thermo_async_over_a_trajectory_equals_the_synchronous_sums(orc):
         assert_close(want[0][8], w0["energy"])
     finally:
         ctx.close()
+
+
+def test_host_register_locks_an_existing_array_in_place(gpu_ctx):
+    """pgt_host_register / pgt_host_unregister: a frame uploaded from, and a field read back into, numpy arrays page-locked
+    in place give the same bits as pageable ones; registering twice is refused, unregistering restores the array."""
+    fr = synth.synth_frame(128, 99)
+    rc = 1.25
+    gpu_ctx.set_potential("poly12", rc, [1.0, 0.2, -28.0 / rc**12, 48.0 / rc**14, -21.0 / rc**16])
+    gpu_ctx.set_max_rcut(rc * float(fr["diameter"].max()))
+    gpu_ctx.set_cg("octic", 2.0, 5)
+    axis = synth.linspace_axis(float(fr["box"][0]), 256)
+    gpu_ctx.set_grid_cartesian(axis, axis)
+
+    def field(pos, diam, out):
+        gpu_ctx.upload(pos, diam, fr["box"])
+        gpu_ctx.build_cells(); gpu_ctx.build_bonds(); gpu_ctx.ik_compute(_capi.OBS_VIRIAL)
+        return gpu_ctx.ik_download(_capi.FIELD_VIRIAL, out)
+    want = field(fr["position"], fr["diameter"], np.empty((256 * 256, 4))).copy()
+    pos, diam, out = fr["position"].copy(), fr["diameter"].copy(), np.empty((256 * 256, 4))
+    assert _capi.host_register(pos) and _capi.host_register(diam) and _capi.host_register(out)
+    assert not _capi.host_register(out)                       # already registered
+    try:
+        got = field(pos, diam, out)
+        assert np.array_equal(got, want)
+    finally:
+        assert _capi.host_unregister(pos) and _capi.host_unregister(diam) and _capi.host_unregister(out)
+    assert not _capi.host_unregister(out)
+    pos[0, 0] += 0.0                                          # the arrays are ordinary memory again
+    assert np.array_equal(field(pos, diam, out), want)
