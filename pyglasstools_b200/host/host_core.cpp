@@ -148,7 +148,7 @@ template <class F>
 void parallel_chunks(std::size_t n, F&& f)
 {
     const unsigned hw = std::thread::hardware_concurrency();
-    const int nt = (int)std::max<std::size_t>(1, std::min<std::size_t>({ hw ? hw : 1, 16, n / 65536 + 1 }));
+    const int nt = (int)std::max<std::size_t>(1, std::min<std::size_t>({ hw ? hw : 1, 16, n / 16384 + 1 }));
     if (nt <= 1) { f((std::size_t)0, n, 0); return; }
     std::vector<std::thread> th;
     for (int t = 1; t < nt; ++t) th.emplace_back([&f, n, nt, t] { f(n * t / nt, n * (t + 1) / nt, t); });

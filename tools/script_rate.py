@@ -77,6 +77,48 @@ def main():
         G, dt, size = run_script("synth.gsd", L / n, range(0, nfr))
         out["synthetic_script"] = {"description": "the same script on a synthetic N = %d trajectory written to GSD, grid %d, %d frames, text .xyz output included" % (n * n, G, nfr),
                                    "value": G * nfr / dt, "unit": "grid-point*frames/s", "ms_per_frame": dt / nfr * 1e3, "text_MB_per_frame": size / nfr / 1e6, "ms_split": run_script.split}
+        # BASELINE configs[1] at script level: example_scripts/thermo/test-thermo-module.py's statements on a synthetic
+        # N = 65536 trajectory (virial stress + potential energy into a log file)
+        os.remove("restart.log"); os.remove("dump.xyz")
+        nth = 200
+        pool = [synth.synth_frame(256, 4000 + k) for k in range(8)]
+        gsdio.write_trajectory("thermo.gsd", [dict(box=pool[k % 8]["box"], position=pool[k % 8]["position"], diameter=pool[k % 8]["diameter"])
+                                              for k in range(nth)])
+        import pyglasstools as pglass
+        import pyglasstools.io as io
+        import pyglasstools.utils as utils
+        import pyglasstools.potential as pot
+        import pyglasstools.thermo as thermo
+        for frames_ in (range(0, 8), range(0, nth)):
+            pglass.reset()
+            if os.path.exists("restart.log"):
+                os.remove("restart.log")
+            poly12 = pot.polydisperse12(v0=1.0, eps=0.2, rcut=1.25)          # noqa: F841
+            mysystem = utils.read_gsd(filename="thermo.gsd", checkpointfile="restart.log")   # noqa: F841
+            calc = thermo.calculator()
+            log = io.logfile(filename="thermo.log", names=['virialstress_00', 'virialstress_11', 'virialstress_01', 'potentialenergy'], solver=calc)
+            split = {"update": 0.0, "run": 0.0, "save": 0.0}
+
+            def timed(obj, name, key):
+                f = getattr(obj, name)
+
+                def g(*a, **k):
+                    t = time.perf_counter()
+                    r = f(*a, **k)
+                    split[key] += time.perf_counter() - t
+                    return r
+                setattr(obj, name, g)
+            timed(calc, "update", "update")
+            timed(calc, "run", "run")
+            timed(log, "save", "save")
+            t0 = time.perf_counter()
+            pglass.analyze(frame_list=frames_)
+            dt = time.perf_counter() - t0
+            del log
+            pglass.reset()
+        out["cfg2_script"] = {"description": "example_scripts/thermo on a synthetic N = 65536 trajectory written to GSD, %d frames, virial stress + potential energy into the log file" % nth,
+                              "value": nth / dt, "unit": "frames/s", "ms_per_frame": dt / nth * 1e3,
+                              "ms_split": {k: v / nth * 1e3 for k, v in split.items()}}
     print(json.dumps(out))
 
 
