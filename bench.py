@@ -823,11 +823,13 @@ def main():
     hbm = peaks.get("hbm_gbs")
     # DRAM bytes of one gather launch: not a counter of THIS run -- the committed `ncu --set full` capture of the same
     # workload and kernel (profiles/), named so that a stale figure is visible
-    traffic, traffic_src = None, None
+    traffic, traffic_src, traffic_commit = None, None, None
     try:
         if args.workload == "cfg5" and not grid_mode:
             prof = os.path.join("profiles", "r2_ik_quad_full_cfg5.txt")
             for line in open(os.path.join(ROOT, prof)):
+                if line.startswith("# kernel source commit:"):
+                    traffic_commit = line.split(":", 1)[1].split()[0]
                 if line.startswith("traffic"):
                     traffic, traffic_src = float(line.split()[-1]), prof
     except Exception:
@@ -870,7 +872,7 @@ def main():
                          "items_per_unique_bond": 1.0,
                          "items_note": "the quad gather integrates every unique bond once (weight 1 or 1/2); the reference's half-bond formulation visits %.3f items per unique bond"
                                        % (float(np.mean(items_per_frame)) / max(1.0, float(np.mean(flops_per_frame)) / (15 * q + 9))),
-                         "traffic": traffic, "traffic_from_profile": traffic_src,
+                         "traffic": traffic, "traffic_from_profile": traffic_src, "traffic_profile_kernel_commit": traffic_commit,
                          "hbm_peak_gbs": hbm},
             "roofline_stages": {"bound": "hbm", "peak_gbs": hbm, "peak_source": "MEASURED_PEAKS.json hbm_gbs (driver-measured copy bandwidth)",
                                 "bytes_model": "SURVEY.md 8(d): cells 60 B/particle + 8 B/cell; bonds 32 B/particle + 36 B/half-bond",
