@@ -95,6 +95,46 @@ def test_particle_system_wraps_and_deletes_like_aboria():
     np.testing.assert_array_equal(ps.getAtomPosition()[0], [-4.75, 0.25, 0.25])
 
 
+def test_particle_system_refill_multithreaded_and_dtype_paths():
+    """ParticleSystem.update (data_gsd.update refills the object it holds): the fused multithreaded pass on float32 arrays
+    read in place, on float64 arrays, and through the sequence overload gives the same particles as a fresh object and as a
+    numpy restatement of enforce_domain; deleted particles compact the arrays, velocities / masses follow."""
+    rng = np.random.default_rng(4)
+    n, L = 200000, 10.0
+    pos = rng.uniform(-3 * L, 3 * L, (n, 3)).astype(np.float32)
+    pos[:, 2] = 0.0
+    pos[::1000, 2] = 0.75                                    # outside the slab: deleted
+    pos[7, 0] = np.inf
+    diam = rng.uniform(0.8, 1.2, n).astype(np.float32)
+    vel = rng.standard_normal((n, 3)).astype(np.float32)
+    mass = (1.0 + rng.integers(0, 2, n)).astype(np.float32)
+    ps, _ = make_system(np.zeros((4, 3)), L=L)               # a small system first: the refill grows it
+    ps.update(n, diam, mass, pos, vel)
+    alive = np.isfinite(pos).all(axis=1) & (pos[:, 2] >= -0.5) & (pos[:, 2] < 0.5)
+    want = pos[alive].astype(np.float64)
+    for k in range(2):
+        x = want[:, k]
+        for _ in range(8):
+            x = np.where(x < -L / 2, x + L, x)
+            x = np.where(x >= L / 2, x - L, x)
+        want[:, k] = x
+    assert len(ps) == int(alive.sum())
+    np.testing.assert_array_equal(ps.getAtomPosition(), want)
+    np.testing.assert_array_equal(ps.getAtomVelocity(), vel[alive].astype(np.float64))
+    assert ps.getDiameter() == diam[alive].astype(np.float64).tolist()
+    assert ps.getMass() == mass[alive].astype(np.float64).tolist()
+    assert not ps.getDisplacement().any()
+    fresh, _ = make_system(pos, diam=diam, L=L, vel=vel, mass=mass)
+    np.testing.assert_array_equal(fresh.getAtomPosition(), want)
+    ps64, _ = make_system(pos.astype(np.float64), diam=diam.astype(np.float64), L=L, vel=vel.astype(np.float64), mass=mass.astype(np.float64))
+    np.testing.assert_array_equal(ps64.getAtomPosition(), want)
+    sl = slice(1, 6)                                         # particles 1..5 survive: rows 0..4 of the compacted arrays
+    small, _ = make_system(pos[sl].tolist(), diam=diam[sl].tolist(), L=L, vel=vel[sl].tolist(), mass=mass[sl].tolist())   # sequences
+    np.testing.assert_array_equal(small.getAtomPosition(), want[:5])
+    ps.update(5, diam[sl], mass[sl], pos[sl], vel[sl])       # and it shrinks again
+    np.testing.assert_array_equal(ps.getAtomPosition(), want[:5])
+
+
 def test_get_neighbors_periodic_inclusive():
     pos = np.array([[4.5, 0, 0], [-4.5, 0, 0], [0, 0, 0], [3.5, 0, 0]], dtype=np.float64)
     ps, _ = make_system(pos)
