@@ -439,7 +439,7 @@ def main():
     ap.add_argument("--e2e-field", default="sym", choices=("auto", "full", "sym"),
                     help="end-to-end read-back: the reference's G x 4 layout, or the symmetric-packed G x 3 (xx, xy, yy); auto: full on one GPU, sym on several (the host's PCIe / memory path is shared)")
     ap.add_argument("--e2e-threads", type=int, default=2, choices=(1, 2), help="1: one host thread drives every end-to-end lane; 2: one host thread per lane")
-    ap.add_argument("--e2e-lanes", type=int, default=2, choices=(1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over (default 2, one host thread each: measured fastest, 2.38 ms per frame at cfg5); 1: one context and one host thread pipeline upload / stages / read-back on the context's three streams (2.54 ms; timed beside the default as e2e_one_context)")
+    ap.add_argument("--e2e-lanes", type=int, default=0, choices=(0, 1, 2, 3, 4), help="contexts the end-to-end trajectory loop is spread over. 0 (default): 2 on one GPU (one host thread each: measured fastest, 2.36-2.41 ms per frame at cfg5; the single-context pipeline, 2.54 ms, is timed beside it as e2e_one_context) and 1 under torchrun (N > 1: the host path is the bound there and more host threads per rank do not help); 1: one context and one host thread pipeline upload / stages / read-back on the context's three streams")
     ap.add_argument("--e2e-buffers", type=int, default=3, choices=(2, 3, 4), help="host field buffers the single-context loop reads back into in turn")
     ap.add_argument("--e2e-pos", default="xy", choices=("xy", "xyz"), help="host position rows of the end-to-end loop: xy = N x 2 float32 through pgt_frame_upload_xy (a 2-D frame has no z column: 12 B per particle cross the link; default), xyz = N x 3 through pgt_frame_upload (the GSD layout, 16 B)")
     ap.add_argument("--shard", default="frames", choices=["frames", "grid"])
@@ -454,6 +454,8 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.e2e_lanes == 0:
+        args.e2e_lanes = 2 if world == 1 else 1
     if args.impl == "reference":
         run_reference(args, wl, rank, world)
         return
